@@ -1,0 +1,110 @@
+// Shared declarations of libdfu3d.so (sm_100a).  See include/dfu3d.h for the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/dfu3d.h"
+
+#define DFU_NSLOTS 48
+
+struct dfu_ctx {
+  int device;
+  char err[512];
+  int64_t launches;
+  // growable device scratch slots (never shrink); slot ids are private to each .cu file range
+  void* slot[DFU_NSLOTS];
+  size_t slot_bytes[DFU_NSLOTS];
+  // pinned host staging for small read-backs
+  void* pinned;
+  size_t pinned_bytes;
+  // ---- bound batch (dfu_fuse_begin) ----
+  cudaStream_t stream;
+  int V;
+  dfu_view* views_host;       // malloc'd copy
+  dfu_fusion_params prm;
+  const void* lidar;
+  const float* depth;
+  const void* image;
+  const uint32_t* labelmap;
+  int max_lidar_cnt;
+  int64_t total_slots;
+  int bpv_pts;                // S1 blocks per view
+  int bpv_pix;                // S2 blocks per view
+  int64_t* cnt_project;       // host [V][3]
+  int64_t* off_project;       // host [3][V+1]  list offsets (F, A, B)
+  int64_t* cnt_vox;           // host [V]
+  int64_t* off_vox;           // host [V+1]
+  int stage;                  // 0 none, 1 begun, 2 projected, 3 densified
+  int total_inst;
+};
+
+// scratch slot ids
+enum {
+  SL_VIEWS = 0, SL_FLAGS, SL_PIX, SL_LABEL, SL_BLKCNT, SL_BLKOFF, SL_CUBTMP, SL_FLIST, SL_ALIST, SL_BLABEL,
+  SL_KEY, SL_TABLE, SL_VOXCNT, SL_VOXOFF, SL_REPZ, SL_REPY, SL_REPY_XYZ, SL_REPY_LABEL, SL_REPZ_XYZ, SL_STATS,
+  SL_SEGCNT, SL_SEGOFF, SL_IPARAMS, SL_ANGLES, SL_ISCRATCH_D, SL_ISCRATCH_I, SL_BOXES, SL_BOXCNT, SL_SEGOUT,
+  SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11
+};
+
+int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...);
+void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes);      // NULL on failure (error recorded)
+void* dfu_pinned(dfu_ctx* ctx, size_t bytes);
+
+#define DFU_CUDA(ctx, call)                                                                   \
+  do {                                                                                        \
+    cudaError_t e__ = (call);                                                                 \
+    if (e__ != cudaSuccess)                                                                   \
+      return dfu_set_err(ctx, DFU_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+  } while (0)
+
+#define DFU_LAUNCH_CHECK(ctx)                                                                 \
+  do {                                                                                        \
+    (ctx)->launches++;                                                                        \
+    cudaError_t e__ = cudaGetLastError();                                                     \
+    if (e__ != cudaSuccess)                                                                   \
+      return dfu_set_err(ctx, DFU_ERR_CUDA, "%s:%d launch: %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \
+  } while (0)
+
+#define DFU_SLOT(ctx, var, type, id, bytes)                 \
+  type var = (type)dfu_slot(ctx, id, bytes);                \
+  if (!var) return DFU_ERR_CUDA;
+
+// exclusive sum of n int32 -> int64 offsets (n+1 outputs, last = total), on `stream`
+int dfu_exclusive_sum_i32(dfu_ctx* ctx, cudaStream_t stream, const int32_t* in, int64_t* out, int64_t n);
+
+// ---------------------------------------------------------------- device helpers
+__device__ __forceinline__ unsigned long long dfu_order_f64(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+
+// The reference's float32 [x y z 1]·M (K = 4) as OpenBLAS evaluates it: one accumulator, k ascending,
+// FMA, first term a rounded product (measured; see oracle/restate.py:_sgemm_fma).
+__device__ __forceinline__ float dfu_row4_f32(float a0, float a1, float a2, float a3, const float* M, int j, int ld) {
+  float acc = __fmul_rn(a0, M[0 * ld + j]);
+  acc = __fmaf_rn(a1, M[1 * ld + j], acc);
+  acc = __fmaf_rn(a2, M[2 * ld + j], acc);
+  acc = __fmaf_rn(a3, M[3 * ld + j], acc);
+  return acc;
+}
+__device__ __forceinline__ double dfu_row4_f64(double a0, double a1, double a2, double a3, const float* M, int j, int ld) {
+  double acc = __dmul_rn(a0, (double)M[0 * ld + j]);
+  acc = __fma_rn(a1, (double)M[1 * ld + j], acc);
+  acc = __fma_rn(a2, (double)M[2 * ld + j], acc);
+  acc = __fma_rn(a3, (double)M[3 * ld + j], acc);
+  return acc;
+}
+
+// calibration_kitti.py:134-144 then :89-102 — pixel (col,row,depth) -> LiDAR frame, float64.
+__device__ __forceinline__ void dfu_backproject(const dfu_view& vw, int col, int row, float d, double& X, double& Y,
+                                                double& Z) {
+  double dd = (double)d;
+  double xr = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)col, (double)vw.cu), dd), (double)vw.fu), (double)vw.tx);
+  double yr = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)row, (double)vw.cv), dd), (double)vw.fv), (double)vw.ty);
+  X = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 0, 4);
+  Y = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 1, 4);
+  Z = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 2, 4);
+}
+
+__device__ __forceinline__ int dfu_warp_excl(unsigned ballot, int lane) { return __popc(ballot & ((1u << lane) - 1u)); }

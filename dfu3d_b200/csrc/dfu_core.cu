@@ -1,0 +1,104 @@
+// Context, scratch slots, error reporting, scan helper.
+#include <stdarg.h>
+#include <stdlib.h>
+#include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+#include "dfu_common.cuh"
+
+int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...) {
+  if (ctx) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  if (ctx->slot_bytes[id] >= bytes) return ctx->slot[id];
+  // growing: everything queued on the device may still read the old block
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess && ctx->slot[id]) e = cudaFree(ctx->slot[id]);
+  ctx->slot[id] = nullptr;
+  ctx->slot_bytes[id] = 0;
+  size_t want = bytes + bytes / 4 + 256;
+  if (e == cudaSuccess) e = cudaMalloc(&ctx->slot[id], want);
+  if (e != cudaSuccess) {
+    dfu_set_err(ctx, DFU_ERR_CUDA, "scratch slot %d: cudaMalloc(%zu) failed: %s", id, want, cudaGetErrorString(e));
+    return nullptr;
+  }
+  ctx->slot_bytes[id] = want;
+  return ctx->slot[id];
+}
+
+void* dfu_pinned(dfu_ctx* ctx, size_t bytes) {
+  if (ctx->pinned_bytes >= bytes) return ctx->pinned;
+  cudaDeviceSynchronize();
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  ctx->pinned = nullptr;
+  ctx->pinned_bytes = 0;
+  size_t want = bytes * 2 + 4096;
+  if (cudaMallocHost(&ctx->pinned, want) != cudaSuccess) {
+    dfu_set_err(ctx, DFU_ERR_CUDA, "cudaMallocHost(%zu) failed", want);
+    return nullptr;
+  }
+  ctx->pinned_bytes = want;
+  return ctx->pinned;
+}
+
+struct I32ToI64 {
+  __host__ __device__ int64_t operator()(const int32_t& v) const { return (int64_t)v; }
+};
+
+__global__ void k_scan_total(const int32_t* in, int64_t* out, int64_t n) {
+  // out[n] = out[n-1] + in[n-1]
+  if (threadIdx.x == 0 && blockIdx.x == 0) out[n] = (n > 0) ? out[n - 1] + (int64_t)in[n - 1] : 0;
+}
+
+int dfu_exclusive_sum_i32(dfu_ctx* ctx, cudaStream_t stream, const int32_t* in, int64_t* out, int64_t n) {
+  if (n > 0) {
+    cub::TransformInputIterator<int64_t, I32ToI64, const int32_t*> it(in, I32ToI64());
+    size_t tmp_bytes = 0;
+    DFU_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, out, n, stream));
+    void* tmp = dfu_slot(ctx, SL_CUBTMP, tmp_bytes);
+    if (!tmp) return DFU_ERR_CUDA;
+    DFU_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, it, out, n, stream));
+    ctx->launches += 2;
+  }
+  k_scan_total<<<1, 32, 0, stream>>>(in, out, n);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
+extern "C" int dfu_create(dfu_ctx** out, int device) {
+  if (!out) return DFU_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return DFU_ERR_CUDA;
+  if (cudaSetDevice(device) != cudaSuccess) return DFU_ERR_CUDA;
+  dfu_ctx* c = (dfu_ctx*)calloc(1, sizeof(dfu_ctx));
+  if (!c) return DFU_ERR_CUDA;
+  c->device = device;
+  *out = c;
+  return DFU_OK;
+}
+
+extern "C" void dfu_destroy(dfu_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  for (int i = 0; i < DFU_NSLOTS; i++)
+    if (ctx->slot[i]) cudaFree(ctx->slot[i]);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  free(ctx->views_host);
+  free(ctx->cnt_project);
+  free(ctx->off_project);
+  free(ctx->cnt_vox);
+  free(ctx->off_vox);
+  free(ctx);
+}
+
+extern "C" const char* dfu_last_error(const dfu_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+extern "C" int64_t dfu_launch_count(const dfu_ctx* ctx) { return ctx ? ctx->launches : 0; }

@@ -1,0 +1,419 @@
+// S2: pixel -> 3-D back-projection, height gate, angular-voxel dedup (evaluated once per view), cloud emit.
+// Reference arithmetic: tools/PENet/dataloaders/my_loader.py:507-509,532-542,554-557 (depth2pointsrgbpm),
+// :166-180 (to_sphere_coords), :247-275 (la_sampling2 / la_sampling20), :69-83 (voxel generators),
+// tools/PENet/dataloaders/calibration_kitti.py:89-102,134-144.
+//
+// The reference materialises new_p [M,8] float64, compacts it twice and re-voxelises the whole cloud once per
+// instance.  Here the pixel's linear index IS the point's rank (np.nonzero is row-major), so nothing is
+// materialised: three passes over the depth map resolve, per angular voxel, the opening pixel, the point count, the
+// min-z representative (la_sampling2) and the min-y representative (la_sampling20, quirk Q2) in a direct-address
+// table, and a fourth kernel gathers the representatives.
+#include <cuda_fp16.h>
+#include "dfu_common.cuh"
+
+#define S2_THREADS 256
+// theta in (1.5, pi] -> bins 3249..4071 ; atan in [-pi/2, pi/2] -> bins 1714..3285 (voxel 0.002f, origin -5)
+#define CT0 3249
+#define NT 823
+#define CF0 1714
+#define NF 1572
+#define NCELL (NT * NF)
+#define KEY_INVALID 0xFFFFFFFFu
+
+struct __align__(32) VoxCell {
+  unsigned long long minz;  // orderable bits of the smallest z
+  unsigned long long miny;
+  unsigned int first;       // opening pixel (smallest linear index)
+  unsigned int cnt;         // count - 1 (starts at 0xFFFFFFFF)
+  unsigned int argz;        // smallest pixel index attaining minz
+  unsigned int argy;
+};
+
+struct S2Prm {
+  int H, W, Hm, Wm, image_is_i32, max_per_voxel;
+  float min_depth;
+  double max_z, min_theta;
+};
+
+static S2Prm make_s2(const dfu_fusion_params* p) {
+  S2Prm s;
+  s.H = p->H; s.W = p->W; s.Hm = p->Hm; s.Wm = p->Wm; s.image_is_i32 = p->image_is_i32;
+  s.max_per_voxel = p->max_per_voxel; s.min_depth = p->min_depth; s.max_z = p->max_z; s.min_theta = p->min_theta;
+  return s;
+}
+
+// returns the table key of the pixel's point or KEY_INVALID; bit flags in *st: 1 valid pixel, 2 passes height gate,
+// 4 out-of-table (should not happen)
+__device__ __forceinline__ unsigned s2_key(const dfu_view& vw, const S2Prm& q, int pix, float d, double& X, double& Y,
+                                           double& Z, unsigned& st) {
+  st = 0;
+  // depth[depth<0.001]=0; nonzero(); depth>0   (my_loader.py:507-509)
+  if (!(d >= q.min_depth)) return KEY_INVALID;
+  st |= 1u;
+  const int row = pix / q.W, col = pix - row * q.W;
+  dfu_backproject(vw, col, row, d, X, Y, Z);
+  if (!(Z < q.max_z)) return KEY_INVALID;  // new_p[:, 2] < 1.  (:540)
+  st |= 2u;
+  // to_sphere_coords (:166-180)
+  double r = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(X, X), __dmul_rn(Y, Y)), __dmul_rn(Z, Z)));
+  double theta = acos(__ddiv_rn(Z, r));
+  double fan = atan(__ddiv_rn(Y, X));
+  if (!(theta > q.min_theta)) return KEY_INVALID;
+  // spconv v1 voxel coordinates with float32 constants (oracle/fakes.py)
+  const double vs = (double)0.002f;
+  double cr = floor(__ddiv_rn(__dadd_rn(r, 100.0), 200.0));
+  double ct = floor(__ddiv_rn(__dadd_rn(theta, 5.0), vs));
+  double cf = floor(__ddiv_rn(__dadd_rn(fan, 5.0), vs));
+  if (!(cr >= 0.0 && cr < 1.0 && ct >= 0.0 && ct < 5000.0 && cf >= 0.0 && cf < 5000.0)) return KEY_INVALID;
+  int it = (int)ct - CT0, jf = (int)cf - CF0;
+  if (it < 0 || it >= NT || jf < 0 || jf >= NF) {
+    st |= 4u;
+    return KEY_INVALID;
+  }
+  return (unsigned)(it * NF + jf);
+}
+
+#define LOAD_VIEW(vw, views, v)                                            \
+  __shared__ dfu_view vw;                                                  \
+  for (int i_ = threadIdx.x; i_ < (int)(sizeof(dfu_view) / 4); i_ += blockDim.x) \
+    ((uint32_t*)&vw)[i_] = ((const uint32_t*)((views) + (v)))[i_];       \
+  __syncthreads();
+
+// pass A: keys + table atomics.  stats int64 [V][4]: valid pixels, gated points, (voxels), overflow | [V][4+]: table misses
+__global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __restrict__ views, S2Prm q,
+                                                          const float* __restrict__ depth, unsigned* __restrict__ key,
+                                                          VoxCell* __restrict__ table,
+                                                          unsigned long long* __restrict__ stats) {
+  const int v = blockIdx.y;
+  LOAD_VIEW(vw, views, v);
+  const int npix = q.H * q.W;
+  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  unsigned st = 0, k = KEY_INVALID;
+  if (pix < npix) {
+    float d = __ldg(depth + (size_t)v * npix + pix);
+    double X, Y, Z;
+    k = s2_key(vw, q, pix, d, X, Y, Z, st);
+    key[(size_t)v * npix + pix] = k;
+    if (k != KEY_INVALID) {
+      VoxCell* c = table + (size_t)v * NCELL + k;
+      atomicMin(&c->first, (unsigned)pix);
+      atomicAdd(&c->cnt, 1u);
+      atomicMin(&c->minz, dfu_order_f64(Z));
+      atomicMin(&c->miny, dfu_order_f64(Y));
+    }
+  }
+  int n1 = __syncthreads_count(st & 1u);
+  int n2 = __syncthreads_count(st & 2u);
+  int n4 = __syncthreads_count(st & 4u);
+  if (threadIdx.x == 0) {
+    if (n1) atomicAdd(stats + v * 8 + 0, (unsigned long long)n1);
+    if (n2) atomicAdd(stats + v * 8 + 1, (unsigned long long)n2);
+    if (n4) atomicAdd(stats + v * 8 + 4, (unsigned long long)n4);
+  }
+}
+
+// pass B: arg-min resolution + opener count per block
+__global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __restrict__ views, S2Prm q,
+                                                          const float* __restrict__ depth,
+                                                          const unsigned* __restrict__ key, VoxCell* __restrict__ table,
+                                                          int32_t* __restrict__ blkcnt,
+                                                          unsigned long long* __restrict__ stats) {
+  const int v = blockIdx.y;
+  LOAD_VIEW(vw, views, v);
+  const int npix = q.H * q.W;
+  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  bool opener = false, over = false;
+  if (pix < npix) {
+    unsigned k = key[(size_t)v * npix + pix];
+    if (k != KEY_INVALID) {
+      VoxCell* c = table + (size_t)v * NCELL + k;
+      float d = __ldg(depth + (size_t)v * npix + pix);
+      const int row = pix / q.W, col = pix - row * q.W;
+      double X, Y, Z;
+      dfu_backproject(vw, col, row, d, X, Y, Z);
+      if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
+      if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
+      opener = (c->first == (unsigned)pix);
+      over = opener && (c->cnt + 1u > (unsigned)q.max_per_voxel);
+    }
+  }
+  int n = __syncthreads_count(opener);
+  int no = __syncthreads_count(over);
+  if (threadIdx.x == 0) {
+    blkcnt[v * gridDim.x + blockIdx.x] = n;
+    if (no) atomicAdd(stats + v * 8 + 3, (unsigned long long)no);
+  }
+}
+
+// pass C: ordered scatter of the voxel representatives (voxel ordinal = rank of the opening pixel)
+__global__ void __launch_bounds__(S2_THREADS) k_densify_c(S2Prm q, const unsigned* __restrict__ key,
+                                                          const VoxCell* __restrict__ table,
+                                                          const int64_t* __restrict__ blkoff, int32_t* __restrict__ repz,
+                                                          int32_t* __restrict__ repy) {
+  __shared__ int wsum[S2_THREADS / 32];
+  const int v = blockIdx.y;
+  const int npix = q.H * q.W;
+  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  bool opener = false;
+  const VoxCell* c = nullptr;
+  if (pix < npix) {
+    unsigned k = key[(size_t)v * npix + pix];
+    if (k != KEY_INVALID) {
+      c = table + (size_t)v * NCELL + k;
+      opener = (c->first == (unsigned)pix);
+    }
+  }
+  unsigned bal = __ballot_sync(0xffffffffu, opener);
+  if (lane == 0) wsum[w] = __popc(bal);
+  __syncthreads();
+  if (opener) {
+    int base = 0;
+    for (int i = 0; i < w; i++) base += wsum[i];
+    int64_t pos = blkoff[v * gridDim.x + blockIdx.x] + base + dfu_warp_excl(bal, lane);
+    repz[pos] = (int32_t)c->argz;
+    repy[pos] = (int32_t)c->argy;
+  }
+}
+
+__global__ void k_vox_view_offsets(const int64_t* __restrict__ blkoff, int V, int bpv, int64_t* out) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v <= V) out[v] = blkoff[(int64_t)v * bpv];
+}
+
+// gathers per voxel: min-y representative xyz (float64 SoA: x[n] y[n] z[n]) + label word, optional min-z xyz
+__global__ void __launch_bounds__(256) k_vox_gather(const dfu_view* __restrict__ views, S2Prm q, int V,
+                                                    const int64_t* __restrict__ voxoff, const float* __restrict__ depth,
+                                                    const uint32_t* __restrict__ labelmap,
+                                                    const int32_t* __restrict__ repz, const int32_t* __restrict__ repy,
+                                                    double* __restrict__ repy_xyz, uint32_t* __restrict__ repy_label,
+                                                    double* __restrict__ repz_xyz, int64_t total) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= total) return;
+  // binary search the view
+  int lo = 0, hi = V;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (voxoff[mid] <= t) lo = mid; else hi = mid;
+  }
+  const int v = lo;
+  const dfu_view& vw = views[v];
+  const size_t npix = (size_t)q.H * q.W;
+  {
+    int pix = repy[t];
+    int row = pix / q.W, col = pix - row * q.W;
+    double X, Y, Z;
+    dfu_backproject(vw, col, row, __ldg(depth + v * npix + pix), X, Y, Z);
+    repy_xyz[t] = X;
+    repy_xyz[total + t] = Y;
+    repy_xyz[2 * total + t] = Z;
+    repy_label[t] = labelmap ? __ldg(labelmap + ((size_t)v * q.Hm + row) * q.Wm + col) : 0u;
+  }
+  if (repz_xyz) {
+    int pix = repz[t];
+    int row = pix / q.W, col = pix - row * q.W;
+    double X, Y, Z;
+    dfu_backproject(vw, col, row, __ldg(depth + v * npix + pix), X, Y, Z);
+    repz_xyz[t] = X;
+    repz_xyz[total + t] = Y;
+    repz_xyz[2 * total + t] = Z;
+  }
+}
+
+// ---------------------------------------------------------------- cloud emit (my_loader.py:611-617, vis_utils.py:164)
+template <typename T> struct Cvt;
+template <> struct Cvt<double> { static __device__ __forceinline__ double f(double v) { return v; } };
+template <> struct Cvt<float>  { static __device__ __forceinline__ float f(double v) { return (float)v; } };
+template <> struct Cvt<__half> { static __device__ __forceinline__ __half f(double v) { return __double2half(v); } };
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_emit_cloud(const dfu_view* __restrict__ views, S2Prm q, int V,
+                                                    const int64_t* __restrict__ rowoff /*[V+1]*/,
+                                                    const int64_t* __restrict__ foff /*[V+1]*/,
+                                                    const int64_t* __restrict__ voxoff /*[V+1]*/,
+                                                    const float4* __restrict__ lidar, const int32_t* __restrict__ flist,
+                                                    const float* __restrict__ depth, const void* __restrict__ image,
+                                                    const int32_t* __restrict__ repz, T* __restrict__ out, int64_t total) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= total) return;
+  int lo = 0, hi = V;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (rowoff[mid] <= t) lo = mid; else hi = mid;
+  }
+  const int v = lo;
+  const dfu_view& vw = views[v];
+  const int64_t r = t - rowoff[v];
+  const int64_t nF = foff[v + 1] - foff[v];
+  double o[8];
+  if (r < nF) {
+    // new_lidar (:611-614): float32 values widened to float64, intensity * 10 in float64
+    float4 p = __ldg(lidar + vw.lidar_off + flist[foff[v] + r]);
+    o[0] = (double)p.x; o[1] = (double)p.y; o[2] = (double)p.z; o[3] = __dmul_rn((double)p.w, 10.0);
+    o[4] = 0; o[5] = 0; o[6] = 0; o[7] = 2.0;
+  } else {
+    const int pix = repz[voxoff[v] + (r - nF)];
+    const int row = pix / q.W, col = pix - row * q.W;
+    const size_t npix = (size_t)q.H * q.W;
+    double X, Y, Z;
+    dfu_backproject(vw, col, row, __ldg(depth + v * npix + pix), X, Y, Z);
+    o[0] = X; o[1] = Y; o[2] = Z; o[3] = 0;
+    const size_t ip = (((size_t)v * q.Hm + row) * q.Wm + col) * 3;
+    int R, G, B;
+    if (image == nullptr) { R = G = B = 0; }
+    else if (q.image_is_i32) { const int* im = (const int*)image; R = im[ip]; G = im[ip + 1]; B = im[ip + 2]; }
+    else { const uint8_t* im = (const uint8_t*)image; R = im[ip]; G = im[ip + 1]; B = im[ip + 2]; }
+    o[4] = __ddiv_rn((double)R, 3.0); o[5] = __ddiv_rn((double)G, 3.0); o[6] = __ddiv_rn((double)B, 3.0);  // image/3 (:539)
+    o[7] = 1.0;
+  }
+  T* dst = out + t * 8;
+#pragma unroll
+  for (int j = 0; j < 8; j++) dst[j] = Cvt<T>::f(o[j]);
+}
+
+// ---------------------------------------------------------------- C ABI
+extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int allow_overflow) {
+  if (!ctx || !(ctx->stage & 1)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_densify_sync: no batch bound");
+  const int V = ctx->V;
+  cudaStream_t st = ctx->stream;
+  S2Prm q = make_s2(&ctx->prm);
+  const int64_t npix = (int64_t)q.H * q.W;
+  if (npix >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_ARG, "depth map too large");
+  const int bpv = (int)((npix + S2_THREADS - 1) / S2_THREADS);
+  ctx->bpv_pix = bpv;
+  dfu_view* vd = (dfu_view*)ctx->slot[SL_VIEWS];
+  DFU_SLOT(ctx, key, unsigned*, SL_KEY, V * npix * sizeof(unsigned));
+  DFU_SLOT(ctx, table, VoxCell*, SL_TABLE, (size_t)V * NCELL * sizeof(VoxCell));
+  DFU_SLOT(ctx, stats, unsigned long long*, SL_VOXCNT, V * 8 * sizeof(unsigned long long));
+  DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, (int64_t)V * bpv * sizeof(int32_t));
+  DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
+  DFU_CUDA(ctx, cudaMemsetAsync(table, 0xFF, (size_t)V * NCELL * sizeof(VoxCell), st));
+  DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
+  dim3 grid(bpv, V);
+  k_densify_a<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, stats);
+  DFU_LAUNCH_CHECK(ctx);
+  k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, stats);
+  DFU_LAUNCH_CHECK(ctx);
+  int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, (int64_t)V * bpv);
+  if (rc) return rc;
+  k_vox_view_offsets<<<(V + 1 + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voxoff);
+  DFU_LAUNCH_CHECK(ctx);
+  // read back offsets + stats (one sync)
+  size_t nb = (V + 1) * sizeof(int64_t) + V * 8 * sizeof(unsigned long long);
+  char* pin = (char*)dfu_pinned(ctx, nb);
+  if (!pin) return DFU_ERR_CUDA;
+  DFU_CUDA(ctx, cudaMemcpyAsync(pin, voxoff, (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaMemcpyAsync(pin + (V + 1) * sizeof(int64_t), stats, V * 8 * sizeof(unsigned long long),
+                                cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  memcpy(ctx->off_vox, pin, (V + 1) * sizeof(int64_t));
+  const unsigned long long* hs = (const unsigned long long*)(pin + (V + 1) * sizeof(int64_t));
+  int64_t total_over = 0, total_miss = 0;
+  for (int v = 0; v < V; v++) {
+    ctx->cnt_vox[v] = ctx->off_vox[v + 1] - ctx->off_vox[v];
+    if (counts_host) {
+      counts_host[v * 4 + 0] = (int64_t)hs[v * 8 + 0];
+      counts_host[v * 4 + 1] = (int64_t)hs[v * 8 + 1];
+      counts_host[v * 4 + 2] = ctx->cnt_vox[v];
+      counts_host[v * 4 + 3] = (int64_t)hs[v * 8 + 3];
+    }
+    total_over += (int64_t)hs[v * 8 + 3];
+    total_miss += (int64_t)hs[v * 8 + 4];
+  }
+  const int64_t nvox = ctx->off_vox[V];
+  const int64_t cap = nvox > 0 ? nvox : 1;
+  DFU_SLOT(ctx, repz, int32_t*, SL_REPZ, cap * sizeof(int32_t));
+  DFU_SLOT(ctx, repy, int32_t*, SL_REPY, cap * sizeof(int32_t));
+  DFU_SLOT(ctx, repy_xyz, double*, SL_REPY_XYZ, cap * 3 * sizeof(double));
+  DFU_SLOT(ctx, repy_label, uint32_t*, SL_REPY_LABEL, cap * sizeof(uint32_t));
+  k_densify_c<<<grid, S2_THREADS, 0, st>>>(q, key, table, blkoff, repz, repy);
+  DFU_LAUNCH_CHECK(ctx);
+  if (nvox > 0) {
+    k_vox_gather<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, voxoff, ctx->depth, ctx->labelmap, repz, repy,
+                                                                 repy_xyz, repy_label, nullptr, nvox);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  ctx->stage |= 4;
+  if (total_miss > 0)
+    return dfu_set_err(ctx, DFU_ERR_DATA, "%lld points fell outside the angular voxel table", (long long)total_miss);
+  if (total_over > 0 && !allow_overflow)
+    return dfu_set_err(ctx, DFU_ERR_DATA,
+                       "%lld angular voxels hold more than max_per_voxel points (the reference keeps only the first "
+                       "ones in input order; not reproduced)", (long long)total_over);
+  return DFU_OK;
+}
+
+extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t capacity_rows, int64_t* row_off_host) {
+  if (!ctx || (ctx->stage & 6) != 6)
+    return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_cloud: project and densify stages must have run");
+  const int V = ctx->V;
+  cudaStream_t st = ctx->stream;
+  int64_t* rowoff_h = (int64_t*)dfu_pinned(ctx, (V + 1) * sizeof(int64_t));
+  if (!rowoff_h) return DFU_ERR_CUDA;
+  int64_t tot = 0;
+  for (int v = 0; v < V; v++) {
+    rowoff_h[v] = tot;
+    tot += ctx->cnt_project[v * 3 + 0] + ctx->cnt_vox[v];
+  }
+  rowoff_h[V] = tot;
+  if (row_off_host) memcpy(row_off_host, rowoff_h, (V + 1) * sizeof(int64_t));
+  if (!out) return DFU_OK;  // size query
+  if (capacity_rows < tot) return dfu_set_err(ctx, DFU_ERR_CAPACITY, "cloud needs %lld rows, capacity %lld", (long long)tot, (long long)capacity_rows);
+  if (tot == 0) return DFU_OK;
+  DFU_SLOT(ctx, rowoff, int64_t*, SL_SEGOUT, (V + 1) * sizeof(int64_t));
+  DFU_CUDA(ctx, cudaMemcpyAsync(rowoff, rowoff_h, (V + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  const int64_t* foff = (const int64_t*)ctx->slot[SL_STATS];  // [3][V+1], list 0 = FOV
+  const int64_t* voxoff = (const int64_t*)ctx->slot[SL_VOXOFF];
+  S2Prm q = make_s2(&ctx->prm);
+  dfu_view* vd = (dfu_view*)ctx->slot[SL_VIEWS];
+  unsigned nblk = (unsigned)((tot + 255) / 256);
+#define EMIT(T)                                                                                                   \
+  k_emit_cloud<T><<<nblk, 256, 0, st>>>(vd, q, V, rowoff, foff, voxoff, (const float4*)ctx->lidar,                 \
+                                        (const int32_t*)ctx->slot[SL_FLIST], ctx->depth, ctx->image,               \
+                                        (const int32_t*)ctx->slot[SL_REPZ], (T*)out, tot)
+  if (dtype == 0) EMIT(double);
+  else if (dtype == 1) EMIT(float);
+  else if (dtype == 2) EMIT(__half);
+  else return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_cloud: dtype must be 0, 1 or 2");
+#undef EMIT
+  DFU_LAUNCH_CHECK(ctx);
+  // rowoff_h (pinned) is re-used by later calls: make sure the H2D copy is done
+  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  return DFU_OK;
+}
+
+__global__ void k_soa_to_rows(const double* __restrict__ soa, double* __restrict__ rows, int64_t n) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  rows[t * 3 + 0] = soa[t];
+  rows[t * 3 + 1] = soa[n + t];
+  rows[t * 3 + 2] = soa[2 * n + t];
+}
+
+extern "C" int dfu_fuse_emit_voxels(dfu_ctx* ctx, int32_t* repz_pix, int32_t* repy_pix, double* repz_xyz,
+                                    double* repy_xyz, int64_t capacity) {
+  if (!ctx || !(ctx->stage & 4)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_voxels: densify stage not run");
+  const int64_t n = ctx->off_vox[ctx->V];
+  if (capacity < n) return dfu_set_err(ctx, DFU_ERR_CAPACITY, "voxel outputs need %lld entries", (long long)n);
+  if (n == 0) return DFU_OK;
+  cudaStream_t st = ctx->stream;
+  if (repz_pix) DFU_CUDA(ctx, cudaMemcpyAsync(repz_pix, ctx->slot[SL_REPZ], n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  if (repy_pix) DFU_CUDA(ctx, cudaMemcpyAsync(repy_pix, ctx->slot[SL_REPY], n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  if (repy_xyz) {
+    k_soa_to_rows<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const double*)ctx->slot[SL_REPY_XYZ], repy_xyz, n);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  if (repz_xyz) {
+    DFU_SLOT(ctx, tmp, double*, SL_REPZ_XYZ, n * 3 * sizeof(double));
+    S2Prm q = make_s2(&ctx->prm);
+    k_vox_gather<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((dfu_view*)ctx->slot[SL_VIEWS], q, ctx->V,
+                                                              (const int64_t*)ctx->slot[SL_VOXOFF], ctx->depth, ctx->labelmap,
+                                                              (const int32_t*)ctx->slot[SL_REPZ], (const int32_t*)ctx->slot[SL_REPY],
+                                                              (double*)ctx->slot[SL_REPY_XYZ], (uint32_t*)ctx->slot[SL_REPY_LABEL], tmp, n);
+    DFU_LAUNCH_CHECK(ctx);
+    k_soa_to_rows<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tmp, repz_xyz, n);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  return DFU_OK;
+}

@@ -1,0 +1,293 @@
+"""Batched fusion / noise-suppression / pseudo-box pipeline over libdfu3d.so.
+
+Host-side orchestration of the stages of the reference's ``depth2pointsrgbpm``
+(tools/PENet/dataloaders/my_loader.py:502-617) and ``save_depth_as_points``
+(tools/PENet/vis_utils.py:136-166) for a BATCH of camera views.  All arithmetic on points and
+pixels happens in the CUDA library; this module only derives per-view constants the way the
+reference derives them (float32 numpy on 3x4 / 4x4 matrices), packs argument structs and formats
+label text.
+"""
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _lib
+
+NUSC_NAMES = ['Car', 'Truck', 'Construction_vehicle', 'Bus', 'Trailer', 'Barrier', 'Motorcycle', 'Bicycle',
+              'Pedestrian', 'Traffic_cone']                                  # my_loader.py:634
+NUSC_VEHICLES = ('Car', 'Truck', 'Construction_vehicle', 'Bus', 'Trailer')   # my_loader.py:581
+NUSC_SMALL = ('Pedestrian', 'Bicycle', 'Motorcycle', 'Barrier', 'Traffic_cone')  # my_loader.py:591
+
+
+@dataclass
+class FusionConfig:
+    """Literals of the reference path, gathered in one place (SURVEY.md §5 'Config / flags').
+    Defaults = the ``nuscenes`` preset, i.e. tools/PENet/dataloaders/my_loader.py as shipped."""
+    bounds: tuple = (1600, 900)            # my_loader.py:526
+    min_depth: float = 0.001               # :507
+    max_z: float = 1.0                     # :540
+    plane_offset: float = 0.05             # :471
+    plane_range: tuple = (-54.0, 54.0, -54.0, 54.0)   # :471
+    min_theta: float = 1.5                 # :176
+    max_per_voxel: int = 100               # :73
+    gate_dist: float = 0.1                 # :603
+    cluster_R0: float = 3.0                # rectangle_fitting.py:36
+    cluster_Rd: float = 0.001              # rectangle_fitting.py:37
+    label_names: list = field(default_factory=lambda: list(NUSC_NAMES))
+    allow_voxel_overflow: bool = False
+
+    def instance_schedule(self, cls_name):
+        """Per-class filter schedule of my_loader.py:581-599.
+        Returns dict(lidar_enabled, lidar_nb, lidar_r, pseudo_nb, pseudo_r, car_aspect_rule)."""
+        if cls_name in NUSC_VEHICLES:
+            return dict(lidar_enabled=1, lidar_nb=1, lidar_r=3.0, pseudo_nb=1, pseudo_r=3.0,
+                        car_aspect_rule=int(cls_name == 'Car'))
+        if cls_name in NUSC_SMALL:
+            # quirk Q5 (my_loader.py:592-594): the LiDAR filter runs on an EMPTY cloud
+            return dict(lidar_enabled=0, lidar_nb=1, lidar_r=0.6, pseudo_nb=1, pseudo_r=0.6, car_aspect_rule=0)
+        # quirk Q9: the reference raises AttributeError for any other class
+        raise AttributeError("class %r is outside both class groups of my_loader.py:581,591 (the reference fails in "
+                             "BallQuery with numpy inputs)" % (cls_name,))
+
+
+def calib_constants(P2, R0, V2C):
+    """The derived matrices of calibration_kitti.py:74-79,95-101,110,120, computed with the SAME numpy
+    expressions the reference uses (float32 BLAS product, float32 inverse)."""
+    P2 = np.asarray(P2, np.float32).reshape(3, 4)
+    R0 = np.asarray(R0, np.float32).reshape(3, 3)
+    V2C = np.asarray(V2C, np.float32).reshape(3, 4)
+    M43 = np.dot(V2C.T, R0.T)
+    R0e = np.hstack((R0, np.zeros((3, 1), dtype=np.float32)))
+    R0e = np.vstack((R0e, np.zeros((1, 4), dtype=np.float32)))
+    R0e[3, 3] = 1
+    V2Ce = np.vstack((V2C, np.zeros((1, 4), dtype=np.float32)))
+    V2Ce[3, 3] = 1
+    inv44 = np.linalg.inv(np.dot(R0e, V2Ce).T)
+    fu, fv = P2[0, 0], P2[1, 1]
+    return dict(M43=np.ascontiguousarray(M43, np.float32), P2T=np.ascontiguousarray(P2.T, np.float32),
+                inv44=np.ascontiguousarray(inv44, np.float32), cu=P2[0, 2], cv=P2[1, 2], fu=fu, fv=fv,
+                tx=P2[0, 3] / (-fu), ty=P2[1, 3] / (-fv))
+
+
+def fill_view(rec, consts, plane=None, lidar_off=0, lidar_cnt=0, n_inst=0, slot_off=0, inst_off=0):
+    rec['M43'] = consts['M43'].reshape(-1)
+    rec['P2T'] = consts['P2T'].reshape(-1)
+    rec['inv44'] = consts['inv44'].reshape(-1)
+    for k in ('cu', 'cv', 'fu', 'fv', 'tx', 'ty'):
+        rec[k] = consts[k]
+    rec['plane'] = np.asarray(plane if plane is not None else (0, 0, 1, 1e9), np.float64)
+    rec['lidar_off'] = lidar_off
+    rec['lidar_cnt'] = lidar_cnt
+    rec['n_inst'] = n_inst
+    rec['slot_off'] = slot_off
+    rec['inst_off'] = inst_off
+
+
+def fusion_params(cfg, H, W, Hm, Wm, image_is_i32=False, round_mode=0):
+    p = np.zeros(1, _lib.FUSION_DTYPE)
+    p['H'], p['W'], p['Hm'], p['Wm'] = H, W, Hm, Wm
+    p['bound_x'], p['bound_y'] = cfg.bounds
+    p['round_mode'] = round_mode
+    p['image_is_i32'] = int(image_is_i32)
+    p['min_depth'] = cfg.min_depth
+    p['max_z'] = cfg.max_z
+    p['plane_offset'] = cfg.plane_offset
+    p['plane_range'] = np.asarray(cfg.plane_range, np.float64)
+    p['min_theta'] = cfg.min_theta
+    p['max_per_voxel'] = cfg.max_per_voxel
+    return p
+
+
+def search_angles_cs():
+    """cos / sin of the 89 search angles of rectangle_fitting.py:117-122, evaluated on the host with the
+    same numpy calls (a 1.4 kB constant table)."""
+    dtheta = np.deg2rad(1.0)
+    th = np.arange(0.0, np.pi / 2.0 - dtheta, dtheta)
+    return np.ascontiguousarray(np.stack([np.cos(th), np.sin(th)], 1)), th
+
+
+@dataclass
+class ViewBatch:
+    """Device-resident inputs of V camera views."""
+    lidar: torch.Tensor            # [sum N, 4] float32 cuda
+    sweeps: list                   # [(offset, count)] rows of `lidar`
+    view_sweep: list               # sweep index per view
+    calibs: list                   # per view (P2, R0, V2C)
+    planes: list                   # per view plane[4] float64
+    depth: torch.Tensor            # [V, H, W] float32 cuda
+    image: torch.Tensor            # [V, Hm, Wm, 3] uint8 (or int32) cuda
+    masks: torch.Tensor            # [sum n_inst, Hm, Wm] uint8 (or float32) cuda
+    n_inst: list                   # per view
+    classes: list                  # per view int array [n_inst]
+    boxes2d: list                  # per view float32 [n_inst, 4]
+    thing_classes: list = field(default_factory=lambda: list(NUSC_NAMES))
+    labelmap: torch.Tensor = None  # [V, Hm, Wm] uint32 as int32 storage (filled by pack)
+
+
+@dataclass
+class FusionResult:
+    cloud: torch.Tensor            # [rows, 8]
+    row_off: np.ndarray            # [V+1]
+    counts_project: np.ndarray     # [V,3]  nFOV, nAbove, nInBounds
+    counts_densify: np.ndarray     # [V,4]  valid pixels, gated, voxels, overflowing voxels
+    boxes: np.ndarray = None       # [nbox, 24] float64 records (include/dfu3d.h)
+    seg_counts: np.ndarray = None  # [n_inst_total, 6]
+    box2d: np.ndarray = None       # [nbox, 4] float32
+    label_lines: list = None       # per view list of KITTI label lines
+
+
+class FusionPipeline(object):
+    def __init__(self, device=0, config=None):
+        self.cfg = config or FusionConfig()
+        self.ctx = _lib.default_context(device)
+        self.device = self.ctx.device
+        self.lib = self.ctx.lib
+        self._angles, _ = search_angles_cs()
+
+    # ------------------------------------------------------------------ helpers
+    def build_views(self, vb):
+        V = len(vb.view_sweep)
+        views = np.zeros(V, _lib.VIEW_DTYPE)
+        slot = 0
+        inst = 0
+        for v in range(V):
+            off, cnt = vb.sweeps[vb.view_sweep[v]]
+            c = calib_constants(*vb.calibs[v])
+            fill_view(views[v], c, vb.planes[v], off, cnt, vb.n_inst[v], slot, inst)
+            slot += cnt
+            inst += vb.n_inst[v]
+        return views
+
+    def pack_masks(self, vb, views=None):
+        V = len(vb.view_sweep)
+        Hm, Wm = vb.image.shape[1:3] if vb.image is not None else vb.masks.shape[1:3]
+        views = self.build_views(vb) if views is None else views
+        vd = torch.from_numpy(views.view(np.uint8).reshape(V, -1)).to(self.device)
+        lm = torch.empty((V, Hm, Wm), dtype=torch.int32, device=self.device)
+        masks = vb.masks
+        is_f32 = int(masks.dtype == torch.float32)
+        if not is_f32 and masks.dtype not in (torch.uint8, torch.bool):
+            raise TypeError('masks must be uint8/bool or float32')
+        if masks.dtype == torch.bool:
+            masks = masks.view(torch.uint8)
+        mptr = _lib.dptr(masks.contiguous()) if masks.numel() else None
+        self.ctx.check(self.lib.dfu_pack_masks(self.ctx.h, self.ctx.stream, V, _lib.dptr(vd), mptr, is_f32, Hm, Wm,
+                                               _lib.dptr(lm)))
+        vb.labelmap = lm
+        return lm
+
+    # ------------------------------------------------------------------ the pipeline
+    def run(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=True):
+        cfg = self.cfg
+        V = len(vb.view_sweep)
+        H, W = vb.depth.shape[1:3]
+        Hm, Wm = vb.image.shape[1:3]
+        views = self.build_views(vb)
+        if vb.labelmap is None:
+            self.pack_masks(vb, views)
+        prm = fusion_params(cfg, H, W, Hm, Wm, image_is_i32=(vb.image.dtype == torch.int32))
+        self.ctx.check(self.lib.dfu_fuse_begin(self.ctx.h, self.ctx.stream, V, _lib.hptr(views), _lib.hptr(prm),
+                                               _lib.dptr(vb.lidar), _lib.dptr(vb.depth), _lib.dptr(vb.image),
+                                               _lib.dptr(vb.labelmap)))
+        cp = np.zeros((V, 3), np.int64)
+        self.ctx.check(self.lib.dfu_fuse_project_sync(self.ctx.h, _lib.hptr(cp)))
+        cd = np.zeros((V, 4), np.int64)
+        self.ctx.check(self.lib.dfu_fuse_densify_sync(self.ctx.h, _lib.hptr(cd), int(cfg.allow_voxel_overflow)))
+        row_off = np.zeros(V + 1, np.int64)
+        self.ctx.check(self.lib.dfu_fuse_emit_cloud(self.ctx.h, None, 0, 0, _lib.hptr(row_off)))
+        dt = {torch.float64: 0, torch.float32: 1, torch.float16: 2}[cloud_dtype]
+        cloud = torch.empty((int(row_off[-1]), 8), dtype=cloud_dtype, device=self.device)
+        self.ctx.check(self.lib.dfu_fuse_emit_cloud(self.ctx.h, _lib.dptr(cloud), dt, cloud.shape[0], _lib.hptr(row_off)))
+        res = FusionResult(cloud=cloud, row_off=row_off, counts_project=cp, counts_densify=cd)
+        if instances:
+            self.run_instances(vb, res, want_lines=want_lines)
+        return res
+
+    def inst_params(self, vb):
+        cfg = self.cfg
+        tot = int(sum(vb.n_inst))
+        ip = np.zeros(tot, _lib.INST_DTYPE)
+        k = 0
+        for v in range(len(vb.view_sweep)):
+            for j in range(vb.n_inst[v]):
+                cls = int(vb.classes[v][j])
+                sch = cfg.instance_schedule(vb.thing_classes[cls])
+                ip[k]['cls'] = cls
+                ip[k]['lidar_enabled'] = sch['lidar_enabled']
+                ip[k]['lidar_nb'] = sch['lidar_nb']
+                ip[k]['lidar_every_k'] = sch.get('lidar_every_k', 1)
+                ip[k]['pseudo_nb'] = sch['pseudo_nb']
+                ip[k]['pseudo_every_k'] = sch.get('pseudo_every_k', 1)
+                ip[k]['car_aspect_rule'] = sch['car_aspect_rule']
+                ip[k]['lidar_r'] = sch['lidar_r']
+                ip[k]['pseudo_r'] = sch['pseudo_r']
+                ip[k]['gate_dist'] = cfg.gate_dist
+                ip[k]['cluster_R0'] = cfg.cluster_R0
+                ip[k]['cluster_Rd'] = cfg.cluster_Rd
+                k += 1
+        return ip
+
+    def run_instances(self, vb, res, want_lines=True, capacity=None):
+        V = len(vb.view_sweep)
+        ip = self.inst_params(vb)
+        tot = ip.shape[0]
+        cap = capacity or max(64, 16 * tot)
+        while True:
+            boxes = np.zeros((cap, _lib.BOX_DOUBLES), np.float64)
+            nb = np.zeros(1, np.int64)
+            segc = np.zeros((max(tot, 1), 6), np.int64)
+            rc = self.lib.dfu_fuse_instances_sync(self.ctx.h, _lib.hptr(ip), tot, _lib.hptr(self._angles),
+                                                  self._angles.shape[0], _lib.hptr(boxes), cap, _lib.hptr(nb), _lib.hptr(segc))
+            if rc == -3 and int(nb[0]) > cap:      # DFU_ERR_CAPACITY: retry with the reported size
+                cap = int(nb[0])
+                continue
+            self.ctx.check(rc)
+            break
+        res.boxes = boxes[:int(nb[0])]
+        res.seg_counts = segc[:tot]
+        b2 = np.concatenate([np.asarray(b, np.float32).reshape(-1, 4) for b in vb.boxes2d] + [np.zeros((0, 4), np.float32)], 0)
+        res.box2d = b2[res.boxes[:, 1].astype(np.int64)] if res.boxes.shape[0] else np.zeros((0, 4), np.float32)
+        if want_lines:
+            res.label_lines = [[] for _ in range(V)]
+            for rec, bb in zip(res.boxes, res.box2d):
+                if rec[20] != 0:       # skipped by the Car aspect rule (my_loader.py:651)
+                    continue
+                res.label_lines[int(rec[0])].append(format_label_line(self.cfg.label_names[int(rec[3])], rec, bb))
+        return res
+
+
+def format_label_line(name, rec, box2d):
+    """The KITTI label line of my_loader.py:680 with Python's str() of float64 / float32 values."""
+    f = lambda x: str(np.float64(x))
+    g = lambda x: str(np.float32(x))
+    return (name + ' ' + str(0) + ' ' + str(0) + ' ' + f(rec[4]) + ' ' + g(box2d[0]) + ' ' + g(box2d[1]) + ' ' +
+            g(box2d[2]) + ' ' + g(box2d[3]) + ' ' + f(rec[5]) + ' ' + f(rec[6]) + ' ' + f(rec[7]) + ' ' + f(rec[8]) +
+            ' ' + f(rec[9]) + ' ' + f(rec[10]) + ' ' + f(rec[11]) + '\n')
+
+
+def batch_from_frames(frames, device, thing_classes=None):
+    """ViewBatch from dfu3d_b200.synth frames (each frame: one sweep, n views)."""
+    lidars, sweeps, view_sweep, calibs, planes, depth, image, masks, n_inst, classes, boxes2d = ([] for _ in range(11))
+    off = 0
+    for fi, fr in enumerate(frames):
+        L = fr['lidar'].to(device=device, dtype=torch.float32)
+        lidars.append(L)
+        sweeps.append((off, L.shape[0]))
+        off += L.shape[0]
+        for vw in fr['views']:
+            view_sweep.append(fi)
+            calibs.append((vw['P2'], vw['R0'], vw['V2C']))
+            planes.append(vw['plane'])
+            depth.append(vw['depth'].to(device))
+            image.append(vw['image'].to(device))
+            masks.append(vw['masks'].to(device))
+            n_inst.append(int(vw['masks'].shape[0]))
+            classes.append(np.asarray(vw['classes'], np.int64))
+            boxes2d.append(np.asarray(vw['boxes2d'], np.float32).reshape(-1, 4))
+    tc = thing_classes or frames[0]['views'][0]['thing_classes']
+    return ViewBatch(lidar=torch.cat(lidars, 0).contiguous(), sweeps=sweeps, view_sweep=view_sweep, calibs=calibs,
+                     planes=planes, depth=torch.stack(depth, 0).contiguous(), image=torch.stack(image, 0).contiguous(),
+                     masks=torch.cat(masks, 0).contiguous(), n_inst=n_inst, classes=classes, boxes2d=boxes2d,
+                     thing_classes=list(tc))

@@ -1,0 +1,193 @@
+/*
+ * dfu3d.h — C ABI of libdfu3d.so: the sm_100a CUDA implementation of DFU3D's data-level
+ * fusion / noise-suppression / pseudo-box path.
+ *
+ * The reference has no FFI: its boundary is a set of Python functions under
+ * /root/reference/tools/PENet.  Each entry point below names the reference
+ * function(s) whose arithmetic it replaces (file:line, relative to tools/PENet).  All pointers
+ * that are not marked "host" are DEVICE pointers owned by the caller (torch allocates); the
+ * library never frees them.  Scratch lives in the context.  All launches go to the caller's
+ * cudaStream_t (passed as void*).  Return value: 0 = ok, negative = dfu_status; the message of
+ * the last failure is returned by dfu_last_error().  Capacity overflow is an error, never a
+ * silent truncation.  Functions whose names end in _sync return host-visible counts and
+ * therefore synchronise the stream once before returning.
+ */
+#ifndef DFU3D_H
+#define DFU3D_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dfu_ctx dfu_ctx;
+
+enum dfu_status {
+  DFU_OK = 0,
+  DFU_ERR_ARG = -1,        /* bad argument */
+  DFU_ERR_CUDA = -2,       /* CUDA runtime error (see dfu_last_error) */
+  DFU_ERR_CAPACITY = -3,   /* a caller-provided buffer is too small */
+  DFU_ERR_UNSUPPORTED = -4,
+  DFU_ERR_DATA = -5        /* input violates a documented precondition (e.g. > 32 instances) */
+};
+
+#define DFU_MAX_INSTANCES 32   /* instance masks per view packed into one uint32 label word */
+#define DFU_N_ANGLES_MAX 96    /* rectangle search angles (reference: 89) */
+#define DFU_BOX_DOUBLES 24     /* doubles per box record, see dfu_instances_run */
+
+/* Per-view constants.  Everything here is derived on the host exactly as the reference derives it
+ * (float32 products / float32 inverse: dataloaders/calibration_kitti.py:62-79,95-101,110). */
+typedef struct dfu_view {
+  float M43[12];       /* V2C^T · R0^T, row-major 4x3      (lidar_to_rect, calibration_kitti.py:110) */
+  float P2T[12];       /* P2^T, row-major 4x3              (rect_to_img,   calibration_kitti.py:120) */
+  float inv44[16];     /* inv((R0ext · V2Cext)^T), 4x4     (rect_to_lidar, calibration_kitti.py:101) */
+  float cu, cv, fu, fv, tx, ty;                         /* calibration_kitti.py:74-79 */
+  int32_t lidar_cnt;   /* LiDAR rows of this view (before the FOV cull) */
+  int32_t n_inst;      /* instance masks of this view (<= DFU_MAX_INSTANCES) */
+  double plane[4];     /* ground plane a,b,c,d (dataloaders/my_loader.py:448-469 output) */
+  int64_t lidar_off;   /* first row of this view's sweep in lidar_xyzi (views may share a sweep) */
+  int64_t slot_off;    /* first per-point output slot of this view (exclusive sum of lidar_cnt) */
+  int32_t inst_off;    /* first instance of this view in the flat per-instance arrays */
+  int32_t pad0;
+} dfu_view;
+
+typedef struct dfu_fusion_params {
+  int32_t H, W;              /* depth map rows / cols (reference crop: vis_utils.py:147,161) */
+  int32_t Hm, Wm;            /* label-map (mask / image) rows / cols, Hm >= H, Wm >= W */
+  int32_t bound_x, bound_y;  /* pixel bounds of the label-inheritance loop (my_loader.py:526: 1600, 900) */
+  int32_t round_mode;        /* 0 = np.round half-to-even (my_loader.py:520); 1 = truncate (my_loader.py:113) */
+  int32_t image_is_i32;      /* image dtype: 0 = uint8 [.,3], 1 = int32 [.,3] */
+  float   min_depth;         /* my_loader.py:507 (0.001) */
+  float   pad1;
+  double  max_z;             /* height gate of my_loader.py:540 (1.0) */
+  double  plane_offset;      /* my_loader.py:471 (0.05) */
+  double  plane_range[4];    /* x lo, x hi, y lo, y hi (my_loader.py:471: -54, 54, -54, 54) */
+  double  min_theta;         /* to_sphere_coords gate, my_loader.py:176 (1.5) */
+  int32_t max_per_voxel;     /* my_loader.py:73 (100) */
+  int32_t pad2;
+} dfu_fusion_params;
+
+/* Per-instance filter schedule (my_loader.py:581-599; variants my_loader_KittiPandasetWaymo.py:780-823). */
+typedef struct dfu_inst_params {
+  int32_t cls;               /* index into thing_classes, copied into the box record */
+  int32_t lidar_enabled;     /* 0 reproduces quirk Q5 (LiDAR filter on an empty cloud, my_loader.py:592-594) */
+  int32_t lidar_nb, lidar_every_k;
+  int32_t pseudo_nb, pseudo_every_k;
+  int32_t car_aspect_rule;   /* 1: skip boxes with aspect > 5 (my_loader.py:651) */
+  int32_t pad;
+  double  lidar_r, pseudo_r;
+  double  gate_dist;         /* BallQuery C (my_loader.py:603: 0.1) */
+  double  cluster_R0, cluster_Rd;   /* rectangle_fitting.py:36-37 */
+} dfu_inst_params;
+
+int  dfu_create(dfu_ctx** out, int device);
+void dfu_destroy(dfu_ctx* ctx);
+const char* dfu_last_error(const dfu_ctx* ctx);
+/* number of kernels this context has launched since creation (bench.py: gpu_launches) */
+int64_t dfu_launch_count(const dfu_ctx* ctx);
+
+/* ---- S1: LiDAR -> image projection with label inheritance --------------------------------------
+ * Replaces Calibration.lidar_to_rect / rect_to_img / lidar_to_img (calibration_kitti.py:104-132),
+ * get_fov_flag (vis_utils.py:108-123), above_plane (my_loader.py:471-484) and the per-instance
+ * getpixel loop (my_loader.py:518-530).  One thread per (view, LiDAR row).
+ *   lidar_xyzi  float4 rows [x y z i]
+ *   labelmap    uint32 [V][Hm][Wm], bit j = instance j of the view (dfu_pack_masks); may be NULL
+ * Per-slot outputs (slot = view.slot_off + row), any may be NULL:
+ *   out_uv   float2  un-rounded u,v      out_depth float   rect depth
+ *   out_pix  int2    rounded/truncated x,y
+ *   out_flags uint8  bit0 FOV (un-rounded u,v inside H x W and depth >= 0), bit1 above-plane,
+ *                    bit2 rounded pixel inside bound_x x bound_y
+ *   out_label uint32 label word at the rounded pixel (0 if outside the label map or bounds)
+ */
+int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, int max_lidar_cnt,
+                      const dfu_fusion_params* prm_host, const void* lidar_xyzi, const uint32_t* labelmap,
+                      float* out_uv, float* out_depth, int32_t* out_pix, uint8_t* out_flags, uint32_t* out_label);
+
+/* masks [sum n_inst][Hm][Wm] (uint8 when is_f32 == 0, float when 1; != 0 means set) -> labelmap.
+ * Replaces Image.fromarray(np.uint8(mask)) (my_loader.py:525). */
+int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, const void* masks, int is_f32,
+                   int Hm, int Wm, uint32_t* labelmap);
+
+/* load_depth_input (my_loader.py:102-122): FOV cull, truncating pixel index, last-writer-wins
+ * scatter of the rect depth into out_depth [V][H][W] (float64, zero elsewhere). */
+int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, int max_lidar_cnt,
+                     const dfu_fusion_params* prm_host, const void* lidar_xyzi, double* out_depth);
+
+/* ---- the batched pipeline --------------------------------------------------------------------
+ * dfu_fuse_begin binds a batch of V views; the stage calls below then run on the bound batch and
+ * keep their intermediates in the context.  Stage order: project -> densify -> instances.
+ */
+int dfu_fuse_begin(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host, const dfu_fusion_params* prm_host,
+                   const void* lidar_xyzi, const float* depth /*[V][H][W]*/, const void* image /*[V][Hm][Wm][3]*/,
+                   const uint32_t* labelmap /*[V][Hm][Wm]*/);
+
+/* S1 + ordered compaction (vis_utils.py:152-154, my_loader.py:511-530).  counts_host [V][3]:
+ * rows after the FOV cull, rows above the plane, of those rows with an in-bounds pixel. */
+int dfu_fuse_project_sync(dfu_ctx* ctx, int64_t* counts_host);
+
+/* S2: pixel -> 3-D back-projection + height gate + angular-voxel dedup evaluated once
+ * (my_loader.py:507-509,532-542,554-557,166-180,247-275; calibration_kitti.py:89-102,134-144).
+ * counts_host [V][4]: valid pixels M, points passing the height gate, angular voxels, voxels with
+ * more than max_per_voxel points (must be 0: DFU_ERR_DATA otherwise unless allow_overflow). */
+int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int allow_overflow);
+
+/* Copy-out of the fused cloud (my_loader.py:611-617 + vis_utils.py:164): rows [x y z i*10 0 0 0 2]
+ * for the FOV-culled LiDAR then [x y z 0 R/3 G/3 B/3 1] per angular voxel (first-appearance
+ * order).  out is [sum over views (nF + nVox)][8]; dtype 0 = float64, 1 = float32, 2 = float16.
+ * row_off_host [V+1] receives the first row of each view. */
+int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t capacity_rows, int64_t* row_off_host);
+
+/* Per-voxel debug / parity outputs: linear pixel index (row*W+col) of the min-z and min-y
+ * representative of each angular voxel, and its xyz (float64).  Any pointer may be NULL. */
+int dfu_fuse_emit_voxels(dfu_ctx* ctx, int32_t* repz_pix, int32_t* repy_pix, double* repz_xyz, double* repy_xyz,
+                         int64_t capacity);
+
+/* Per-slot S1 results of the bound batch (same layout as dfu_project_label). */
+int dfu_fuse_emit_project(dfu_ctx* ctx, int32_t* out_pix, uint8_t* out_flags, uint32_t* out_label);
+
+/* Instances: gather of inherited LiDAR points and masked pseudo points, radius filters
+ * (Open3D remove_radius_outlier / uniform_down_sample call sites my_loader.py:569-599), BallQuery
+ * gate (:489-494,602-604), adaptive-range clustering (rectangle_fitting.py:161-191), rectangle
+ * search (:113-159,83-111) and the GenerateAnns arithmetic (my_loader.py:633-684).
+ *   inst_params_host [total instances]; boxes2d is copied through by the host wrapper.
+ *   angles_cs_host   [n_angles][2] cos, sin of the search angles (host-evaluated np.cos/np.sin)
+ * Box record (DFU_BOX_DOUBLES doubles): 0 view, 1 instance (global), 2 cluster ordinal, 3 cls,
+ *   4 alpha, 5 h, 6 w, 7 l, 8 x, 9 y, 10 z (rect frame), 11 ry, 12 n points, 13 near-tie flag,
+ *   14 theta_fit, 15 cx, 16 cy, 17 cz (lidar frame), 18 best cost, 19 runner-up cost,
+ *   20 skipped-by-aspect flag, 21..23 reserved.
+ * Records arrive sorted by (view, instance, cluster).  n_boxes_host receives the count.
+ * seg_counts_host [total instances][6] (may be NULL): nL, nP, nL', nP', nP'', clusters. */
+int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* inst_params_host, int n_inst_total,
+                            const double* angles_cs_host, int n_angles, double* boxes_out_host, int64_t capacity_boxes,
+                            int64_t* n_boxes_host, int64_t* seg_counts_host);
+
+/* ---- stand-alone operators on caller-provided point sets (segments) -----------------------------
+ * xyz: float64 [n][3] rows.  seg_off_host [nseg+1].  Used by the drop-in Python functions and by
+ * the filter benchmarks. */
+
+/* Open3D remove_radius_outlier semantics (oracle/fakes.py): keep iff #{q: |p-q|^2 < r^2} > nb. */
+int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
+                      const double* radius_host, const int32_t* nb_host, uint8_t* out_keep, int32_t* out_count /*nullable*/);
+
+/* Open3D remove_statistical_outlier semantics: mean distance to the k nearest (self included),
+ * mu / Bessel sigma over the segment, keep iff 0 < mean < mu + ratio*sigma.
+ * out_mean float64 [n] (nullable), out_stats_host [nseg][2] = mu, sigma (nullable; forces a sync). */
+int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
+                   int k, double std_ratio, uint8_t* out_keep, double* out_mean, double* out_stats_host);
+
+/* BallQuery gate: keep[i] = min_j |query_i - ref_j| < max_dist. */
+int dfu_nn_gate(dfu_ctx* ctx, void* stream, const double* query_xyz, int64_t nq, const double* ref_xyz, int64_t nr,
+                double max_dist, uint8_t* out_keep);
+
+/* LShapeFitting.fitting (rectangle_fitting.py:39-53) on one point set: cluster id per point
+ * (numbered by minimum point index) and one rectangle a[4] b[4] c[4] + theta + 2 costs per cluster
+ * (rect_out_host [cap][16]). */
+int dfu_lshape_fit_sync(dfu_ctx* ctx, void* stream, const double* xy /*[n][2]*/, int64_t n, double R0, double Rd,
+                        const double* angles_cs_host, int n_angles, int32_t* out_cluster /*dev [n]*/,
+                        double* rect_out_host, int64_t capacity, int64_t* n_clusters_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DFU3D_H */
