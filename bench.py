@@ -1,0 +1,327 @@
+"""bench.py — pseudo-box frames/s of the DFU3D fusion / noise-suppression / pseudo-box path on B200.
+
+One "step" = one pass of the full path (mask packing, S1 projection + label inheritance, S2
+densification + angular dedup, per-instance radius filters + BallQuery gate + clustering + box
+fitting, fp16 cloud emit) over one batch of synthetic nuScenes-shaped frames
+(BASELINE.json configs[3]: 10-sweep frames, 6 cameras of 1600x900, batch 64, one B200).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl reference]
+
+N > 1: launched by torchrun, one rank per GPU, frames sharded frame-wise (weak scaling: every rank
+processes its own F frames), no data-path collective; the timed region is bracketed by a barrier and
+torch.cuda.synchronize() and the max over ranks is reported.
+
+The line carries: value (inputs resident in HBM), e2e (host pinned buffers in, cloud + boxes back to
+the host, through dfu3d_b200.pipeline.FusionPipeline — the public API), roofline (dominant kernel,
+CUDA-event time inside the timed region, algorithmic bytes of SURVEY.md §8(d)), cpu_baseline (the
+oracle port on the host cores, bounded sample; rank 0, N=1 only), clocks, gpu_launches.
+
+--impl reference: the reference's CPU implementation of the path.  The reference is pure Python over
+numpy / Open3D / spconv / sklearn (no native code) and /root/reference does not exist on the GPU box,
+so this arm times the oracle port (oracle/restate.py: the reference's first-party arithmetic restated
+in numpy + the restated third-party filters) on all host cores, one whole view per worker process.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'pseudo-box frames/s (nuScenes-shaped)'
+UNIT = 'frames/s'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--frames', type=int, default=int(os.environ.get('DFU_BENCH_FRAMES', 64)), help='frames per step per GPU')
+    ap.add_argument('--cams', type=int, default=6)
+    ap.add_argument('--sweeps', type=int, default=10)
+    ap.add_argument('--distinct', type=int, default=int(os.environ.get('DFU_BENCH_DISTINCT', 8)),
+                    help='distinct synthetic frames generated per rank (tiled to --frames)')
+    ap.add_argument('--max-inst', type=int, default=8)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--cpu-sample-views', type=int, default=1)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    return ap.parse_args()
+
+
+def workload_config(a):
+    return {'workload': 'configs[3]: full pipeline (S1 projection+label inheritance, S2 densification+angular dedup, '
+                        'radius filters, BallQuery gate, clustering, box fitting, fp16 cloud emit)',
+            'frames_per_step_per_gpu': a.frames, 'cams_per_frame': a.cams, 'sweeps': a.sweeps,
+            'lidar_pts_per_frame': 34720 * a.sweeps, 'image': '1600x900', 'max_instances_per_view': a.max_inst,
+            'distinct_frames': min(a.distinct, a.frames), 'l2': 'inputs per step >> 126 MB L2 (no flush needed)',
+            'parallelism': 'frame-wise sharding, 1 process per GPU, no collective'}
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler(object):
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            f = [x.strip() for x in r.split(',')]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU side (oracle port)
+def _cpu_view_worker(job):
+    seed, cams, sweeps, cam, max_inst = job
+    import torch
+    torch.set_num_threads(1)
+    from dfu3d_b200 import synth
+    from oracle import restate
+    fr = synth.make_frame(seed, 'nuscenes', n_cams=cams, sweeps=sweeps, max_inst=max_inst, only_cam=cam)
+    inp = synth.view_as_reference_inputs(fr, 0)
+    t0 = time.perf_counter()
+    out = restate.run_view(inp)
+    return time.perf_counter() - t0, len(out[2])
+
+
+def cpu_baseline(a, n_views, procs):
+    """Times the oracle port on whole views; returns (frames/s, seconds of CPU wall, sample text)."""
+    jobs = [(910000 + i // a.cams, a.cams, a.sweeps, i % a.cams, a.max_inst) for i in range(n_views)]
+    t0 = time.perf_counter()
+    if procs <= 1:
+        res = [_cpu_view_worker(j) for j in jobs]
+        wall = sum(r[0] for r in res)
+    else:
+        import multiprocessing as mp
+        with mp.get_context('spawn').Pool(procs) as pool:
+            t0 = time.perf_counter()
+            res = pool.map(_cpu_view_worker, jobs, chunksize=1)
+            wall = time.perf_counter() - t0
+    fps = (n_views / float(a.cams)) / wall
+    return fps, wall, '%d view(s) of %d-cam %d-sweep nuScenes-shaped frames, compute only (inputs generated outside the timed part)' % (
+        n_views, a.cams, a.sweeps)
+
+
+def run_reference(a):
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    procs = max(1, min(cores, 32))
+    per_step = max(procs, a.cpu_sample_views)
+    # warmup: imports + one view
+    for _ in range(min(a.warmup, 1)):
+        cpu_baseline(a, 1, 1)
+    times, views = [], 0
+    for s in range(a.steps):
+        fps, wall, sample = cpu_baseline(a, per_step, procs)
+        times.append(wall)
+        views += per_step
+    tot = sum(times)
+    value = (views / float(a.cams)) / tot
+    line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup,
+            'ms_per_step': 1000.0 * tot / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'f64', 'data': 'synthetic', 'impl': 'reference', 'config': workload_config(a),
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': procs, 'kind': 'port',
+                             'sample': '%d views per step (%s), one whole view per worker process' % (per_step, sample)},
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------- algorithmic bytes
+def algorithmic_bytes(tag, st):
+    """Compulsory bytes of one launch of kernel `tag` on the benchmark batch (DESIGN.md 'Kernels')."""
+    if tag == 'pack_masks':
+        return st['mask_bytes'] + 4 * st['pixels_m']
+    if tag == 'project':
+        return 45 * st['lidar_slots']
+    if tag == 'densify_a':                       # S2: 4 B depth per pixel + key write 4 B; per valid point table atomics not counted
+        return 8 * st['pixels'] + 0 * st['gated']
+    if tag == 'densify_b':
+        return 8 * st['pixels']
+    if tag == 'densify_c':
+        return 4 * st['pixels'] + 8 * st['voxels']
+    if tag == 'emit_cloud':
+        return st['cloud_rows'] * (16 + 16)
+    if tag == 'vox_gather':
+        return st['voxels'] * (8 + 4 + 24 + 4 + 4)
+    if tag == 'radius':
+        return 13 * st.get('inst_points', 0)
+    if tag == 'grid_build':
+        return 28 * st.get('inst_points', 0)
+    if tag == 'cluster':
+        return 20 * st.get('fused_points', 0)
+    if tag == 'fit':
+        return 20 * st.get('fused_points', 0) + 120 * st.get('boxes', 0)
+    if tag == 'gate':
+        return 13 * st.get('inst_points', 0)
+    return None
+
+
+def main():
+    a = parse()
+    if a.impl == 'reference':
+        return run_reference(a)
+    import torch
+    import torch.distributed as dist
+    from dfu3d_b200 import synth, pipeline
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+    pipe = pipeline.FusionPipeline(local)
+
+    # ---- synthetic batch, generated on the device (identical generator for the CPU arm)
+    nd = max(1, min(a.distinct, a.frames))
+    frames = [synth.make_frame(1000 * 3 + rank * 100 + i, 'nuscenes', n_cams=a.cams, sweeps=a.sweeps, device=dev,
+                               max_inst=a.max_inst) for i in range(nd)]
+    frames = [frames[i % nd] for i in range(a.frames)]
+    vb = pipeline.batch_from_frames(frames, dev)
+    del frames
+    host = pipeline.HostBatch.from_device(vb)          # pinned host copies of every input tensor
+
+    def step_resident():
+        vb.labelmap = None
+        return pipe.run(vb, cloud_dtype=torch.float16, instances=True, want_lines=False)
+
+    def step_e2e():
+        return pipe.run_host(host, cloud_dtype=torch.float16, want_lines=False)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, profile=False):
+        barrier()
+        l0 = pipe.ctx.launches
+        if profile:
+            pipe.ctx.profile(True)
+            pipe.ctx.profile_read(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for _ in range(steps):
+            last = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        prof = pipe.ctx.profile_read(reset=True) if profile else None
+        if profile:
+            pipe.ctx.profile(False)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), pipe.ctx.launches - l0, prof, last
+
+    for _ in range(max(a.warmup, 0)):
+        step_resident()
+    clk = ClockSampler(local)
+    if rank == 0:
+        clk.start()
+    ms, launches, _, res = timed(step_resident, a.steps)
+    clocks = clk.stop() if rank == 0 else None
+    # same steps again with per-kernel events (the events perturb the step a little, so they are kept out of `value`)
+    ms_prof, _, prof, res = timed(step_resident, a.steps, profile=True)
+    value = world * a.frames * a.steps / (ms / 1000.0)
+
+    e2e = None
+    if not a.no_e2e:
+        for _ in range(max(min(a.warmup, 2), 1)):
+            step_e2e()
+        ms_e, _, _, res_e = timed(step_e2e, a.steps)
+        e2e = {'value': world * a.frames * a.steps / (ms_e / 1000.0), 'unit': UNIT,
+               'h2d_bytes_per_step': int(host.h2d_bytes), 'd2h_bytes_per_step': int(res_e.d2h_bytes),
+               'ms_per_step': ms_e / a.steps}
+
+    if rank == 0:
+        st = pipe.batch_stats(vb, res)
+        roof = None
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        except Exception:
+            pass
+        peak = float(peaks.get('hbm_gbs', 6650.0))
+        peak_src = 'measured (MEASURED_PEAKS.json hbm_gbs)' if 'hbm_gbs' in peaks else 'fallback 6650 GB/s'
+        kernels = {}
+        for tag, (tms, calls) in (prof or {}).items():
+            ab = algorithmic_bytes(tag, st)
+            kernels[tag] = {'ms_per_step': tms / a.steps, 'launches_per_step': calls / a.steps,
+                            'algorithmic_bytes_per_step': ab,
+                            'achieved_gbs': (ab / 1e9) / (tms / a.steps / 1000.0) if ab and tms > 0 else None}
+        cand = [(v['ms_per_step'], k) for k, v in kernels.items() if v['achieved_gbs'] is not None]
+        if cand:
+            _, top = max(cand)
+            k = kernels[top]
+            roof = {'bound': 'hbm', 'kernel': top, 'achieved': k['achieved_gbs'], 'peak': peak, 'unit': 'GB/s',
+                    'frac': k['achieved_gbs'] / peak, 'traffic': None, 'peak_source': peak_src,
+                    'share_of_step': k['ms_per_step'] / (ms_prof / a.steps)}
+        cpu = None
+        if world == 1 and not a.no_cpu_baseline:
+            fps, wall, sample = cpu_baseline(a, a.cpu_sample_views, 1)
+            cpu = {'value': fps, 'unit': UNIT, 'cores': 1, 'kind': 'port', 'sample': sample, 'seconds': wall}
+        line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': a.steps, 'warmup': a.warmup,
+                'ms_per_step': ms / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+                'dtype': 'f64', 'data': 'synthetic', 'config': workload_config(a), 'e2e': e2e,
+                'gpu_launches': int(launches), 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
+                'kernels': kernels, 'batch': st}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -37,6 +37,11 @@ INST_DTYPE = np.dtype([
 ], align=True)
 assert INST_DTYPE.itemsize == 72, INST_DTYPE.itemsize
 
+PROF_NTAGS = 24
+PROF_TAGS = ['pack_masks', 'project', 'lists', 'densify_a', 'densify_b', 'densify_c', 'vox_gather', 'emit_cloud',
+             'inst_pairs', 'inst_sort', 'grid_build', 'radius', 'gate', 'cluster', 'fit', 'sor_knn', 'sor_mask',
+             'sparse_depth', 'misc']
+
 _lib = None
 
 _P = C.c_void_p
@@ -45,6 +50,8 @@ _SIGS = {
     'dfu_destroy': (None, [_P]),
     'dfu_last_error': (C.c_char_p, [_P]),
     'dfu_launch_count': (C.c_int64, [_P]),
+    'dfu_profile_enable': (C.c_int, [_P, C.c_int]),
+    'dfu_profile_read': (C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
     'dfu_project_label': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
     'dfu_pack_masks': (C.c_int, [_P, _P, C.c_int, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
     'dfu_sparse_depth': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P]),
@@ -123,6 +130,16 @@ class Context(object):
     @property
     def launches(self):
         return int(self.lib.dfu_launch_count(self.h))
+
+    def profile(self, on=True):
+        self.check(self.lib.dfu_profile_enable(self.h, int(on)))
+
+    def profile_read(self, reset=True):
+        """{tag: (total ms, launches)} of the instrumented kernels since the last reset."""
+        ms = np.zeros(PROF_NTAGS, np.float64)
+        calls = np.zeros(PROF_NTAGS, np.int64)
+        self.check(self.lib.dfu_profile_read(self.h, hptr(ms), hptr(calls), PROF_NTAGS, int(reset)))
+        return {PROF_TAGS[i]: (float(ms[i]), int(calls[i])) for i in range(len(PROF_TAGS)) if calls[i] > 0}
 
     def close(self):
         if getattr(self, 'h', None):

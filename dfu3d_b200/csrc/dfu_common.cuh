@@ -6,7 +6,11 @@
 #include <string.h>
 #include "../../include/dfu3d.h"
 
-#define DFU_NSLOTS 48
+#define DFU_NSLOTS 96
+#define DFU_PROF_POOL 8192
+#ifndef DFU_PROF_NTAGS
+#define DFU_PROF_NTAGS 24
+#endif
 
 struct dfu_ctx {
   int device;
@@ -37,7 +41,34 @@ struct dfu_ctx {
   int64_t* off_vox;           // host [V+1]
   int stage;                  // 0 none, 1 begun, 2 projected, 3 densified
   int total_inst;
+  // ---- per-kernel device timing (dfu_profile_*) ----
+  int prof_on;
+  int prof_used;
+  cudaEvent_t* prof_ev;       // [2 * DFU_PROF_POOL]
+  int* prof_tag;              // [DFU_PROF_POOL]
+  double prof_ms[DFU_PROF_NTAGS];
+  int64_t prof_calls[DFU_PROF_NTAGS];
 };
+
+// kernel tags of dfu_profile_read (order is part of the ABI, see include/dfu3d.h)
+enum {
+  PT_PACK_MASKS = 0, PT_PROJECT, PT_LISTS, PT_DENSIFY_A, PT_DENSIFY_B, PT_DENSIFY_C, PT_VOX_GATHER, PT_EMIT_CLOUD,
+  PT_INST_PAIRS, PT_INST_SORT, PT_GRID_BUILD, PT_RADIUS, PT_GATE, PT_CLUSTER, PT_FIT, PT_SOR_KNN, PT_SOR_MASK,
+  PT_SPARSE_DEPTH, PT_MISC
+};
+
+struct dfu_prof_scope {
+  dfu_ctx* c; cudaStream_t st; int slot;
+  dfu_prof_scope(dfu_ctx* ctx, cudaStream_t s, int tag) : c(ctx), st(s), slot(-1) {
+    if (ctx->prof_on && ctx->prof_used < DFU_PROF_POOL) {
+      slot = ctx->prof_used++;
+      ctx->prof_tag[slot] = tag;
+      cudaEventRecord(ctx->prof_ev[2 * slot], s);
+    }
+  }
+  ~dfu_prof_scope() { if (slot >= 0) cudaEventRecord(c->prof_ev[2 * slot + 1], st); }
+};
+#define DFU_PROF(ctx, stream, tag) dfu_prof_scope prof_scope__##tag(ctx, stream, tag)
 
 // scratch slot ids
 enum {

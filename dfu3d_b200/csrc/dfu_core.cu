@@ -92,6 +92,11 @@ extern "C" void dfu_destroy(dfu_ctx* ctx) {
   for (int i = 0; i < DFU_NSLOTS; i++)
     if (ctx->slot[i]) cudaFree(ctx->slot[i]);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->prof_ev) {
+    for (int i = 0; i < 2 * DFU_PROF_POOL; i++) cudaEventDestroy(ctx->prof_ev[i]);
+    free(ctx->prof_ev);
+    free(ctx->prof_tag);
+  }
   free(ctx->views_host);
   free(ctx->cnt_project);
   free(ctx->off_project);
@@ -102,3 +107,39 @@ extern "C" void dfu_destroy(dfu_ctx* ctx) {
 
 extern "C" const char* dfu_last_error(const dfu_ctx* ctx) { return ctx ? ctx->err : "null context"; }
 extern "C" int64_t dfu_launch_count(const dfu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ---------------------------------------------------------------- per-kernel device timing
+extern "C" int dfu_profile_enable(dfu_ctx* ctx, int on) {
+  if (!ctx) return DFU_ERR_ARG;
+  if (on && !ctx->prof_ev) {
+    ctx->prof_ev = (cudaEvent_t*)calloc(2 * DFU_PROF_POOL, sizeof(cudaEvent_t));
+    ctx->prof_tag = (int*)calloc(DFU_PROF_POOL, sizeof(int));
+    for (int i = 0; i < 2 * DFU_PROF_POOL; i++) DFU_CUDA(ctx, cudaEventCreate(&ctx->prof_ev[i]));
+  }
+  ctx->prof_on = on;
+  return DFU_OK;
+}
+
+extern "C" int dfu_profile_read(dfu_ctx* ctx, double* ms_out, int64_t* calls_out, int n, int reset) {
+  if (!ctx) return DFU_ERR_ARG;
+  if (ctx->prof_used > 0) {
+    DFU_CUDA(ctx, cudaDeviceSynchronize());
+    for (int i = 0; i < ctx->prof_used; i++) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ctx->prof_ev[2 * i], ctx->prof_ev[2 * i + 1]) == cudaSuccess) {
+        ctx->prof_ms[ctx->prof_tag[i]] += ms;
+        ctx->prof_calls[ctx->prof_tag[i]] += 1;
+      }
+    }
+    ctx->prof_used = 0;
+  }
+  for (int i = 0; i < n && i < DFU_PROF_NTAGS; i++) {
+    if (ms_out) ms_out[i] = ctx->prof_ms[i];
+    if (calls_out) calls_out[i] = ctx->prof_calls[i];
+  }
+  if (reset) {
+    memset(ctx->prof_ms, 0, sizeof(ctx->prof_ms));
+    memset(ctx->prof_calls, 0, sizeof(ctx->prof_calls));
+  }
+  return DFU_OK;
+}

@@ -288,17 +288,26 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, (int64_t)V * bpv * sizeof(int32_t));
   DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
   DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
-  DFU_CUDA(ctx, cudaMemsetAsync(table, 0xFF, (size_t)V * NCELL * sizeof(VoxCell), st));
-  DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
   dim3 grid(bpv, V);
-  k_densify_a<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, stats);
-  DFU_LAUNCH_CHECK(ctx);
-  k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, stats);
-  DFU_LAUNCH_CHECK(ctx);
-  int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, (int64_t)V * bpv);
-  if (rc) return rc;
-  k_vox_view_offsets<<<(V + 1 + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voxoff);
-  DFU_LAUNCH_CHECK(ctx);
+  {
+    DFU_PROF(ctx, st, PT_DENSIFY_A);
+    DFU_CUDA(ctx, cudaMemsetAsync(table, 0xFF, (size_t)V * NCELL * sizeof(VoxCell), st));
+    DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
+    k_densify_a<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, stats);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  {
+    DFU_PROF(ctx, st, PT_DENSIFY_B);
+    k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, stats);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  {
+    DFU_PROF(ctx, st, PT_MISC);
+    int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, (int64_t)V * bpv);
+    if (rc) return rc;
+    k_vox_view_offsets<<<(V + 1 + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voxoff);
+    DFU_LAUNCH_CHECK(ctx);
+  }
   // read back offsets + stats (one sync)
   size_t nb = (V + 1) * sizeof(int64_t) + V * 8 * sizeof(unsigned long long);
   char* pin = (char*)dfu_pinned(ctx, nb);
@@ -327,9 +336,13 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, repy, int32_t*, SL_REPY, cap * sizeof(int32_t));
   DFU_SLOT(ctx, repy_xyz, double*, SL_REPY_XYZ, cap * 3 * sizeof(double));
   DFU_SLOT(ctx, repy_label, uint32_t*, SL_REPY_LABEL, cap * sizeof(uint32_t));
-  k_densify_c<<<grid, S2_THREADS, 0, st>>>(q, key, table, blkoff, repz, repy);
-  DFU_LAUNCH_CHECK(ctx);
+  {
+    DFU_PROF(ctx, st, PT_DENSIFY_C);
+    k_densify_c<<<grid, S2_THREADS, 0, st>>>(q, key, table, blkoff, repz, repy);
+    DFU_LAUNCH_CHECK(ctx);
+  }
   if (nvox > 0) {
+    DFU_PROF(ctx, st, PT_VOX_GATHER);
     k_vox_gather<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, voxoff, ctx->depth, ctx->labelmap, repz, repy,
                                                                  repy_xyz, repy_label, nullptr, nvox);
     DFU_LAUNCH_CHECK(ctx);
@@ -368,6 +381,8 @@ extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t c
   S2Prm q = make_s2(&ctx->prm);
   dfu_view* vd = (dfu_view*)ctx->slot[SL_VIEWS];
   unsigned nblk = (unsigned)((tot + 255) / 256);
+  {
+  DFU_PROF(ctx, st, PT_EMIT_CLOUD);
 #define EMIT(T)                                                                                                   \
   k_emit_cloud<T><<<nblk, 256, 0, st>>>(vd, q, V, rowoff, foff, voxoff, (const float4*)ctx->lidar,                 \
                                         (const int32_t*)ctx->slot[SL_FLIST], ctx->depth, ctx->image,               \
@@ -378,6 +393,7 @@ extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t c
   else return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_cloud: dtype must be 0, 1 or 2");
 #undef EMIT
   DFU_LAUNCH_CHECK(ctx);
+  }
   // rowoff_h (pinned) is re-used by later calls: make sure the H2D copy is done
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
   return DFU_OK;

@@ -213,6 +213,7 @@ extern "C" int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_vi
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_project_label: bad argument");
   if (max_lidar_cnt == 0) return DFU_OK;
   dim3 grid((max_lidar_cnt + S1_THREADS - 1) / S1_THREADS, V);
+  DFU_PROF(ctx, (cudaStream_t)stream, PT_PROJECT);
   k_project<<<grid, S1_THREADS, 0, (cudaStream_t)stream>>>(views_dev, make_s1(prm), (const float4*)lidar_xyzi, labelmap,
                                                             (float2*)out_uv, out_depth, (int2*)out_pix, out_flags,
                                                             out_label, nullptr);
@@ -226,6 +227,7 @@ extern "C" int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view*
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_pack_masks: bad argument");
   const int HW = Hm * Wm;
   dim3 grid((HW + 255) / 256, V);
+  DFU_PROF(ctx, (cudaStream_t)stream, PT_PACK_MASKS);
   if (is_f32)
     k_pack_masks<float><<<grid, 256, 0, (cudaStream_t)stream>>>(views_dev, (const float*)masks, HW, labelmap);
   else
@@ -243,6 +245,7 @@ extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_vie
   q.round_mode = 1;
   const int64_t npix = (int64_t)V * q.H * q.W;
   DFU_SLOT(ctx, winner, int*, SL_OP0, npix * sizeof(int));
+  DFU_PROF(ctx, st, PT_SPARSE_DEPTH);
   DFU_CUDA(ctx, cudaMemsetAsync(winner, 0xFF, npix * sizeof(int), st));
   if (max_lidar_cnt > 0) {
     dim3 g1((max_lidar_cnt + S1_THREADS - 1) / S1_THREADS, V);
@@ -318,15 +321,21 @@ extern "C" int dfu_fuse_project_sync(dfu_ctx* ctx, int64_t* counts_host) {
   DFU_SLOT(ctx, blabel, uint32_t*, SL_BLABEL, ns * sizeof(uint32_t));
   DFU_SLOT(ctx, voff, int64_t*, SL_STATS, 3 * (V + 1) * sizeof(int64_t) + 64);
   dim3 grid(bpv, V);
-  k_project<<<grid, S1_THREADS, 0, st>>>(vd, make_s1(&ctx->prm), (const float4*)ctx->lidar, ctx->labelmap, nullptr,
-                                         nullptr, pix, flags, label, blkcnt);
-  DFU_LAUNCH_CHECK(ctx);
-  int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, 3 * VB);
-  if (rc) return rc;
-  k_lists_scatter<<<grid, S1_THREADS, 0, st>>>(vd, flags, label, blkoff, flist, alist, blabel);
-  DFU_LAUNCH_CHECK(ctx);
-  k_lists_view_offsets<<<(3 * (V + 1) + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voff);
-  DFU_LAUNCH_CHECK(ctx);
+  {
+    DFU_PROF(ctx, st, PT_PROJECT);
+    k_project<<<grid, S1_THREADS, 0, st>>>(vd, make_s1(&ctx->prm), (const float4*)ctx->lidar, ctx->labelmap, nullptr,
+                                           nullptr, pix, flags, label, blkcnt);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  {
+    DFU_PROF(ctx, st, PT_LISTS);
+    int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, 3 * VB);
+    if (rc) return rc;
+    k_lists_scatter<<<grid, S1_THREADS, 0, st>>>(vd, flags, label, blkoff, flist, alist, blabel);
+    DFU_LAUNCH_CHECK(ctx);
+    k_lists_view_offsets<<<(3 * (V + 1) + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voff);
+    DFU_LAUNCH_CHECK(ctx);
+  }
   int64_t* pin = (int64_t*)dfu_pinned(ctx, 3 * (V + 1) * sizeof(int64_t));
   if (!pin) return DFU_ERR_CUDA;
   DFU_CUDA(ctx, cudaMemcpyAsync(pin, voff, 3 * (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));

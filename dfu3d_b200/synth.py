@@ -206,14 +206,17 @@ def make_view(shape, boxes, seed, cam=0, crop=None, scale=1.0, device='cpu', max
     }
 
 
-def make_frame(seed, shape='nuscenes', n_cams=1, sweeps=1, scale=1.0, crop=None, device='cpu', n_obj=None):
-    """``dict(lidar [N,4] f32, views [n_cams], boxes_gt)``; seeded by ``seed`` alone."""
+def make_frame(seed, shape='nuscenes', n_cams=1, sweeps=1, scale=1.0, crop=None, device='cpu', n_obj=None, max_inst=32,
+               only_cam=None):
+    """``dict(lidar [N,4] f32, views [n_cams], boxes_gt)``; seeded by ``seed`` alone.  ``only_cam`` keeps a
+    single camera of the ``n_cams``-camera frame (same scene, same sweep)."""
     rng = np.random.default_rng(int(seed))
     cfg = SHAPES[shape]
     yaws = [math.radians(_NUSC_CAM_YAWS_DEG[c % 6]) for c in range(n_cams)] if shape == 'nuscenes' else [0.0]
     boxes = make_scene(rng, n_obj=n_obj, h=cfg['h'], yaw_centers=yaws)
     lidar = make_lidar(shape, boxes, seed, sweeps=sweeps, device=device)
-    views = [make_view(shape, boxes, seed, cam=c, crop=crop, scale=scale, device=device) for c in range(n_cams)]
+    cams = range(n_cams) if only_cam is None else [only_cam]
+    views = [make_view(shape, boxes, seed, cam=c, crop=crop, scale=scale, device=device, max_inst=max_inst) for c in cams]
     return {'lidar': lidar, 'views': views, 'boxes_gt': boxes, 'shape': shape}
 
 

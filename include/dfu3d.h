@@ -87,6 +87,16 @@ const char* dfu_last_error(const dfu_ctx* ctx);
 /* number of kernels this context has launched since creation (bench.py: gpu_launches) */
 int64_t dfu_launch_count(const dfu_ctx* ctx);
 
+/* Per-kernel device timing with CUDA events on the launching stream (bench.py: roofline.achieved).
+ * While enabled every instrumented launch is bracketed by two events (pool of 8192 launches between
+ * reads).  dfu_profile_read synchronises the device, accumulates, and returns the totals per tag:
+ *  0 pack_masks  1 project  2 lists  3 densify_a  4 densify_b  5 densify_c  6 vox_gather  7 emit_cloud
+ *  8 inst_pairs  9 inst_sort  10 grid_build  11 radius  12 gate  13 cluster  14 fit  15 sor_knn
+ *  16 sor_mask  17 sparse_depth  18 misc */
+#define DFU_PROF_NTAGS 24
+int dfu_profile_enable(dfu_ctx* ctx, int on);
+int dfu_profile_read(dfu_ctx* ctx, double* ms_out, int64_t* calls_out, int n, int reset);
+
 /* ---- S1: LiDAR -> image projection with label inheritance --------------------------------------
  * Replaces Calibration.lidar_to_rect / rect_to_img / lidar_to_img (calibration_kitti.py:104-132),
  * get_fov_flag (vis_utils.py:108-123), above_plane (my_loader.py:471-484) and the per-instance
