@@ -1,0 +1,289 @@
+// Uniform hash grid (radix-sorted cell keys) + the two neighbourhood operators built on it:
+//   * radius filter  — Open3D PointCloud::RemoveRadiusOutliers semantics as restated in oracle/fakes.py
+//                      (call sites tools/PENet/dataloaders/my_loader.py:569-599)
+//   * NN gate        — BallQuery (tools/PENet/dataloaders/my_loader.py:489-494, 602-604)
+// Cell edge = radius * (1 + 2^-30): every neighbour closer than the radius lies in the 3x3x3 block around the query's
+// cell.  Keys put z in the lowest bits, so the three z-cells of one (x, y) column are ONE contiguous range of the
+// sorted array: 9 range look-ups per query instead of 27.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include "dfu_ops.cuh"
+
+#define G_THREADS 256
+
+__global__ void __launch_bounds__(G_THREADS) k_grid_bbox(const double* __restrict__ x, const double* __restrict__ y,
+                                                         const double* __restrict__ z, const int32_t* __restrict__ seg,
+                                                         const uint8_t* __restrict__ active, int64_t n,
+                                                         unsigned long long* __restrict__ segmin) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  bool ok = i < n && (active == nullptr || active[i]);
+  int s = ok ? seg[i] : -1;
+  unsigned long long bx = ~0ull, by = ~0ull, bz = ~0ull;
+  if (ok) {
+    bx = dfu_order_f64(x[i]);
+    by = dfu_order_f64(y[i]);
+    bz = z ? dfu_order_f64(z[i]) : dfu_order_f64(0.0);
+  }
+  // warp-aggregate when the whole warp sits in one segment (the common case)
+  const int s0 = __shfl_sync(0xffffffffu, s, 0);
+  const bool uniform = __all_sync(0xffffffffu, s == s0 || s == -1);
+  if (uniform) {
+    int sv = s;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      unsigned long long ox = __shfl_xor_sync(0xffffffffu, bx, o), oy = __shfl_xor_sync(0xffffffffu, by, o),
+                         oz = __shfl_xor_sync(0xffffffffu, bz, o);
+      int os = __shfl_xor_sync(0xffffffffu, sv, o);
+      bx = ox < bx ? ox : bx; by = oy < by ? oy : by; bz = oz < bz ? oz : bz;
+      sv = os > sv ? os : sv;
+    }
+    if ((threadIdx.x & 31) == 0 && sv >= 0) {
+      atomicMin(segmin + 3 * sv + 0, bx);
+      atomicMin(segmin + 3 * sv + 1, by);
+      atomicMin(segmin + 3 * sv + 2, bz);
+    }
+  } else if (ok) {
+    atomicMin(segmin + 3 * s + 0, bx);
+    atomicMin(segmin + 3 * s + 1, by);
+    atomicMin(segmin + 3 * s + 2, bz);
+  }
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_grid_keys(const double* __restrict__ x, const double* __restrict__ y,
+                                                         const double* __restrict__ z, const int32_t* __restrict__ seg,
+                                                         const uint8_t* __restrict__ active, int64_t n,
+                                                         const unsigned long long* __restrict__ segmin,
+                                                         const double* __restrict__ cell, unsigned long long* __restrict__ key,
+                                                         int32_t* __restrict__ idx, int32_t* __restrict__ errflag) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (i >= n) return;
+  idx[i] = (int32_t)i;
+  unsigned long long k = ~0ull;
+  if (active == nullptr || active[i]) {
+    const int s = seg[i];
+    const double c = cell[s];
+    int cx = dfu_cell_coord(x[i], dfu_unorder_f64(segmin[3 * s + 0]), c);
+    int cy = dfu_cell_coord(y[i], dfu_unorder_f64(segmin[3 * s + 1]), c);
+    int cz = z ? dfu_cell_coord(z[i], dfu_unorder_f64(segmin[3 * s + 2]), c) : 1;
+    if (cx < 1 || cy < 1 || cz < 1) atomicOr(errflag, 1);   // NaN / overflow of the 16-bit cell range
+    else k = dfu_grid_key(s, cx, cy, cz);
+  }
+  key[i] = k;
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_grid_heads(const unsigned long long* __restrict__ skey,
+                                                          const int32_t* __restrict__ sidx, const double* __restrict__ x,
+                                                          const double* __restrict__ y, const double* __restrict__ z,
+                                                          int64_t n, double* __restrict__ sx, double* __restrict__ sy,
+                                                          double* __restrict__ sz, int32_t* __restrict__ head) {
+  const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (t >= n) return;
+  const int i = sidx[t];
+  sx[t] = x[i];
+  sy[t] = y[i];
+  sz[t] = z ? z[i] : 0.0;
+  head[t] = (t == 0 || skey[t] != skey[t - 1]) ? 1 : 0;
+}
+
+// pcell (inclusive scan of head) -> cell ordinal; scatter the cell table
+__global__ void __launch_bounds__(G_THREADS) k_grid_cells(const unsigned long long* __restrict__ skey, int64_t n,
+                                                          int32_t* __restrict__ pcell, unsigned long long* __restrict__ ukey,
+                                                          int32_t* __restrict__ ustart, int32_t* __restrict__ ncell) {
+  const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (t >= n) return;
+  const int c = pcell[t] - 1;
+  pcell[t] = c;
+  if (t == 0 || skey[t] != skey[t - 1]) {
+    ukey[c] = skey[t];
+    ustart[c] = (int32_t)t;
+  }
+  if (t == n - 1) {
+    ustart[c + 1] = (int32_t)n;
+    *ncell = c + 1;
+  }
+}
+
+int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const double* y, const double* z,
+                   const int32_t* seg, const uint8_t* active, int64_t n, int nseg, const double* cell_dev, DfuGrid* g) {
+  if (nseg > 65534) return dfu_set_err(ctx, DFU_ERR_DATA, "grid: %d segments (max 65534)", nseg);
+  if (n >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_DATA, "grid: too many points");
+  const int64_t m = n > 0 ? n : 1;
+  DFU_SLOT(ctx, segmin, unsigned long long*, sb + 0, (size_t)(nseg > 0 ? nseg : 1) * 3 * 8);
+  DFU_SLOT(ctx, key, unsigned long long*, sb + 1, m * 8);
+  DFU_SLOT(ctx, idx, int32_t*, sb + 2, m * 4);
+  DFU_SLOT(ctx, skey, unsigned long long*, sb + 3, m * 8);
+  DFU_SLOT(ctx, sidx, int32_t*, sb + 4, m * 4);
+  DFU_SLOT(ctx, sx, double*, sb + 5, m * 8);
+  DFU_SLOT(ctx, sy, double*, sb + 6, m * 8);
+  DFU_SLOT(ctx, sz, double*, sb + 7, m * 8);
+  DFU_SLOT(ctx, pcell, int32_t*, sb + 8, m * 4);
+  DFU_SLOT(ctx, ukey, unsigned long long*, sb + 9, m * 8);
+  DFU_SLOT(ctx, ustart, int32_t*, sb + 10, (m + 1) * 4);
+  DFU_SLOT(ctx, scal, int32_t*, sb + 11, 64);
+  g->n = n; g->nseg = nseg; g->cell = cell_dev; g->segmin = segmin; g->skey = skey; g->sidx = sidx;
+  g->sx = sx; g->sy = sy; g->sz = sz; g->pcell = pcell; g->ukey = ukey; g->ustart = ustart;
+  g->ncell = scal; g->errflag = scal + 1;
+  DFU_CUDA(ctx, cudaMemsetAsync(scal, 0, 4, st));   // ncell only; errflag (scal[1]) is reset by dfu_grid_err_reset
+  DFU_CUDA(ctx, cudaMemsetAsync(ustart, 0, 8, st));
+  if (n == 0) return DFU_OK;
+  DFU_CUDA(ctx, cudaMemsetAsync(segmin, 0xFF, (size_t)nseg * 3 * 8, st));
+  const unsigned nb = (unsigned)((n + G_THREADS - 1) / G_THREADS);
+  k_grid_bbox<<<nb, G_THREADS, 0, st>>>(x, y, z, seg, active, n, segmin);
+  DFU_LAUNCH_CHECK(ctx);
+  k_grid_keys<<<nb, G_THREADS, 0, st>>>(x, y, z, seg, active, n, segmin, cell_dev, key, idx, g->errflag);
+  DFU_LAUNCH_CHECK(ctx);
+  size_t tb = 0, tb2 = 0;
+  DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, key, skey, idx, sidx, (int)n, 0, 64, st));
+  DFU_CUDA(ctx, cub::DeviceScan::InclusiveSum(nullptr, tb2, pcell, pcell, (int)n, st));
+  if (tb2 > tb) tb = tb2;
+  DFU_SLOT(ctx, tmp, void*, sb + 12, tb);
+  DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, key, skey, idx, sidx, (int)n, 0, 64, st));
+  ctx->launches += 8;
+  k_grid_heads<<<nb, G_THREADS, 0, st>>>(skey, sidx, x, y, z, n, sx, sy, sz, pcell);
+  DFU_LAUNCH_CHECK(ctx);
+  DFU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tb, pcell, pcell, (int)n, st));
+  ctx->launches += 2;
+  k_grid_cells<<<nb, G_THREADS, 0, st>>>(skey, n, pcell, ukey, ustart, g->ncell);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
+// ---------------------------------------------------------------- neighbourhood walks
+// MODE 0: count points with d2 < r2 until the count exceeds nb (self included)     -> keep = count > nb
+// MODE 1: any reference point with sqrt(d2) < maxdist                             -> keep
+// The squared distance is ((dx*dx + dy*dy) + dz*dz) with separately rounded products, as numpy evaluates
+// ((a - b) ** 2).sum(-1) (oracle/fakes.py: radius_outlier_mask; oracle/restate.py: ball_gate).
+template <int MODE>
+__device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, double px, double py, double pz, double lim,
+                                          int nb) {
+  const double c = g.cell[s];
+  const int cx = dfu_cell_coord(px, dfu_unorder_f64(g.segmin[3 * s + 0]), c);
+  const int cy = dfu_cell_coord(py, dfu_unorder_f64(g.segmin[3 * s + 1]), c);
+  const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
+  if (cx < 0 || cy < 0 || cz < 0) return false;   // far outside the reference bounding box (or an empty segment)
+  int count = 0;
+  for (int dx = -1; dx <= 1; dx++) {
+    const int ex = cx + dx;
+    if (ex < 1) continue;
+    for (int dy = -1; dy <= 1; dy++) {
+      const int ey = cy + dy;
+      if (ey < 1) continue;
+      const int zlo = cz - 1 < 1 ? 1 : cz - 1;
+      const int c0 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, zlo));
+      const int c1 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
+      if (c1 <= c0) continue;
+      const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
+      for (int j = lo; j < hi; j++) {
+        const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
+                     az = __dsub_rn(__ldg(g.sz + j), pz);
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az));
+        if (MODE == 0) {
+          if (d2 < lim) {
+            if (++count > nb) return true;
+          }
+        } else {
+          if (__dsqrt_rn(d2) < lim) return true;
+        }
+      }
+    }
+  }
+  return false;
+}
+
+// one thread per SORTED position: neighbouring threads walk the same cells (broadcast loads)
+__global__ void __launch_bounds__(G_THREADS) k_radius_count(DfuGrid g, const SegPrm* __restrict__ prm,
+                                                            uint8_t* __restrict__ keep) {
+  const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (t >= g.n) return;
+  const unsigned long long k = g.skey[t];
+  if (k == ~0ull) return;                       // inactive: keep stays 0
+  const int s = (int)(k >> 48);
+  const SegPrm p = prm[s];
+  const double r2 = __dmul_rn(p.r, p.r);
+  const bool kp = grid_walk<0>(g, *g.ncell, s, g.sx[t], g.sy[t], g.sz[t], r2, p.nb);
+  keep[g.sidx[t]] = kp ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_seg_active(const int32_t* __restrict__ seg, const int64_t* __restrict__ seg_off,
+                                                          int64_t n, const SegPrm* __restrict__ prm, uint8_t* __restrict__ active,
+                                                          double* __restrict__ cell, int nseg) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (i < nseg) cell[i] = prm[i].r * (1.0 + 9.313225746154785e-10);
+  if (i >= n) return;
+  const int s = seg[i];
+  const SegPrm p = prm[s];
+  const int64_t local = i - seg_off[s];
+  active[i] = (p.enabled && p.r > 0.0 && (p.every_k <= 1 || (local % p.every_k) == 0)) ? 1 : 0;
+}
+
+int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const double* y, const double* z,
+                    const int32_t* seg, const int64_t* seg_off_dev, int64_t n, int nseg, const SegPrm* prm_dev,
+                    uint8_t* keep) {
+  if (n == 0) return DFU_OK;
+  DFU_SLOT(ctx, active, uint8_t*, sb + GRID_SLOTS - 1, n);
+  DFU_SLOT(ctx, cellv, double*, sb + GRID_SLOTS, (size_t)nseg * 8);
+  const int64_t span = n > nseg ? n : nseg;
+  const unsigned nb = (unsigned)((span + G_THREADS - 1) / G_THREADS);
+  k_seg_active<<<nb, G_THREADS, 0, st>>>(seg, seg_off_dev, n, prm_dev, active, cellv, nseg);
+  DFU_LAUNCH_CHECK(ctx);
+  DFU_CUDA(ctx, cudaMemsetAsync(keep, 0, n, st));
+  DfuGrid g;
+  {
+    DFU_PROF(ctx, st, PT_GRID_BUILD);
+    int rc = dfu_grid_build(ctx, st, sb, x, y, z, seg, active, n, nseg, cellv, &g);
+    if (rc) return rc;
+  }
+  {
+    DFU_PROF(ctx, st, PT_RADIUS);
+    k_radius_count<<<(unsigned)((n + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(g, prm_dev, keep);
+    DFU_LAUNCH_CHECK(ctx);
+  }
+  return DFU_OK;
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_gate_cells(const double* __restrict__ maxdist, double* __restrict__ cell, int nseg) {
+  const int i = blockIdx.x * G_THREADS + threadIdx.x;
+  if (i < nseg) cell[i] = maxdist[i] * (1.0 + 9.313225746154785e-10);
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_gate(DfuGrid g, const double* __restrict__ qx, const double* __restrict__ qy,
+                                                    const double* __restrict__ qz, const int32_t* __restrict__ qseg, int64_t nq,
+                                                    const double* __restrict__ maxdist, uint8_t* __restrict__ keep) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (i >= nq) return;
+  const int s = qseg[i];
+  // an empty reference segment has segmin = +inf-ish bits -> dfu_cell_coord fails -> false
+  if (g.segmin[3 * s] == ~0ull) { keep[i] = 0; return; }
+  keep[i] = grid_walk<1>(g, *g.ncell, s, qx[i], qy[i], qz[i], maxdist[s], 0) ? 1 : 0;
+}
+
+int dfu_gate_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* qx, const double* qy, const double* qz,
+                  const int32_t* qseg, int64_t nq, const double* rx, const double* ry, const double* rz,
+                  const int32_t* rseg, const uint8_t* ractive, int64_t nr, int nseg, const double* maxdist_dev,
+                  uint8_t* keep) {
+  if (nq == 0) return DFU_OK;
+  if (nr == 0) {
+    DFU_CUDA(ctx, cudaMemsetAsync(keep, 0, nq, st));
+    return DFU_OK;
+  }
+  DFU_SLOT(ctx, cellv, double*, sb + GRID_SLOTS, (size_t)nseg * 8);
+  k_gate_cells<<<(nseg + G_THREADS - 1) / G_THREADS, G_THREADS, 0, st>>>(maxdist_dev, cellv, nseg);
+  DFU_LAUNCH_CHECK(ctx);
+  DfuGrid g;
+  {
+    DFU_PROF(ctx, st, PT_GRID_BUILD);
+    int rc = dfu_grid_build(ctx, st, sb, rx, ry, rz, rseg, ractive, nr, nseg, cellv, &g);
+    if (rc) return rc;
+  }
+  DFU_PROF(ctx, st, PT_GATE);
+  k_gate<<<(unsigned)((nq + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(g, qx, qy, qz, qseg, nq, maxdist_dev, keep);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
+int dfu_grid_err_reset(dfu_ctx* ctx, cudaStream_t st, int sb) {
+  DFU_SLOT(ctx, scal, int32_t*, sb + 11, 64);
+  DFU_CUDA(ctx, cudaMemsetAsync(scal, 0, 64, st));
+  return DFU_OK;
+}
+const int32_t* dfu_grid_err_ptr(dfu_ctx* ctx, int sb) { return (const int32_t*)ctx->slot[sb + 11] + 1; }

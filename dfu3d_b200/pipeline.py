@@ -291,3 +291,80 @@ def batch_from_frames(frames, device, thing_classes=None):
                      planes=planes, depth=torch.stack(depth, 0).contiguous(), image=torch.stack(image, 0).contiguous(),
                      masks=torch.cat(masks, 0).contiguous(), n_inst=n_inst, classes=classes, boxes2d=boxes2d,
                      thing_classes=list(tc))
+
+
+@dataclass
+class HostBatch:
+    """Pinned host copies of a ViewBatch's tensors (what a caller of the reference holds: numpy arrays on
+    the host).  FusionPipeline.run_host copies them to the device inside the call."""
+    lidar: torch.Tensor
+    depth: torch.Tensor
+    image: torch.Tensor
+    masks: torch.Tensor
+    meta: ViewBatch            # everything that is not a tensor (tensor fields are None)
+    h2d_bytes: int = 0
+
+    @staticmethod
+    def from_device(vb):
+        def pin(t):
+            h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            h.copy_(t)
+            return h
+        meta = ViewBatch(lidar=None, sweeps=vb.sweeps, view_sweep=vb.view_sweep, calibs=vb.calibs, planes=vb.planes,
+                         depth=None, image=None, masks=None, n_inst=vb.n_inst, classes=vb.classes, boxes2d=vb.boxes2d,
+                         thing_classes=vb.thing_classes)
+        hb = HostBatch(lidar=pin(vb.lidar), depth=pin(vb.depth), image=pin(vb.image), masks=pin(vb.masks), meta=meta)
+        hb.h2d_bytes = sum(t.numel() * t.element_size() for t in (hb.lidar, hb.depth, hb.image, hb.masks))
+        return hb
+
+
+def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True):
+    """The end-to-end call: host buffers in, cloud + boxes back on the host.  Device staging buffers are kept
+    between calls (re-allocated only when a shape grows)."""
+    dev = self.device
+    st = getattr(self, '_stage', None)
+    if st is None:
+        st = self._stage = {}
+    def up(name, h):
+        d = st.get(name)
+        if d is None or d.shape != h.shape or d.dtype != h.dtype:
+            d = st[name] = torch.empty(h.shape, dtype=h.dtype, device=dev)
+        d.copy_(h, non_blocking=True)
+        return d
+    m = hb.meta
+    vb = ViewBatch(lidar=up('lidar', hb.lidar), sweeps=m.sweeps, view_sweep=m.view_sweep, calibs=m.calibs, planes=m.planes,
+                   depth=up('depth', hb.depth), image=up('image', hb.image), masks=up('masks', hb.masks), n_inst=m.n_inst,
+                   classes=m.classes, boxes2d=m.boxes2d, thing_classes=m.thing_classes)
+    res = self.run(vb, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
+    hc = st.get('cloud_host')
+    if hc is None or hc.shape[0] < res.cloud.shape[0] or hc.dtype != res.cloud.dtype:
+        hc = st['cloud_host'] = torch.empty((int(res.cloud.shape[0] * 1.25) + 1024, 8), dtype=res.cloud.dtype, pin_memory=True)
+    out = hc[:res.cloud.shape[0]]
+    out.copy_(res.cloud, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    res.cloud_host = out
+    res.d2h_bytes = out.numel() * out.element_size() + (res.boxes.nbytes if res.boxes is not None else 0)
+    return res
+
+
+def _batch_stats(self, vb, res):
+    """Counts the algorithmic-byte formulas of bench.py need (per step)."""
+    V = len(vb.view_sweep)
+    H, W = vb.depth.shape[1:3]
+    Hm, Wm = vb.image.shape[1:3]
+    st = {'views': V, 'pixels': int(V * H * W), 'pixels_m': int(V * Hm * Wm),
+          'mask_bytes': int(vb.masks.numel() * vb.masks.element_size()),
+          'lidar_slots': int(sum(vb.sweeps[s][1] for s in vb.view_sweep)),
+          'valid_pixels': int(res.counts_densify[:, 0].sum()), 'gated': int(res.counts_densify[:, 1].sum()),
+          'voxels': int(res.counts_densify[:, 2].sum()), 'cloud_rows': int(res.row_off[-1]),
+          'instances': int(sum(vb.n_inst))}
+    if res.seg_counts is not None and res.seg_counts.size:
+        sc = res.seg_counts
+        st['inst_points'] = int(sc[:, 0].sum() + sc[:, 1].sum())
+        st['fused_points'] = int(sc[:, 2].sum() + sc[:, 4].sum())
+        st['boxes'] = int(res.boxes.shape[0])
+    return st
+
+
+FusionPipeline.run_host = _run_host
+FusionPipeline.batch_stats = _batch_stats

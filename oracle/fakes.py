@@ -25,20 +25,29 @@ from scipy.spatial import cKDTree
 
 # --------------------------------------------------------------------------- Open3D
 def radius_outlier_mask(points, nb_points, radius):
-    """bool[n]: keep iff #{q : |p-q|^2 < r^2} > nb_points (self included), float64."""
+    """bool[n]: keep iff #{q : |p-q|^2 < r^2} > nb_points (self included), float64.
+
+    Evaluated through the (nb_points+1)-th nearest neighbour: the count exceeds nb_points iff that neighbour's
+    squared distance is below r^2.  The squared distance is recomputed as ((a-b)**2).sum(-1); queries whose
+    value lies within 1e-9 (relative) of r^2 are re-done by brute force so that the KD-tree's own rounding can
+    never decide a case."""
     pts = np.asarray(points, dtype=np.float64).reshape(-1, 3)
     n = pts.shape[0]
     if n == 0:
         return np.zeros(0, dtype=bool)
-    tree = cKDTree(pts)
     r2 = float(radius) * float(radius)
-    keep = np.zeros(n, dtype=bool)
-    # candidates from a slightly inflated ball, then the strict squared-distance test
-    cand = tree.query_ball_point(pts, r=float(radius) * (1 + 1e-9) + 1e-12, workers=-1)
-    for i in range(n):
-        idx = np.asarray(cand[i], dtype=np.int64)
-        d2 = ((pts[idx] - pts[i]) ** 2).sum(-1)
-        keep[i] = int((d2 < r2).sum()) > nb_points
+    k = int(nb_points) + 1
+    if k > n:
+        return np.zeros(n, dtype=bool)
+    tree = cKDTree(pts)
+    _, idx = tree.query(pts, k=k, workers=-1)
+    idx = idx.reshape(n, k)[:, -1]
+    d2 = ((pts[idx] - pts) ** 2).sum(-1)
+    keep = d2 < r2
+    amb = np.nonzero(np.abs(d2 - r2) <= 1e-9 * r2)[0]
+    for i in amb:
+        dd = ((pts - pts[i]) ** 2).sum(-1)
+        keep[i] = int((dd < r2).sum()) > nb_points
     return keep
 
 

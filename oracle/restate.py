@@ -355,14 +355,18 @@ def instance_filter_params(cls_name):
 
 
 def ball_gate(pseudo, lidar, C=0.1):
-    """BallQuery (my_loader.py:489-494) with Q4: keep iff min_j |p - l_j| < C (float64 sqrt of sum of squares)."""
+    """BallQuery (my_loader.py:489-494) with Q4: keep iff min_j |p - l_j| < C (float64 sqrt of sum of squares).
+    Nearest neighbour through a KD-tree, distance recomputed; queries within 1e-9 of C re-done by brute force."""
+    pseudo = np.asarray(pseudo, np.float64).reshape(-1, 3)
+    lidar = np.asarray(lidar, np.float64).reshape(-1, 3)
+    if pseudo.shape[0] == 0 or lidar.shape[0] == 0:
+        return np.zeros(pseudo.shape[0], bool)
     tree = cKDTree(lidar)
-    cand = tree.query_ball_point(pseudo, C * (1 + 1e-9))
-    keep = np.zeros(pseudo.shape[0], bool)
-    for i, lst in enumerate(cand):
-        if lst:
-            d = np.sqrt(((pseudo[i][None, :] - lidar[lst]) ** 2).sum(-1))
-            keep[i] = d.min() < C
+    _, idx = tree.query(pseudo, k=1, workers=-1)
+    d = np.sqrt(((pseudo - lidar[idx]) ** 2).sum(-1))
+    keep = d < C
+    for i in np.nonzero(np.abs(d - C) <= 1e-9 * C)[0]:
+        keep[i] = np.sqrt(((pseudo[i][None, :] - lidar) ** 2).sum(-1)).min() < C
     return keep
 
 
