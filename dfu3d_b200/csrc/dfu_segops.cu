@@ -162,28 +162,26 @@ __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, do
   const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
   if (cx < 0 || cy < 0 || cz < 0) return false;   // far outside the reference bounding box (or an empty segment)
   int count = 0;
-  for (int dx = -1; dx <= 1; dx++) {
-    const int ex = cx + dx;
-    if (ex < 1) continue;
-    for (int dy = -1; dy <= 1; dy++) {
-      const int ey = cy + dy;
-      if (ey < 1) continue;
-      const int zlo = cz - 1 < 1 ? 1 : cz - 1;
-      const int c0 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, zlo));
-      const int c1 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
-      if (c1 <= c0) continue;
-      const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
-      for (int j = lo; j < hi; j++) {
-        const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
-                     az = __dsub_rn(__ldg(g.sz + j), pz);
-        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az));
-        if (MODE == 0) {
-          if (d2 < lim) {
-            if (++count > nb) return true;
-          }
-        } else {
-          if (__dsqrt_rn(d2) < lim) return true;
+  // the query's own (x, y) column first: with a small nb the walk usually ends there
+  for (int o = 0; o < 9; o++) {
+    const int dx = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) / 3 - 1), dy = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) % 3 - 1);
+    const int ex = cx + dx, ey = cy + dy;
+    if (ex < 1 || ey < 1) continue;
+    const int zlo = cz - 1 < 1 ? 1 : cz - 1;
+    const int c0 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, zlo));
+    const int c1 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
+    if (c1 <= c0) continue;
+    const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
+    for (int j = lo; j < hi; j++) {
+      const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
+                   az = __dsub_rn(__ldg(g.sz + j), pz);
+      const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az));
+      if (MODE == 0) {
+        if (d2 < lim) {
+          if (++count > nb) return true;
         }
+      } else {
+        if (__dsqrt_rn(d2) < lim) return true;
       }
     }
   }

@@ -145,19 +145,40 @@ class FusionPipeline(object):
         self.device = self.ctx.device
         self.lib = self.ctx.lib
         self._angles, _ = search_angles_cs()
+        self._calib_cache = {}
 
     # ------------------------------------------------------------------ helpers
     def build_views(self, vb):
+        """dfu_view records of the batch (cached on the ViewBatch: calibs / sweeps / planes are treated as immutable)."""
+        cached = getattr(vb, '_views', None)
+        if cached is not None:
+            return cached
         V = len(vb.view_sweep)
         views = np.zeros(V, _lib.VIEW_DTYPE)
-        slot = 0
-        inst = 0
+        consts = []
         for v in range(V):
-            off, cnt = vb.sweeps[vb.view_sweep[v]]
-            c = calib_constants(*vb.calibs[v])
-            fill_view(views[v], c, vb.planes[v], off, cnt, vb.n_inst[v], slot, inst)
-            slot += cnt
-            inst += vb.n_inst[v]
+            P2, R0, V2C = vb.calibs[v]
+            ck = (np.asarray(P2, np.float32).tobytes(), np.asarray(R0, np.float32).tobytes(), np.asarray(V2C, np.float32).tobytes())
+            c = self._calib_cache.get(ck)
+            if c is None:
+                if len(self._calib_cache) > 4096:
+                    self._calib_cache.clear()
+                c = self._calib_cache[ck] = calib_constants(P2, R0, V2C)
+            consts.append(c)
+        views['M43'] = np.stack([c['M43'].reshape(-1) for c in consts])
+        views['P2T'] = np.stack([c['P2T'].reshape(-1) for c in consts])
+        views['inv44'] = np.stack([c['inv44'].reshape(-1) for c in consts])
+        for k in ('cu', 'cv', 'fu', 'fv', 'tx', 'ty'):
+            views[k] = np.array([c[k] for c in consts], np.float32)
+        views['plane'] = np.stack([np.asarray(p if p is not None else (0, 0, 1, 1e9), np.float64) for p in vb.planes])
+        sw = np.asarray([vb.sweeps[s] for s in vb.view_sweep], np.int64).reshape(V, 2)
+        views['lidar_off'] = sw[:, 0]
+        views['lidar_cnt'] = sw[:, 1]
+        ni = np.asarray(vb.n_inst, np.int64)
+        views['n_inst'] = ni
+        views['slot_off'] = np.cumsum(sw[:, 1]) - sw[:, 1]
+        views['inst_off'] = np.cumsum(ni) - ni
+        vb._views = views
         return views
 
     def pack_masks(self, vb, views=None):
@@ -206,27 +227,31 @@ class FusionPipeline(object):
         return res
 
     def inst_params(self, vb):
+        """dfu_inst_params of every instance of the batch (cached on the ViewBatch)."""
+        cached = getattr(vb, '_inst_params', None)
+        if cached is not None:
+            return cached
         cfg = self.cfg
-        tot = int(sum(vb.n_inst))
-        ip = np.zeros(tot, _lib.INST_DTYPE)
-        k = 0
-        for v in range(len(vb.view_sweep)):
-            for j in range(vb.n_inst[v]):
-                cls = int(vb.classes[v][j])
-                sch = cfg.instance_schedule(vb.thing_classes[cls])
-                ip[k]['cls'] = cls
-                ip[k]['lidar_enabled'] = sch['lidar_enabled']
-                ip[k]['lidar_nb'] = sch['lidar_nb']
-                ip[k]['lidar_every_k'] = sch.get('lidar_every_k', 1)
-                ip[k]['pseudo_nb'] = sch['pseudo_nb']
-                ip[k]['pseudo_every_k'] = sch.get('pseudo_every_k', 1)
-                ip[k]['car_aspect_rule'] = sch['car_aspect_rule']
-                ip[k]['lidar_r'] = sch['lidar_r']
-                ip[k]['pseudo_r'] = sch['pseudo_r']
-                ip[k]['gate_dist'] = cfg.gate_dist
-                ip[k]['cluster_R0'] = cfg.cluster_R0
-                ip[k]['cluster_Rd'] = cfg.cluster_Rd
-                k += 1
+        cls = np.concatenate([np.asarray(c, np.int64).reshape(-1) for c in vb.classes] + [np.zeros(0, np.int64)])
+        assert cls.shape[0] == int(sum(vb.n_inst)), 'classes / n_inst mismatch'
+        table = np.zeros(len(vb.thing_classes), _lib.INST_DTYPE)
+        for c in np.unique(cls):
+            sch = cfg.instance_schedule(vb.thing_classes[int(c)])
+            t = table[int(c)]
+            t['cls'] = int(c)
+            t['lidar_enabled'] = sch['lidar_enabled']
+            t['lidar_nb'] = sch['lidar_nb']
+            t['lidar_every_k'] = sch.get('lidar_every_k', 1)
+            t['pseudo_nb'] = sch['pseudo_nb']
+            t['pseudo_every_k'] = sch.get('pseudo_every_k', 1)
+            t['car_aspect_rule'] = sch['car_aspect_rule']
+            t['lidar_r'] = sch['lidar_r']
+            t['pseudo_r'] = sch['pseudo_r']
+            t['gate_dist'] = cfg.gate_dist
+            t['cluster_R0'] = cfg.cluster_R0
+            t['cluster_Rd'] = cfg.cluster_Rd
+        ip = np.ascontiguousarray(table[cls])
+        vb._inst_params = ip
         return ip
 
     def run_instances(self, vb, res, want_lines=True, capacity=None):
@@ -332,9 +357,9 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True):
         d.copy_(h, non_blocking=True)
         return d
     m = hb.meta
-    vb = ViewBatch(lidar=up('lidar', hb.lidar), sweeps=m.sweeps, view_sweep=m.view_sweep, calibs=m.calibs, planes=m.planes,
-                   depth=up('depth', hb.depth), image=up('image', hb.image), masks=up('masks', hb.masks), n_inst=m.n_inst,
-                   classes=m.classes, boxes2d=m.boxes2d, thing_classes=m.thing_classes)
+    m.lidar, m.depth, m.image, m.masks = up('lidar', hb.lidar), up('depth', hb.depth), up('image', hb.image), up('masks', hb.masks)
+    m.labelmap = None
+    vb = m
     res = self.run(vb, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
     hc = st.get('cloud_host')
     if hc is None or hc.shape[0] < res.cloud.shape[0] or hc.dtype != res.cloud.dtype:

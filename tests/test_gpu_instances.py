@@ -103,8 +103,9 @@ def test_nn_gate_matches_oracle():
     q = np.concatenate([ref[:1500] + rng.normal(size=(1500, 3)) * 0.06, rng.uniform(-6, 6, size=(3000, 3))])
     ctx = _ctx()
     keep = torch.zeros(q.shape[0], dtype=torch.uint8, device='cuda')
-    ctx.check(ctx.lib.dfu_nn_gate(ctx.h, ctx.stream, _lib.dptr(torch.from_numpy(q).cuda()), q.shape[0],
-                                  _lib.dptr(torch.from_numpy(ref).cuda()), ref.shape[0], C.c_double(0.1), _lib.dptr(keep)))
+    qd, rd = torch.from_numpy(q).cuda(), torch.from_numpy(ref).cuda()
+    ctx.check(ctx.lib.dfu_nn_gate(ctx.h, ctx.stream, _lib.dptr(qd), q.shape[0], _lib.dptr(rd), ref.shape[0],
+                                  C.c_double(0.1), _lib.dptr(keep)))
     torch.cuda.synchronize()
     want = restate.ball_gate(q, ref, 0.1)
     assert np.array_equal(keep.cpu().numpy().astype(bool), want)
@@ -134,7 +135,8 @@ def test_lshape_fit_matches_oracle(seed, n):
     cl = torch.zeros(xy.shape[0], dtype=torch.int32, device='cuda')
     rect = np.zeros((xy.shape[0], 16))
     nk = np.zeros(1, np.int64)
-    ctx.check(ctx.lib.dfu_lshape_fit_sync(ctx.h, ctx.stream, _lib.dptr(torch.from_numpy(xy).cuda()), xy.shape[0],
+    xyd = torch.from_numpy(xy).cuda()
+    ctx.check(ctx.lib.dfu_lshape_fit_sync(ctx.h, ctx.stream, _lib.dptr(xyd), xy.shape[0],
                                           C.c_double(3.0), C.c_double(0.001), _lib.hptr(ang), ang.shape[0], _lib.dptr(cl),
                                           _lib.hptr(rect), rect.shape[0], _lib.hptr(nk)))
     lab, nc = restate.cluster_adaptive(xy[:, 0], xy[:, 1])
