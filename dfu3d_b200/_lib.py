@@ -53,6 +53,7 @@ _SIGS = {
     'dfu_profile_enable': (C.c_int, [_P, C.c_int]),
     'dfu_profile_read': (C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
     'dfu_project_label': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
+    'dfu_calib_apply': (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, C.c_int64, _P, _P]),
     'dfu_pack_masks': (C.c_int, [_P, _P, C.c_int, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
     'dfu_sparse_depth': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P]),
     'dfu_fuse_begin': (C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P, _P, _P]),
@@ -62,6 +63,7 @@ _SIGS = {
     'dfu_fuse_emit_voxels': (C.c_int, [_P, _P, _P, _P, _P, C.c_int64]),
     'dfu_fuse_emit_project': (C.c_int, [_P, _P, _P, _P]),
     'dfu_fuse_instances_sync': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, C.c_int64, _P, _P]),
+    'dfu_backproject_sync': (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.c_int, _P, _P, C.c_int64, _P]),
     'dfu_radius_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
     'dfu_sor_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_double, _P, _P, _P]),
     'dfu_nn_gate': (C.c_int, [_P, _P, _P, C.c_int64, _P, C.c_int64, C.c_double, _P]),

@@ -41,6 +41,8 @@ struct dfu_ctx {
   int64_t* off_vox;           // host [V+1]
   int stage;                  // 0 none, 1 begun, 2 projected, 3 densified
   int total_inst;
+  void* table_clean_ptr;      // angular voxel table known to be all-ones (pass C resets what pass A touched)
+  size_t table_clean_bytes;
   // ---- per-kernel device timing (dfu_profile_*) ----
   int prof_on;
   int prof_used;

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __rest
 
 // pass C: ordered scatter of the voxel representatives (voxel ordinal = rank of the opening pixel)
 __global__ void __launch_bounds__(S2_THREADS) k_densify_c(S2Prm q, const unsigned* __restrict__ key,
-                                                          const VoxCell* __restrict__ table,
+                                                          VoxCell* __restrict__ table,
                                                           const int64_t* __restrict__ blkoff, int32_t* __restrict__ repz,
                                                           int32_t* __restrict__ repy) {
   __shared__ int wsum[S2_THREADS / 32];
@@ -156,12 +156,12 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_c(S2Prm q, const unsigne
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   bool opener = false;
-  const VoxCell* c = nullptr;
+  VoxCell* c = nullptr;
   if (pix < npix) {
     unsigned k = key[(size_t)v * npix + pix];
     if (k != KEY_INVALID) {
       c = table + (size_t)v * NCELL + k;
-      opener = (c->first == (unsigned)pix);
+      opener = (*(volatile unsigned*)&c->first == (unsigned)pix);
     }
   }
   unsigned bal = __ballot_sync(0xffffffffu, opener);
@@ -173,6 +173,12 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_c(S2Prm q, const unsigne
     int64_t pos = blkoff[v * gridDim.x + blockIdx.x] + base + dfu_warp_excl(bal, lane);
     repz[pos] = (int32_t)c->argz;
     repy[pos] = (int32_t)c->argy;
+    // After this read the cell is dead: its opener puts it back to all-ones, so the next batch starts from a clean
+    // table without a 41 MB-per-view memset (a few % of the cells are ever touched).  Pixels of other blocks that
+    // still test `first` of this cell are non-openers and stay so whether they see the old value or 0xFFFFFFFF.
+    uint4* w4 = reinterpret_cast<uint4*>(c);
+    const uint4 ones = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    w4[0] = ones; w4[1] = ones;
   }
 }
 
@@ -291,7 +297,13 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   dim3 grid(bpv, V);
   {
     DFU_PROF(ctx, st, PT_DENSIFY_A);
-    DFU_CUDA(ctx, cudaMemsetAsync(table, 0xFF, (size_t)V * NCELL * sizeof(VoxCell), st));
+    const size_t tbytes = (size_t)V * NCELL * sizeof(VoxCell);
+    if (ctx->table_clean_ptr != (void*)table || ctx->table_clean_bytes < tbytes) {
+      // first use, or the slot was re-allocated: the whole allocation becomes the clean region
+      DFU_CUDA(ctx, cudaMemsetAsync(table, 0xFF, ctx->slot_bytes[SL_TABLE], st));
+    }
+    ctx->table_clean_ptr = nullptr;   // dirty until pass C has been queued
+    ctx->table_clean_bytes = 0;
     DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
     k_densify_a<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, stats);
     DFU_LAUNCH_CHECK(ctx);
@@ -340,6 +352,8 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     DFU_PROF(ctx, st, PT_DENSIFY_C);
     k_densify_c<<<grid, S2_THREADS, 0, st>>>(q, key, table, blkoff, repz, repy);
     DFU_LAUNCH_CHECK(ctx);
+    ctx->table_clean_ptr = (void*)table;
+    ctx->table_clean_bytes = ctx->slot_bytes[SL_TABLE];
   }
   if (nvox > 0) {
     DFU_PROF(ctx, st, PT_VOX_GATHER);
@@ -431,5 +445,101 @@ extern "C" int dfu_fuse_emit_voxels(dfu_ctx* ctx, int32_t* repz_pix, int32_t* re
     k_soa_to_rows<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tmp, repz_xyz, n);
     DFU_LAUNCH_CHECK(ctx);
   }
+  return DFU_OK;
+}
+
+// ---------------------------------------------------------------- stand-alone back-projection
+// my_loader.py:507-509 (depth threshold, row-major nonzero), calibration_kitti.py:134-144 + 89-102 (float64), and
+// optionally the height gate of my_loader.py:540.  Ordered compaction: block counts -> scan -> ballot-prefix scatter.
+__global__ void __launch_bounds__(S2_THREADS) k_bp_count(const dfu_view* __restrict__ views, S2Prm q, int gate,
+                                                         const float* __restrict__ depth, int32_t* __restrict__ blkcnt) {
+  const int v = blockIdx.y;
+  LOAD_VIEW(vw, views, v);
+  const int npix = q.H * q.W;
+  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  bool ok = false;
+  if (pix < npix) {
+    const float d = __ldg(depth + (size_t)v * npix + pix);
+    if (d >= q.min_depth) {
+      ok = true;
+      if (gate) {
+        const int row = pix / q.W, col = pix - row * q.W;
+        double X, Y, Z;
+        dfu_backproject(vw, col, row, d, X, Y, Z);
+        ok = Z < q.max_z;
+      }
+    }
+  }
+  const int n = __syncthreads_count(ok);
+  if (threadIdx.x == 0) blkcnt[v * gridDim.x + blockIdx.x] = n;
+}
+
+__global__ void __launch_bounds__(S2_THREADS) k_bp_scatter(const dfu_view* __restrict__ views, S2Prm q, int gate,
+                                                           const float* __restrict__ depth, const int64_t* __restrict__ blkoff,
+                                                           double* __restrict__ xyz, int32_t* __restrict__ pixout) {
+  __shared__ int wsum[S2_THREADS / 32];
+  const int v = blockIdx.y;
+  LOAD_VIEW(vw, views, v);
+  const int npix = q.H * q.W;
+  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  bool ok = false;
+  double X = 0, Y = 0, Z = 0;
+  if (pix < npix) {
+    const float d = __ldg(depth + (size_t)v * npix + pix);
+    if (d >= q.min_depth) {
+      const int row = pix / q.W, col = pix - row * q.W;
+      dfu_backproject(vw, col, row, d, X, Y, Z);
+      ok = !gate || Z < q.max_z;
+    }
+  }
+  const unsigned bal = __ballot_sync(0xffffffffu, ok);
+  if (lane == 0) wsum[w] = __popc(bal);
+  __syncthreads();
+  if (ok) {
+    int base = 0;
+    for (int i = 0; i < w; i++) base += wsum[i];
+    const int64_t pos = blkoff[v * gridDim.x + blockIdx.x] + base + dfu_warp_excl(bal, lane);
+    xyz[3 * pos] = X; xyz[3 * pos + 1] = Y; xyz[3 * pos + 2] = Z;
+    if (pixout) pixout[pos] = pix;
+  }
+}
+
+extern "C" int dfu_backproject_sync(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host,
+                                    const dfu_fusion_params* prm_host, const float* depth, int height_gate,
+                                    double* out_xyz, int32_t* out_pix, int64_t capacity, int64_t* counts_host) {
+  if (!ctx || V <= 0 || !views_host || !prm_host || !depth || !counts_host)
+    return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_backproject_sync: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  S2Prm q = make_s2(prm_host);
+  const int64_t npix = (int64_t)q.H * q.W;
+  if (npix <= 0 || npix >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_backproject_sync: bad depth map size");
+  const int bpv = (int)((npix + S2_THREADS - 1) / S2_THREADS);
+  DFU_SLOT(ctx, vd, dfu_view*, SL_VIEWS, sizeof(dfu_view) * V);
+  DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, (int64_t)V * bpv * sizeof(int32_t));
+  DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
+  ctx->stage = 0;   // SL_VIEWS / SL_BLK* are shared with the batched pipeline: any bound batch is gone
+  DFU_CUDA(ctx, cudaMemcpyAsync(vd, views_host, sizeof(dfu_view) * V, cudaMemcpyHostToDevice, st));
+  dim3 grid(bpv, V);
+  k_bp_count<<<grid, S2_THREADS, 0, st>>>(vd, q, height_gate, depth, blkcnt);
+  DFU_LAUNCH_CHECK(ctx);
+  int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, (int64_t)V * bpv);
+  if (rc) return rc;
+  k_vox_view_offsets<<<(V + 1 + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voxoff);
+  DFU_LAUNCH_CHECK(ctx);
+  int64_t* pin = (int64_t*)dfu_pinned(ctx, (V + 1) * sizeof(int64_t));
+  if (!pin) return DFU_ERR_CUDA;
+  DFU_CUDA(ctx, cudaMemcpyAsync(pin, voxoff, (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaStreamSynchronize(st));   // also covers the pageable views_host copy
+  for (int v = 0; v < V; v++) counts_host[v] = pin[v + 1] - pin[v];
+  const int64_t total = pin[V];
+  if (!out_xyz) return DFU_OK;   // size query
+  if (capacity < total)
+    return dfu_set_err(ctx, DFU_ERR_CAPACITY, "back-projection needs %lld rows, capacity %lld", (long long)total, (long long)capacity);
+  if (total == 0) return DFU_OK;
+  DFU_PROF(ctx, st, PT_MISC);
+  k_bp_scatter<<<grid, S2_THREADS, 0, st>>>(vd, q, height_gate, depth, blkoff, out_xyz, out_pix);
+  DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }

@@ -258,6 +258,68 @@ extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_vie
   return DFU_OK;
 }
 
+// ---------------------------------------------------------------- Calibration methods on caller arrays
+// op 0 lidar_to_rect f32 [n][3] -> f32 [n][3]            (calibration_kitti.py:104-112)
+// op 1 lidar_to_rect f64 [n][3] -> f64 [n][3]            (same call with a float64 argument, my_loader.py:679)
+// op 2 rect_to_img   f32 [n][3] -> f32 [n][2], f32 [n]   (:114-123)
+// op 3 img_to_rect   u i64 [n], v i64 [n], d f32 [n] -> f64 [n][3]   (:134-144)
+// op 4 rect_to_lidar f64 [n][3] -> f64 [n][3]            (:89-102)
+// op 5 lidar_to_img  f32 [n][3] -> f32 [n][2], f32 [n]   (:125-132)
+__global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const void* __restrict__ in0,
+                                                     const void* __restrict__ in1, const void* __restrict__ in2, int64_t n,
+                                                     void* __restrict__ out0, void* __restrict__ out1) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  if (op == 0 || op == 2 || op == 5) {
+    const float* a = (const float*)in0 + 3 * i;
+    float x = a[0], y = a[1], z = a[2];
+    if (op != 2) {
+      const float rx = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 0, 3), ry = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 1, 3),
+                  rz = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 2, 3);
+      x = rx; y = ry; z = rz;
+    }
+    if (op == 0) {
+      float* o = (float*)out0 + 3 * i;
+      o[0] = x; o[1] = y; o[2] = z;
+      return;
+    }
+    const float h0 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 0, 3), h1 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 1, 3),
+                h2 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 2, 3);
+    float* o = (float*)out0 + 2 * i;
+    o[0] = __fdiv_rn(h0, z);
+    o[1] = __fdiv_rn(h1, z);
+    ((float*)out1)[i] = __fsub_rn(h2, vw.P2T[3 * 3 + 2]);
+  } else if (op == 1) {
+    const double* a = (const double*)in0 + 3 * i;
+    double* o = (double*)out0 + 3 * i;
+    for (int j = 0; j < 3; j++) o[j] = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.M43, j, 3);
+  } else if (op == 3) {
+    const long long u = ((const long long*)in0)[i], v = ((const long long*)in1)[i];
+    const double dd = (double)((const float*)in2)[i];
+    double* o = (double*)out0 + 3 * i;
+    o[0] = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)u, (double)vw.cu), dd), (double)vw.fu), (double)vw.tx);
+    o[1] = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)v, (double)vw.cv), dd), (double)vw.fv), (double)vw.ty);
+    o[2] = dd;
+  } else if (op == 4) {
+    const double* a = (const double*)in0 + 3 * i;
+    double* o = (double*)out0 + 3 * i;
+    for (int j = 0; j < 3; j++) o[j] = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.inv44, j, 4);
+  }
+}
+
+extern "C" int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0,
+                               const void* in1, const void* in2, int64_t n, void* out0, void* out1) {
+  if (!ctx || !view_host || op < 0 || op > 5 || n < 0 || (n > 0 && (!in0 || !out0)))
+    return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: bad argument");
+  if (n > 0 && (op == 2 || op == 5) && !out1) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op needs out1");
+  if (n > 0 && op == 3 && (!in1 || !in2)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op 3 needs u, v, depth");
+  if (n == 0) return DFU_OK;
+  DFU_PROF(ctx, (cudaStream_t)stream, PT_PROJECT);
+  k_calib_apply<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*view_host, op, in0, in1, in2, n, out0, out1);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
 // ---------------------------------------------------------------- batched pipeline: begin + project
 extern "C" int dfu_fuse_begin(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host,
                               const dfu_fusion_params* prm, const void* lidar_xyzi, const float* depth,

@@ -1,0 +1,156 @@
+"""Stand-alone operators of libdfu3d.so on caller-provided point sets (include/dfu3d.h, last section).
+
+Thin argument marshalling only: numpy or torch in, the same kind out.  Segments (``seg_off``) are independent
+point sets processed in one launch sequence.  No CPU fallback: every function needs the CUDA library.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _dev_f64(ctx, a, cols):
+    """(device float64 [n, cols] contiguous, was_numpy)"""
+    if isinstance(a, torch.Tensor):
+        t = a.to(device=ctx.device, dtype=torch.float64).reshape(-1, cols).contiguous()
+        return t, False
+    t = torch.from_numpy(np.ascontiguousarray(np.asarray(a, np.float64).reshape(-1, cols))).to(ctx.device)
+    return t, True
+
+
+def _seg(n, seg_off):
+    if seg_off is None:
+        return np.array([0, n], np.int64)
+    so = np.ascontiguousarray(np.asarray(seg_off, np.int64))
+    assert so[0] == 0 and so[-1] == n and np.all(np.diff(so) >= 0), 'seg_off must ascend from 0 to n'
+    return so
+
+
+def _out(t, as_numpy, dtype=None):
+    if as_numpy:
+        torch.cuda.current_stream(t.device).synchronize()
+        a = t.cpu().numpy()
+        return a.astype(dtype) if dtype is not None else a
+    return t.to(dtype=torch.bool) if dtype is bool else t
+
+
+def radius_filter(points, nb_points, radius, seg_off=None, ctx=None, return_counts=False):
+    """Open3D ``remove_radius_outlier(nb_points, radius)`` keep mask (call sites
+    tools/PENet/dataloaders/my_loader.py:569-599): keep iff #{q : |p - q|^2 < r^2} > nb_points, self included.
+    ``nb_points`` / ``radius`` are scalars or one value per segment."""
+    ctx = ctx or _lib.default_context(0)
+    xyz, as_np = _dev_f64(ctx, points, 3)
+    n = xyz.shape[0]
+    so = _seg(n, seg_off)
+    nseg = so.shape[0] - 1
+    rad = np.ascontiguousarray(np.broadcast_to(np.asarray(radius, np.float64), (nseg,)))
+    nbs = np.ascontiguousarray(np.broadcast_to(np.asarray(nb_points, np.int32), (nseg,)))
+    keep = torch.zeros(n, dtype=torch.uint8, device=ctx.device)
+    cnt = torch.zeros(nseg, dtype=torch.int32, device=ctx.device)
+    ctx.check(ctx.lib.dfu_radius_filter(ctx.h, ctx.stream, _lib.dptr(xyz) if n else None, nseg, _lib.hptr(so),
+                                        _lib.hptr(rad), _lib.hptr(nbs), _lib.dptr(keep) if n else _lib.dptr(cnt),
+                                        _lib.dptr(cnt)))
+    k = _out(keep, as_np, bool)
+    return (k, _out(cnt, as_np)) if return_counts else k
+
+
+def sor_filter(points, nb_neighbors, std_ratio, seg_off=None, ctx=None, return_stats=False):
+    """Open3D ``remove_statistical_outlier(nb_neighbors, std_ratio)`` keep mask (commented-out call
+    tools/PENet/dataloaders/my_loader0.py:735; BASELINE.json config 3).  With ``return_stats``: (keep, mean k-NN
+    distance per point, [nseg, 2] mu / sigma)."""
+    ctx = ctx or _lib.default_context(0)
+    xyz, as_np = _dev_f64(ctx, points, 3)
+    n = xyz.shape[0]
+    so = _seg(n, seg_off)
+    nseg = so.shape[0] - 1
+    keep = torch.zeros(max(n, 1), dtype=torch.uint8, device=ctx.device)
+    mean = torch.zeros(max(n, 1), dtype=torch.float64, device=ctx.device) if return_stats else None
+    stats = np.zeros((nseg, 2), np.float64) if return_stats else None
+    ctx.check(ctx.lib.dfu_sor_filter(ctx.h, ctx.stream, _lib.dptr(xyz) if n else None, nseg, _lib.hptr(so),
+                                     int(nb_neighbors), C.c_double(float(std_ratio)), _lib.dptr(keep), _lib.dptr(mean),
+                                     _lib.hptr(stats)))
+    k = _out(keep[:n], as_np, bool)
+    if return_stats:
+        return k, _out(mean[:n], as_np), stats
+    return k
+
+
+def nn_gate(query, ref, max_dist, ctx=None):
+    """BallQuery (tools/PENet/dataloaders/my_loader.py:489-494 with quirk Q4): keep[i] = min_j |q_i - r_j| < max_dist."""
+    ctx = ctx or _lib.default_context(0)
+    q, as_np = _dev_f64(ctx, query, 3)
+    r, _ = _dev_f64(ctx, ref, 3)
+    keep = torch.zeros(max(q.shape[0], 1), dtype=torch.uint8, device=ctx.device)
+    ctx.check(ctx.lib.dfu_nn_gate(ctx.h, ctx.stream, _lib.dptr(q) if q.shape[0] else None, q.shape[0],
+                                  _lib.dptr(r) if r.shape[0] else None, r.shape[0], C.c_double(float(max_dist)), _lib.dptr(keep)))
+    return _out(keep[:q.shape[0]], as_np, bool)
+
+
+_ANGLES = None
+
+
+def search_angles_cs():
+    """cos / sin of the 89 angles of rectangle_fitting.py:117-122 (host numpy, as the reference evaluates them)."""
+    global _ANGLES
+    if _ANGLES is None:
+        dtheta = np.deg2rad(1.0)
+        th = np.arange(0.0, np.pi / 2.0 - dtheta, dtheta)
+        _ANGLES = (np.ascontiguousarray(np.stack([np.cos(th), np.sin(th)], 1)), th)
+    return _ANGLES
+
+
+def lshape_fit(ox, oy, R0=3.0, Rd=0.001, ctx=None):
+    """LShapeFitting.fitting arithmetic (rectangle_fitting.py:39-191): (cluster id per point numbered by minimum point
+    index [n] int32 numpy, rect [K, 16] float64 numpy: a[4] b[4] c[4] theta best-cost runner-up n)."""
+    ctx = ctx or _lib.default_context(0)
+    xy = np.ascontiguousarray(np.stack([np.asarray(ox, np.float64).reshape(-1), np.asarray(oy, np.float64).reshape(-1)], 1))
+    n = xy.shape[0]
+    if n == 0:
+        return np.zeros(0, np.int32), np.zeros((0, 16))
+    ang, _ = search_angles_cs()
+    xyd = torch.from_numpy(xy).to(ctx.device)
+    cl = torch.zeros(n, dtype=torch.int32, device=ctx.device)
+    rect = np.zeros((n, 16))
+    nk = np.zeros(1, np.int64)
+    ctx.check(ctx.lib.dfu_lshape_fit_sync(ctx.h, ctx.stream, _lib.dptr(xyd), n, C.c_double(R0), C.c_double(Rd),
+                                          _lib.hptr(ang), ang.shape[0], _lib.dptr(cl), _lib.hptr(rect), n, _lib.hptr(nk)))
+    torch.cuda.current_stream(ctx.device).synchronize()
+    return cl.cpu().numpy(), rect[:int(nk[0])].copy()
+
+
+def backproject(depth, calibs, min_depth=0.001, max_z=None, ctx=None):
+    """Depth maps -> LiDAR-frame points (my_loader.py:507-509,535-536 [+ the height gate of :540 when ``max_z`` is
+    given]; calibration_kitti.py:134-144,89-102, float64).  ``depth`` [V,H,W] or [H,W] float32 (NOT mutated — quirk
+    Q10 is the drop-in wrapper's business); ``calibs``: one (P2, R0, V2C) per view.
+    Returns (xyz [M,3] float64, pix [M] int32 linear pixel index, counts [V] int64); rows are ordered by (view, pixel)."""
+    from . import pipeline
+    ctx = ctx or _lib.default_context(0)
+    as_np = not isinstance(depth, torch.Tensor)
+    d = torch.as_tensor(np.asarray(depth, np.float32) if as_np else depth)
+    d = d.to(device=ctx.device, dtype=torch.float32)
+    if d.dim() == 2:
+        d = d[None]
+    d = d.contiguous()
+    V, H, W = d.shape
+    if len(calibs) == 3 and not isinstance(calibs[0], (tuple, list)):
+        calibs = [calibs]      # a single (P2, R0, V2C)
+    assert len(calibs) == V, 'one calibration per view'
+    views = np.zeros(V, _lib.VIEW_DTYPE)
+    for v in range(V):
+        pipeline.fill_view(views[v], pipeline.calib_constants(*calibs[v]))
+    prm = np.zeros(1, _lib.FUSION_DTYPE)
+    prm['H'], prm['W'], prm['Hm'], prm['Wm'] = H, W, H, W
+    prm['min_depth'] = min_depth
+    prm['max_z'] = 0.0 if max_z is None else max_z
+    counts = np.zeros(V, np.int64)
+    gate = int(max_z is not None)
+    ctx.check(ctx.lib.dfu_backproject_sync(ctx.h, ctx.stream, V, _lib.hptr(views), _lib.hptr(prm), _lib.dptr(d), gate,
+                                           None, None, 0, _lib.hptr(counts)))
+    M = int(counts.sum())
+    xyz = torch.empty((max(M, 1), 3), dtype=torch.float64, device=ctx.device)
+    pix = torch.empty(max(M, 1), dtype=torch.int32, device=ctx.device)
+    ctx.check(ctx.lib.dfu_backproject_sync(ctx.h, ctx.stream, V, _lib.hptr(views), _lib.hptr(prm), _lib.dptr(d), gate,
+                                           _lib.dptr(xyz), _lib.dptr(pix), xyz.shape[0], _lib.hptr(counts)))
+    return _out(xyz[:M], as_np), _out(pix[:M], as_np), counts

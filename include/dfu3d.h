@@ -114,6 +114,17 @@ int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_d
                       const dfu_fusion_params* prm_host, const void* lidar_xyzi, const uint32_t* labelmap,
                       float* out_uv, float* out_depth, int32_t* out_pix, uint8_t* out_flags, uint32_t* out_label);
 
+/* The Calibration methods (calibration_kitti.py:89-144) on caller arrays, one thread per row, with the reference's
+ * dtypes and operation order.  view_host: only the calibration fields are read.
+ *   op 0 lidar_to_rect  in0 float  [n][3]                          -> out0 float  [n][3]
+ *   op 1 lidar_to_rect  in0 double [n][3] (my_loader.py:679)       -> out0 double [n][3]
+ *   op 2 rect_to_img    in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n] (depth)
+ *   op 3 img_to_rect    in0 int64 u[n], in1 int64 v[n], in2 float d[n] -> out0 double [n][3]
+ *   op 4 rect_to_lidar  in0 double [n][3]                          -> out0 double [n][3]
+ *   op 5 lidar_to_img   in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n] */
+int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0, const void* in1,
+                    const void* in2, int64_t n, void* out0, void* out1);
+
 /* masks [sum n_inst][Hm][Wm] (uint8 when is_f32 == 0, float when 1; != 0 means set) -> labelmap.
  * Replaces Image.fromarray(np.uint8(mask)) (my_loader.py:525). */
 int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, const void* masks, int is_f32,
@@ -175,6 +186,15 @@ int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* inst_params_hos
 /* ---- stand-alone operators on caller-provided point sets (segments) -----------------------------
  * xyz: float64 [n][3] rows.  seg_off_host [nseg+1].  Used by the drop-in Python functions and by
  * the filter benchmarks. */
+
+/* Back-projection of depth maps into the LiDAR frame (my_loader.py:507-509 depth threshold + row-major nonzero,
+ * calibration_kitti.py:134-144 img_to_rect and :89-102 rect_to_lidar in float64; height_gate != 0 also applies
+ * new_p[:, 2] < max_z of my_loader.py:540).  depth [V][H][W]; rows come out per view in row-major pixel order.
+ * counts_host [V] receives the rows per view.  out_xyz == NULL: size query only.  out_xyz float64 [capacity][3],
+ * out_pix int32 [capacity] linear pixel index (nullable).  Only H, W, min_depth, max_z of prm_host are read. */
+int dfu_backproject_sync(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host, const dfu_fusion_params* prm_host,
+                         const float* depth, int height_gate, double* out_xyz, int32_t* out_pix, int64_t capacity,
+                         int64_t* counts_host);
 
 /* Open3D remove_radius_outlier semantics (oracle/fakes.py): keep iff #{q: |p-q|^2 < r^2} > nb. */
 int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,

@@ -52,16 +52,30 @@ def radius_outlier_mask(points, nb_points, radius):
 
 
 def knn_mean_distance(points, k):
-    """float64[n]: mean of the min(k, n) smallest distances (self, 0.0, included)."""
+    """float64[n]: mean of the min(k, n) smallest distances (self, 0.0, included).
+
+    Open3D (PointCloud::RemoveStatisticalOutliers) takes the squared distances of KDTreeFlann::SearchKNN, which
+    arrive in ascending order, replaces each by its square root and adds them with std::accumulate, i.e.
+    sequentially.  The neighbours come from the KD-tree; the squared distances are recomputed as
+    ((a - b) ** 2).sum(-1) so that the tree's own rounding never enters the result."""
     pts = np.asarray(points, dtype=np.float64).reshape(-1, 3)
     n = pts.shape[0]
     if n == 0:
         return np.zeros(0)
     kk = min(int(k), n)
     tree = cKDTree(pts)
-    d, _ = tree.query(pts, k=kk, workers=-1)
-    d = d.reshape(n, kk)
-    return d.sum(-1) / kk
+    out = np.empty(n)
+    for a in range(0, n, 1 << 18):
+        q = pts[a:a + (1 << 18)]
+        _, idx = tree.query(q, k=kk, workers=-1)
+        idx = idx.reshape(q.shape[0], kk)
+        d = np.sqrt(((pts[idx] - q[:, None, :]) ** 2).sum(-1))
+        d.sort(axis=1)
+        acc = np.zeros(q.shape[0])
+        for j in range(kk):
+            acc = acc + d[:, j]
+        out[a:a + q.shape[0]] = acc / kk
+    return out
 
 
 def statistical_outlier_mask(points, nb_neighbors, std_ratio, return_stats=False):
