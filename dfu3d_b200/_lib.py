@@ -25,7 +25,7 @@ FUSION_DTYPE = np.dtype([
     ('H', np.int32), ('W', np.int32), ('Hm', np.int32), ('Wm', np.int32), ('bound_x', np.int32), ('bound_y', np.int32),
     ('round_mode', np.int32), ('image_is_i32', np.int32), ('min_depth', np.float32), ('pad1', np.float32),
     ('max_z', np.float64), ('plane_offset', np.float64), ('plane_range', np.float64, (4,)), ('min_theta', np.float64),
-    ('max_per_voxel', np.int32), ('pad2', np.int32),
+    ('max_per_voxel', np.int32), ('no_fov_cull', np.int32),
 ], align=True)
 assert FUSION_DTYPE.itemsize == 104, FUSION_DTYPE.itemsize
 
@@ -67,6 +67,7 @@ _SIGS = {
     'dfu_radius_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
     'dfu_sor_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_double, _P, _P, _P]),
     'dfu_nn_gate': (C.c_int, [_P, _P, _P, C.c_int64, _P, C.c_int64, C.c_double, _P]),
+    'dfu_generate_anns_sync': (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int, C.c_double, C.c_double, _P, C.c_int, _P, C.c_int64, _P]),
     'dfu_lshape_fit_sync': (C.c_int, [_P, _P, _P, C.c_int64, C.c_double, C.c_double, _P, C.c_int, _P, _P, C.c_int64, _P]),
 }
 EXPORTED = sorted(_SIGS)

@@ -6,7 +6,7 @@
 #include <string.h>
 #include "../../include/dfu3d.h"
 
-#define DFU_NSLOTS 160
+#define DFU_NSLOTS 224
 #define DFU_PROF_POOL 8192
 #ifndef DFU_PROF_NTAGS
 #define DFU_PROF_NTAGS 24

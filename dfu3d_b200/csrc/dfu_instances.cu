@@ -233,6 +233,81 @@ __global__ void __launch_bounds__(128) k_anns(const double* __restrict__ rect, i
   anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(zmax[g]), views[d.view].M43, d.car_rule, o);
 }
 
+// ---------------------------------------------------------------- stand-alone GenerateAnns (my_loader.py:633-684)
+__global__ void __launch_bounds__(256) k_anns_prepare(const double* __restrict__ pts, int64_t n, double* __restrict__ x,
+                                                      double* __restrict__ y, int32_t* __restrict__ seg,
+                                                      unsigned long long* __restrict__ zmax) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  unsigned long long b = 0;
+  if (i < n) {
+    x[i] = pts[3 * i]; y[i] = pts[3 * i + 1]; seg[i] = 0;
+    b = dfu_order_f64(pts[3 * i + 2]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+    b = ob > b ? ob : b;
+  }
+  if ((threadIdx.x & 31) == 0 && b) atomicMax(zmax, b);
+}
+
+__global__ void __launch_bounds__(128) k_anns_single(const double* __restrict__ rect, int K, const dfu_view vw, int car_rule,
+                                                     const unsigned long long* __restrict__ zmax, double* __restrict__ boxes) {
+  const int k = blockIdx.x * 128 + threadIdx.x;
+  if (k >= K) return;
+  double* o = boxes + (int64_t)k * DFU_BOX_DOUBLES;
+  o[0] = 0; o[1] = 0; o[2] = k; o[3] = 0;
+  anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(*zmax), vw.M43, car_rule, o);
+}
+
+#define GA_CLUSTER OPS_B
+#define GA_FIT OPS_C
+enum { GA_X = 160, GA_Y, GA_SEG, GA_MISC, GA_ANG, GA_RECT, GA_BOX };
+
+extern "C" int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host, const double* points, int64_t n,
+                                      int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int na,
+                                      double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host) {
+  if (!ctx || !view_host || n < 0 || !angles_cs_host || na <= 0 || na > DFU_N_ANGLES_MAX || !n_boxes_host)
+    return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_generate_anns_sync: bad argument");
+  *n_boxes_host = 0;
+  if (n == 0) return DFU_OK;        // my_loader.py:635: empty objects write nothing
+  if (!points) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_generate_anns_sync: points is NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+  DFU_SLOT(ctx, x, double*, GA_X, n * 8);
+  DFU_SLOT(ctx, y, double*, GA_Y, n * 8);
+  DFU_SLOT(ctx, seg, int32_t*, GA_SEG, n * 4);
+  DFU_SLOT(ctx, misc, double*, GA_MISC, 64);
+  DFU_SLOT(ctx, ang, double*, GA_ANG, (size_t)na * 16);
+  const double rr[3] = {R0, Rd, 0.0};
+  DFU_CUDA(ctx, cudaMemcpyAsync(misc, rr, 24, cudaMemcpyHostToDevice, st));   // misc[2] = zmax bits (0 = none yet)
+  DFU_CUDA(ctx, cudaMemcpyAsync(ang, angles_cs_host, (size_t)na * 16, cudaMemcpyHostToDevice, st));
+  k_anns_prepare<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(points, n, x, y, seg, (unsigned long long*)(misc + 2));
+  DFU_LAUNCH_CHECK(ctx);
+  int rc = dfu_grid_err_reset(ctx, st, GA_CLUSTER);
+  if (rc) return rc;
+  ClusterOut co;
+  rc = dfu_cluster_points(ctx, st, GA_CLUSTER, x, y, seg, nullptr, n, 1, misc, misc + 1, &co);
+  if (rc) return rc;
+  int32_t hk[2] = {0, 0};
+  DFU_CUDA(ctx, cudaMemcpyAsync(&hk[0], co.ncluster, 4, cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaMemcpyAsync(&hk[1], dfu_grid_err_ptr(ctx, GA_CLUSTER), 4, cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  if (hk[1]) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_generate_anns_sync: a coordinate is NaN or the set spans more than 65533 cells");
+  const int K = hk[0];
+  *n_boxes_host = K;
+  if (K > capacity || !boxes_out_host)
+    return dfu_set_err(ctx, DFU_ERR_CAPACITY, "box output needs %d records, capacity %lld", K, (long long)capacity);
+  DFU_SLOT(ctx, rect, double*, GA_RECT, (size_t)K * 16 * 8);
+  DFU_SLOT(ctx, boxes, double*, GA_BOX, (size_t)K * DFU_BOX_DOUBLES * 8);
+  rc = dfu_fit_clusters(ctx, st, GA_FIT, x, y, co.cluster_of_point, n, K, ang, na, rect);
+  if (rc) return rc;
+  k_anns_single<<<(K + 127) / 128, 128, 0, st>>>(rect, K, *view_host, car_aspect_rule, (const unsigned long long*)(misc + 2), boxes);
+  DFU_LAUNCH_CHECK(ctx);
+  DFU_CUDA(ctx, cudaMemcpyAsync(boxes_out_host, boxes, (size_t)K * DFU_BOX_DOUBLES * 8, cudaMemcpyDeviceToHost, st));
+  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  return DFU_OK;
+}
+
 // ---------------------------------------------------------------- host orchestration
 enum {
   IS_CNT = 100, IS_POFF, IS_KEY, IS_VAL, IS_SKEY, IS_SVAL, IS_TMP, IS_SEGOFF, IS_PX, IS_PY, IS_PZ, IS_SEG, IS_INST,

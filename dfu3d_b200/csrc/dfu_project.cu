@@ -6,14 +6,14 @@
 #define S1_THREADS 256
 
 struct S1Prm {
-  int H, W, Hm, Wm, bound_x, bound_y, round_mode;
+  int H, W, Hm, Wm, bound_x, bound_y, round_mode, no_fov;
   double plane_offset, xlo, xhi, ylo, yhi;
 };
 
 static S1Prm make_s1(const dfu_fusion_params* p) {
   S1Prm s;
   s.H = p->H; s.W = p->W; s.Hm = p->Hm; s.Wm = p->Wm;
-  s.bound_x = p->bound_x; s.bound_y = p->bound_y; s.round_mode = p->round_mode;
+  s.bound_x = p->bound_x; s.bound_y = p->bound_y; s.round_mode = p->round_mode; s.no_fov = p->no_fov_cull;
   s.plane_offset = p->plane_offset;
   s.xlo = p->plane_range[0]; s.xhi = p->plane_range[1]; s.ylo = p->plane_range[2]; s.yhi = p->plane_range[3];
   return s;
@@ -40,7 +40,7 @@ __device__ __forceinline__ S1Out s1_point(const dfu_view& vw, const S1Prm& q, fl
   o.v = __fdiv_rn(h1, rz);
   o.depth = __fsub_rn(h2, vw.P2T[3 * 3 + 2]);
   // get_fov_flag (vis_utils.py:108-123): un-rounded coordinates against the depth-map shape
-  bool fov = (o.u >= 0.0f) && (o.u < (float)q.W) && (o.v >= 0.0f) && (o.v < (float)q.H) && (o.depth >= 0.0f);
+  bool fov = q.no_fov || ((o.u >= 0.0f) && (o.u < (float)q.W) && (o.v >= 0.0f) && (o.v < (float)q.H) && (o.depth >= 0.0f));
   // above_plane (my_loader.py:471-484); dgemv order measured on the reference container: y*b first
   double acc = __dmul_rn((double)p.y, vw.plane[1]);
   acc = __fma_rn((double)p.x, vw.plane[0], acc);
@@ -243,6 +243,7 @@ extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_vie
   cudaStream_t st = (cudaStream_t)stream;
   S1Prm q = make_s1(prm);
   q.round_mode = 1;
+  q.no_fov = 0;
   const int64_t npix = (int64_t)V * q.H * q.W;
   DFU_SLOT(ctx, winner, int*, SL_OP0, npix * sizeof(int));
   DFU_PROF(ctx, st, PT_SPARSE_DEPTH);
@@ -265,15 +266,16 @@ extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_vie
 // op 3 img_to_rect   u i64 [n], v i64 [n], d f32 [n] -> f64 [n][3]   (:134-144)
 // op 4 rect_to_lidar f64 [n][3] -> f64 [n][3]            (:89-102)
 // op 5 lidar_to_img  f32 [n][3] -> f32 [n][2], f32 [n]   (:125-132)
+// op 6 get_fov_flag  f32 rect [n][3], in1 = int32 {H, W} -> u8 [n]   (vis_utils.py:108-123 == my_loader.py:85-100)
 __global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const void* __restrict__ in0,
                                                      const void* __restrict__ in1, const void* __restrict__ in2, int64_t n,
                                                      void* __restrict__ out0, void* __restrict__ out1) {
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
-  if (op == 0 || op == 2 || op == 5) {
+  if (op == 0 || op == 2 || op == 5 || op == 6) {
     const float* a = (const float*)in0 + 3 * i;
     float x = a[0], y = a[1], z = a[2];
-    if (op != 2) {
+    if (op != 2 && op != 6) {
       const float rx = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 0, 3), ry = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 1, 3),
                   rz = dfu_row4_f32(x, y, z, 1.0f, vw.M43, 2, 3);
       x = rx; y = ry; z = rz;
@@ -285,10 +287,16 @@ __global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const 
     }
     const float h0 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 0, 3), h1 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 1, 3),
                 h2 = dfu_row4_f32(x, y, z, 1.0f, vw.P2T, 2, 3);
+    const float u = __fdiv_rn(h0, z), v = __fdiv_rn(h1, z), dep = __fsub_rn(h2, vw.P2T[3 * 3 + 2]);
+    if (op == 6) {
+      const int H = ((const int*)in1)[0], W = ((const int*)in1)[1];
+      ((uint8_t*)out0)[i] = (u >= 0.0f && u < (float)W && v >= 0.0f && v < (float)H && dep >= 0.0f) ? 1 : 0;
+      return;
+    }
     float* o = (float*)out0 + 2 * i;
-    o[0] = __fdiv_rn(h0, z);
-    o[1] = __fdiv_rn(h1, z);
-    ((float*)out1)[i] = __fsub_rn(h2, vw.P2T[3 * 3 + 2]);
+    o[0] = u;
+    o[1] = v;
+    ((float*)out1)[i] = dep;
   } else if (op == 1) {
     const double* a = (const double*)in0 + 3 * i;
     double* o = (double*)out0 + 3 * i;
@@ -309,9 +317,10 @@ __global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const 
 
 extern "C" int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0,
                                const void* in1, const void* in2, int64_t n, void* out0, void* out1) {
-  if (!ctx || !view_host || op < 0 || op > 5 || n < 0 || (n > 0 && (!in0 || !out0)))
+  if (!ctx || !view_host || op < 0 || op > 6 || n < 0 || (n > 0 && (!in0 || !out0)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: bad argument");
   if (n > 0 && (op == 2 || op == 5) && !out1) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op needs out1");
+  if (n > 0 && op == 6 && !in1) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op 6 needs the image shape");
   if (n > 0 && op == 3 && (!in1 || !in2)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op 3 needs u, v, depth");
   if (n == 0) return DFU_OK;
   DFU_PROF(ctx, (cudaStream_t)stream, PT_PROJECT);

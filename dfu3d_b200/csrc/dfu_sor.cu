@@ -26,7 +26,7 @@
 #define SOR_THREADS 128
 #define SOR_KMAX 64
 #define SOR_CHUNK 4096
-enum { SO_X = 100, SO_Y, SO_Z, SO_SEG, SO_SEGOFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_SX, SO_SY, SO_SZ, SO_TMP,
+enum { SO_X = 170, SO_Y, SO_Z, SO_SEG, SO_SEGOFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_SX, SO_SY, SO_SZ, SO_TMP,
        SO_MEAN, SO_CHSEG, SO_CHSTART, SO_PART, SO_SEGSTAT, SO_SEGCH };
 
 __device__ __forceinline__ unsigned long long sor_spread3(unsigned v) {

@@ -85,7 +85,7 @@ def fill_view(rec, consts, plane=None, lidar_off=0, lidar_cnt=0, n_inst=0, slot_
     rec['inst_off'] = inst_off
 
 
-def fusion_params(cfg, H, W, Hm, Wm, image_is_i32=False, round_mode=0):
+def fusion_params(cfg, H, W, Hm, Wm, image_is_i32=False, round_mode=0, no_fov_cull=False):
     p = np.zeros(1, _lib.FUSION_DTYPE)
     p['H'], p['W'], p['Hm'], p['Wm'] = H, W, Hm, Wm
     p['bound_x'], p['bound_y'] = cfg.bounds
@@ -97,6 +97,7 @@ def fusion_params(cfg, H, W, Hm, Wm, image_is_i32=False, round_mode=0):
     p['plane_range'] = np.asarray(cfg.plane_range, np.float64)
     p['min_theta'] = cfg.min_theta
     p['max_per_voxel'] = cfg.max_per_voxel
+    p['no_fov_cull'] = int(no_fov_cull)
     return p
 
 
@@ -200,7 +201,7 @@ class FusionPipeline(object):
         return lm
 
     # ------------------------------------------------------------------ the pipeline
-    def run(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=True):
+    def run(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=True, no_fov_cull=False):
         cfg = self.cfg
         V = len(vb.view_sweep)
         H, W = vb.depth.shape[1:3]
@@ -208,7 +209,7 @@ class FusionPipeline(object):
         views = self.build_views(vb)
         if vb.labelmap is None:
             self.pack_masks(vb, views)
-        prm = fusion_params(cfg, H, W, Hm, Wm, image_is_i32=(vb.image.dtype == torch.int32))
+        prm = fusion_params(cfg, H, W, Hm, Wm, image_is_i32=(vb.image.dtype == torch.int32), no_fov_cull=no_fov_cull)
         self.ctx.check(self.lib.dfu_fuse_begin(self.ctx.h, self.ctx.stream, V, _lib.hptr(views), _lib.hptr(prm),
                                                _lib.dptr(vb.lidar), _lib.dptr(vb.depth), _lib.dptr(vb.image),
                                                _lib.dptr(vb.labelmap)))

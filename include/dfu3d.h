@@ -65,7 +65,7 @@ typedef struct dfu_fusion_params {
   double  plane_range[4];    /* x lo, x hi, y lo, y hi (my_loader.py:471: -54, 54, -54, 54) */
   double  min_theta;         /* to_sphere_coords gate, my_loader.py:176 (1.5) */
   int32_t max_per_voxel;     /* my_loader.py:73 (100) */
-  int32_t pad2;
+  int32_t no_fov_cull;       /* 1: the sweep is already FOV-culled by the caller (vis_utils.py:152-154); every row is kept */
 } dfu_fusion_params;
 
 /* Per-instance filter schedule (my_loader.py:581-599; variants my_loader_KittiPandasetWaymo.py:780-823). */
@@ -121,7 +121,8 @@ int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_d
  *   op 2 rect_to_img    in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n] (depth)
  *   op 3 img_to_rect    in0 int64 u[n], in1 int64 v[n], in2 float d[n] -> out0 double [n][3]
  *   op 4 rect_to_lidar  in0 double [n][3]                          -> out0 double [n][3]
- *   op 5 lidar_to_img   in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n] */
+ *   op 5 lidar_to_img   in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n]
+ *   op 6 get_fov_flag   in0 float rect [n][3], in1 int32 {H, W} (device) -> out0 uint8 [n]   (vis_utils.py:108-123) */
 int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0, const void* in1,
                     const void* in2, int64_t n, void* out0, void* out1);
 
@@ -216,6 +217,14 @@ int dfu_nn_gate(dfu_ctx* ctx, void* stream, const double* query_xyz, int64_t nq,
 int dfu_lshape_fit_sync(dfu_ctx* ctx, void* stream, const double* xy /*[n][2]*/, int64_t n, double R0, double Rd,
                         const double* angles_cs_host, int n_angles, int32_t* out_cluster /*dev [n]*/,
                         double* rect_out_host, int64_t capacity, int64_t* n_clusters_host);
+
+/* GenerateAnns (my_loader.py:633-684) on one object's fused points (float64 [n][3]): adaptive-range clustering,
+ * rectangle search and the box arithmetic, one record per cluster in cluster order (fields 4..20 as in
+ * dfu_fuse_instances_sync; field 20 = skipped by the Car aspect rule of :651).  view_host supplies the calibration
+ * for the lidar_to_rect of :679. */
+int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host, const double* points, int64_t n,
+                           int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int n_angles,
+                           double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host);
 
 #ifdef __cplusplus
 }
