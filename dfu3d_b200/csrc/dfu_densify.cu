@@ -19,6 +19,7 @@
 #define NF 1572
 #define NCELL (NT * NF)
 #define KEY_INVALID 0xFFFFFFFFu
+#define S2_EPS 2e-6f   /* rad: twice the error bound of the float32 angle evaluation in s2_key */
 
 struct __align__(32) VoxCell {
   unsigned long long minz;  // orderable bits of the smallest z
@@ -54,7 +55,33 @@ __device__ __forceinline__ unsigned s2_key(const dfu_view& vw, const S2Prm& q, i
   dfu_backproject(vw, col, row, d, X, Y, Z);
   if (!(Z < q.max_z)) return KEY_INVALID;  // new_p[:, 2] < 1.  (:540)
   st |= 2u;
-  // to_sphere_coords (:166-180)
+  // ---- fast path: float32 angles with a proven error bound; the float64 evaluation below is only needed when an
+  // angle lies within S2_EPS of a bin edge (or of the theta gate), i.e. for ~0.4 % of the points.  atan2f(rho, z)
+  // equals acos(z / r) on [0, pi] and is well conditioned everywhere; CUDA's atan2f / atanf are accurate to 3 / 1 ulp,
+  // the float32 inputs carry <= 2 ulp: |error| < 1e-6 rad, half of S2_EPS.
+  {
+    const float Xf = (float)X, Yf = (float)Y, Zf = (float)Z;
+    const float rho = sqrtf(__fmaf_rn(Xf, Xf, Yf * Yf));
+    const float rf = sqrtf(__fmaf_rn(rho, rho, Zf * Zf));
+    const float th = atan2f(rho, Zf);
+    const float fa = atanf(__fdividef(Yf, Xf));
+    const double inv_vs = 1.0 / (double)0.002f;
+    const double tt = ((double)th + 5.0) * inv_vs, tf = ((double)fa + 5.0) * inv_vs;
+    const double ft = tt - floor(tt), ff = tf - floor(tf);
+    const double D = (double)S2_EPS * inv_vs;
+    const bool sure = (rf < 99.0f) && (rf > 1e-3f) && (fabsf(Xf) > 1e-6f) && (fabsf(th - (float)q.min_theta) > S2_EPS) &&
+                      (ft > D) && (ft < 1.0 - D) && (ff > D) && (ff < 1.0 - D);
+    if (sure) {
+      if (!(th > (float)q.min_theta)) return KEY_INVALID;
+      const int it = (int)tt - CT0, jf = (int)tf - CF0;
+      if (it < 0 || it >= NT || jf < 0 || jf >= NF) {
+        st |= 4u;
+        return KEY_INVALID;
+      }
+      return (unsigned)(it * NF + jf);
+    }
+  }
+  // ---- exact path: to_sphere_coords (:166-180) in float64
   double r = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(X, X), __dmul_rn(Y, Y)), __dmul_rn(Z, Z)));
   double theta = acos(__ddiv_rn(Z, r));
   double fan = atan(__ddiv_rn(Y, X));
@@ -89,17 +116,35 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __rest
   const int npix = q.H * q.W;
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
   unsigned st = 0, k = KEY_INVALID;
+  unsigned long long oz = ~0ull, oy = ~0ull;
   if (pix < npix) {
     float d = __ldg(depth + (size_t)v * npix + pix);
     double X, Y, Z;
     k = s2_key(vw, q, pix, d, X, Y, Z, st);
     key[(size_t)v * npix + pix] = k;
-    if (k != KEY_INVALID) {
+    if (k != KEY_INVALID) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
+  }
+  // Neighbouring pixels of a row mostly fall into the same angular voxel (a voxel spans ~2.5 pixels), so each RUN of
+  // equal keys inside the warp is reduced with shuffles and only its first lane touches the table: the L2 atomic
+  // units, not the arithmetic, bound this kernel.
+  {
+    const int lane = threadIdx.x & 31;
+    const unsigned kprev = __shfl_up_sync(0xffffffffu, k, 1);
+    const bool head = (lane == 0) || (k != kprev);
+    const unsigned heads = __ballot_sync(0xffffffffu, head);
+    const unsigned above = heads & ~((2u << lane) - 1u);
+    const int end = above ? (__ffs(above) - 2) : 31;          // last lane of this lane's run
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long z2 = __shfl_down_sync(0xffffffffu, oz, o), y2 = __shfl_down_sync(0xffffffffu, oy, o);
+      if (lane + o <= end) { oz = z2 < oz ? z2 : oz; oy = y2 < oy ? y2 : oy; }
+    }
+    if (head && k != KEY_INVALID) {
       VoxCell* c = table + (size_t)v * NCELL + k;
-      atomicMin(&c->first, (unsigned)pix);
-      atomicAdd(&c->cnt, 1u);
-      atomicMin(&c->minz, dfu_order_f64(Z));
-      atomicMin(&c->miny, dfu_order_f64(Y));
+      atomicMin(&c->first, (unsigned)pix);                    // pixels ascend inside a run: the head is its minimum
+      atomicAdd(&c->cnt, (unsigned)(end - lane + 1));
+      atomicMin(&c->minz, oz);
+      atomicMin(&c->miny, oy);
     }
   }
   int n1 = __syncthreads_count(st & 1u);
@@ -112,11 +157,13 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __rest
   }
 }
 
-// pass B: arg-min resolution + opener count per block
+// pass B: arg-min resolution; per block the number of voxel-opening pixels and their bitmap (one ballot per warp).
+// The voxel ordinal is the rank of the opening pixel in (view, pixel) order = exclusive scan of the block counts + the
+// rank inside the bitmap, so no further pass over the pixels is needed: pass C runs one thread per VOXEL.
 __global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __restrict__ views, S2Prm q,
                                                           const float* __restrict__ depth,
                                                           const unsigned* __restrict__ key, VoxCell* __restrict__ table,
-                                                          int32_t* __restrict__ blkcnt,
+                                                          int32_t* __restrict__ blkcnt, unsigned* __restrict__ blkbits,
                                                           unsigned long long* __restrict__ stats) {
   const int v = blockIdx.y;
   LOAD_VIEW(vw, views, v);
@@ -137,49 +184,65 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __rest
       over = opener && (c->cnt + 1u > (unsigned)q.max_per_voxel);
     }
   }
+  const unsigned bal = __ballot_sync(0xffffffffu, opener);
+  const int b = v * gridDim.x + blockIdx.x;
+  if ((threadIdx.x & 31) == 0) blkbits[(size_t)b * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
   int n = __syncthreads_count(opener);
   int no = __syncthreads_count(over);
   if (threadIdx.x == 0) {
-    blkcnt[v * gridDim.x + blockIdx.x] = n;
+    blkcnt[b] = n;
     if (no) atomicAdd(stats + v * 8 + 3, (unsigned long long)no);
   }
 }
 
-// pass C: ordered scatter of the voxel representatives (voxel ordinal = rank of the opening pixel)
-__global__ void __launch_bounds__(S2_THREADS) k_densify_c(S2Prm q, const unsigned* __restrict__ key,
-                                                          VoxCell* __restrict__ table,
-                                                          const int64_t* __restrict__ blkoff, int32_t* __restrict__ repz,
-                                                          int32_t* __restrict__ repy) {
-  __shared__ int wsum[S2_THREADS / 32];
-  const int v = blockIdx.y;
-  const int npix = q.H * q.W;
-  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  bool opener = false;
-  VoxCell* c = nullptr;
-  if (pix < npix) {
-    unsigned k = key[(size_t)v * npix + pix];
-    if (k != KEY_INVALID) {
-      c = table + (size_t)v * NCELL + k;
-      opener = (*(volatile unsigned*)&c->first == (unsigned)pix);
-    }
+// pass C, one thread per VOXEL: find the opening pixel (block by binary search in the scanned counts, lane by rank in
+// the bitmap), read the representatives out of its cell, put the cell back to all-ones (so that the next batch
+// starts from a clean table without a 41 MB-per-view memset), and gather the min-y representative's xyz + label word
+// for the instance stage.
+__global__ void __launch_bounds__(256) k_vox_finish(const dfu_view* __restrict__ views, S2Prm q, int V, int bpv,
+                                                    const int64_t* __restrict__ voxoff, const int64_t* __restrict__ blkoff,
+                                                    const unsigned* __restrict__ blkbits, const unsigned* __restrict__ key,
+                                                    const float* __restrict__ depth, const uint32_t* __restrict__ labelmap,
+                                                    VoxCell* __restrict__ table, int32_t* __restrict__ repz,
+                                                    int32_t* __restrict__ repy, double* __restrict__ repy_xyz,
+                                                    uint32_t* __restrict__ repy_label, int64_t total) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= total) return;
+  int lo = 0, hi = V;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (voxoff[mid] <= t) lo = mid; else hi = mid;
   }
-  unsigned bal = __ballot_sync(0xffffffffu, opener);
-  if (lane == 0) wsum[w] = __popc(bal);
-  __syncthreads();
-  if (opener) {
-    int base = 0;
-    for (int i = 0; i < w; i++) base += wsum[i];
-    int64_t pos = blkoff[v * gridDim.x + blockIdx.x] + base + dfu_warp_excl(bal, lane);
-    repz[pos] = (int32_t)c->argz;
-    repy[pos] = (int32_t)c->argy;
-    // After this read the cell is dead: its opener puts it back to all-ones, so the next batch starts from a clean
-    // table without a 41 MB-per-view memset (a few % of the cells are ever touched).  Pixels of other blocks that
-    // still test `first` of this cell are non-openers and stay so whether they see the old value or 0xFFFFFFFF.
-    uint4* w4 = reinterpret_cast<uint4*>(c);
-    const uint4 ones = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-    w4[0] = ones; w4[1] = ones;
+  const int v = lo;
+  // last block of the view with blkoff[b] <= t
+  int64_t blo = (int64_t)v * bpv, bhi = blo + bpv;
+  while (bhi - blo > 1) {
+    const int64_t mid = (blo + bhi) >> 1;
+    if (__ldg(blkoff + mid) <= t) blo = mid; else bhi = mid;
   }
+  int r = (int)(t - __ldg(blkoff + blo));
+  const unsigned* bits = blkbits + (size_t)blo * (S2_THREADS / 32);
+  int w = 0;
+  unsigned m = __ldg(bits);
+  while (r >= __popc(m)) { r -= __popc(m); w++; m = __ldg(bits + w); }
+  const int lane = (int)__fns(m, 0, r + 1);
+  const size_t npix = (size_t)q.H * q.W;
+  const int opix = (int)(blo - (int64_t)v * bpv) * S2_THREADS + w * 32 + lane;
+  VoxCell* c = table + (size_t)v * NCELL + __ldg(key + v * npix + opix);
+  const int pz = (int)c->argz, py = (int)c->argy;
+  uint4* w4 = reinterpret_cast<uint4*>(c);
+  const uint4 ones = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+  w4[0] = ones; w4[1] = ones;
+  repz[t] = pz;
+  repy[t] = py;
+  const dfu_view& vw = views[v];
+  const int row = py / q.W, col = py - row * q.W;
+  double X, Y, Z;
+  dfu_backproject(vw, col, row, __ldg(depth + v * npix + py), X, Y, Z);
+  repy_xyz[t] = X;
+  repy_xyz[total + t] = Y;
+  repy_xyz[2 * total + t] = Z;
+  repy_label[t] = labelmap ? __ldg(labelmap + ((size_t)v * q.Hm + row) * q.Wm + col) : 0u;
 }
 
 __global__ void k_vox_view_offsets(const int64_t* __restrict__ blkoff, int V, int bpv, int64_t* out) {
@@ -293,6 +356,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, stats, unsigned long long*, SL_VOXCNT, V * 8 * sizeof(unsigned long long));
   DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, (int64_t)V * bpv * sizeof(int32_t));
   DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, blkbits, unsigned*, SL_VOXCELL, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
   DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
   dim3 grid(bpv, V);
   {
@@ -310,7 +374,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   }
   {
     DFU_PROF(ctx, st, PT_DENSIFY_B);
-    k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, stats);
+    k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, blkbits, stats);
     DFU_LAUNCH_CHECK(ctx);
   }
   {
@@ -348,19 +412,14 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, repy, int32_t*, SL_REPY, cap * sizeof(int32_t));
   DFU_SLOT(ctx, repy_xyz, double*, SL_REPY_XYZ, cap * 3 * sizeof(double));
   DFU_SLOT(ctx, repy_label, uint32_t*, SL_REPY_LABEL, cap * sizeof(uint32_t));
-  {
-    DFU_PROF(ctx, st, PT_DENSIFY_C);
-    k_densify_c<<<grid, S2_THREADS, 0, st>>>(q, key, table, blkoff, repz, repy);
-    DFU_LAUNCH_CHECK(ctx);
-    ctx->table_clean_ptr = (void*)table;
-    ctx->table_clean_bytes = ctx->slot_bytes[SL_TABLE];
-  }
   if (nvox > 0) {
-    DFU_PROF(ctx, st, PT_VOX_GATHER);
-    k_vox_gather<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, voxoff, ctx->depth, ctx->labelmap, repz, repy,
-                                                                 repy_xyz, repy_label, nullptr, nvox);
+    DFU_PROF(ctx, st, PT_DENSIFY_C);
+    k_vox_finish<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, bpv, voxoff, blkoff, blkbits, key, ctx->depth,
+                                                                 ctx->labelmap, table, repz, repy, repy_xyz, repy_label, nvox);
     DFU_LAUNCH_CHECK(ctx);
   }
+  ctx->table_clean_ptr = (void*)table;
+  ctx->table_clean_bytes = ctx->slot_bytes[SL_TABLE];
   ctx->stage |= 4;
   if (total_miss > 0)
     return dfu_set_err(ctx, DFU_ERR_DATA, "%lld points fell outside the angular voxel table", (long long)total_miss);
