@@ -344,33 +344,134 @@ class HostBatch:
         return hb
 
 
-def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True):
-    """The end-to-end call: host buffers in, cloud + boxes back on the host.  Device staging buffers are kept
-    between calls (re-allocated only when a shape grows)."""
-    dev = self.device
-    st = getattr(self, '_stage', None)
-    if st is None:
-        st = self._stage = {}
-    def up(name, h):
-        d = st.get(name)
-        if d is None or d.shape != h.shape or d.dtype != h.dtype:
-            d = st[name] = torch.empty(h.shape, dtype=h.dtype, device=dev)
-        d.copy_(h, non_blocking=True)
-        return d
+def _chunk_metas(hb, nchunk):
+    """Split a HostBatch frame-wise into `nchunk` contiguous groups of sweeps (frames); cached on the HostBatch.
+    Each entry: (meta ViewBatch with chunk-local sweep offsets, lidar row range, view range, instance range)."""
+    cache = hb.__dict__.setdefault('_chunks', {})
+    if nchunk in cache:
+        return cache[nchunk]
     m = hb.meta
-    m.lidar, m.depth, m.image, m.masks = up('lidar', hb.lidar), up('depth', hb.depth), up('image', hb.image), up('masks', hb.masks)
-    m.labelmap = None
-    vb = m
-    res = self.run(vb, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
+    S = len(m.sweeps)
+    nchunk = max(1, min(nchunk, S))
+    bounds = [round(i * S / nchunk) for i in range(nchunk + 1)]
+    vs = np.asarray(m.view_sweep, np.int64)
+    assert np.all(np.diff(vs) >= 0), 'views must be grouped by frame'
+    inst_off = np.concatenate([[0], np.cumsum(np.asarray(m.n_inst, np.int64))])
+    out = []
+    for c in range(nchunk):
+        s0, s1 = bounds[c], bounds[c + 1]
+        v0, v1 = int(np.searchsorted(vs, s0, 'left')), int(np.searchsorted(vs, s1, 'left'))
+        l0 = m.sweeps[s0][0]
+        l1 = m.sweeps[s1 - 1][0] + m.sweeps[s1 - 1][1]
+        meta = ViewBatch(lidar=None, sweeps=[(o - l0, n) for (o, n) in m.sweeps[s0:s1]],
+                         view_sweep=[int(x - s0) for x in vs[v0:v1]], calibs=m.calibs[v0:v1], planes=m.planes[v0:v1],
+                         depth=None, image=None, masks=None, n_inst=m.n_inst[v0:v1], classes=m.classes[v0:v1],
+                         boxes2d=m.boxes2d[v0:v1], thing_classes=m.thing_classes)
+        out.append((meta, (l0, l1), (v0, v1), (int(inst_off[v0]), int(inst_off[v1]))))
+    cache[nchunk] = out
+    return out
+
+
+def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
+    """The end-to-end call: pinned host buffers in, cloud + boxes back on the host.
+
+    The batch is cut frame-wise into `chunks` groups that flow through three streams: host->device copies of group
+    i+1 (copy stream) overlap the kernels of group i (the caller's stream) and the device->host copy of the cloud of
+    group i-1 (second copy stream); PCIe is full duplex, so the call costs about max(transfer, compute) instead of
+    their sum.  Device staging buffers are double-buffered and kept between calls."""
+    dev = self.device
+    st = self.__dict__.setdefault('_stage', {})
+    metas = _chunk_metas(hb, chunks)
+    main = torch.cuda.current_stream(dev)
+    if 's_in' not in st:
+        st['s_in'], st['s_out'] = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    s_in, s_out = st['s_in'], st['s_out']
+    s_in.wait_stream(main)
+    s_out.wait_stream(main)
+
+    def dbuf(name, par, h):
+        key = (name, par)
+        d = st.get(key)
+        if d is None or d.dtype != h.dtype or d.shape[1:] != h.shape[1:] or d.shape[0] < h.shape[0]:
+            d = st[key] = torch.empty((int(h.shape[0] * 1.1) + 1,) + tuple(h.shape[1:]), dtype=h.dtype, device=dev)
+        return d[:h.shape[0]]
+
+    done = {}
+
+    def upload(i):
+        meta, (l0, l1), (v0, v1), (m0, m1) = metas[i]
+        par = i & 1
+        with torch.cuda.stream(s_in):
+            if i - 2 in done:
+                s_in.wait_event(done[i - 2])          # the staging buffers of this parity are free again
+            srcs = (hb.lidar[l0:l1], hb.depth[v0:v1], hb.image[v0:v1], hb.masks[m0:m1])
+            dst = [dbuf(n, par, h) for n, h in zip(('lidar', 'depth', 'image', 'masks'), srcs)]
+            for d, h in zip(dst, srcs):
+                d.copy_(h, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(s_in)
+        return dst, ev
+
     hc = st.get('cloud_host')
-    if hc is None or hc.shape[0] < res.cloud.shape[0] or hc.dtype != res.cloud.dtype:
-        hc = st['cloud_host'] = torch.empty((int(res.cloud.shape[0] * 1.25) + 1024, 8), dtype=res.cloud.dtype, pin_memory=True)
-    out = hc[:res.cloud.shape[0]]
-    out.copy_(res.cloud, non_blocking=True)
-    torch.cuda.current_stream(dev).synchronize()
-    res.cloud_host = out
-    res.d2h_bytes = out.numel() * out.element_size() + (res.boxes.nbytes if res.boxes is not None else 0)
-    return res
+    results, pending = [], upload(0)
+    row_base, rows_needed, d2h_ev = 0, 0, []
+    for i in range(len(metas)):
+        dst, ev = pending
+        pending = upload(i + 1) if i + 1 < len(metas) else None
+        meta = metas[i][0]
+        main.wait_event(ev)
+        meta.lidar, meta.depth, meta.image, meta.masks = dst
+        meta.labelmap = None
+        res = self.run(meta, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
+        e = torch.cuda.Event()
+        e.record(main)
+        done[i] = e
+        n = int(res.cloud.shape[0])
+        if hc is None or hc.dtype != res.cloud.dtype or hc.shape[0] < row_base + n:
+            # first call (or a larger batch than ever seen): grow the pinned output, keeping what is already there
+            for x in d2h_ev:
+                x.synchronize()
+            est = int((row_base + n) * max(1.0, len(metas) / float(i + 1)) * 1.25) + 1024
+            new = torch.empty((est, 8), dtype=res.cloud.dtype, pin_memory=True)
+            if hc is not None and row_base and hc.dtype == new.dtype:
+                new[:row_base].copy_(hc[:row_base])
+            hc = st['cloud_host'] = new
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(e)
+            hc[row_base:row_base + n].copy_(res.cloud, non_blocking=True)
+            res.cloud.record_stream(s_out)
+            x = torch.cuda.Event()
+            x.record(s_out)
+            d2h_ev.append(x)
+        results.append((res, row_base))
+        row_base += n
+    s_out.synchronize()
+    main.synchronize()
+    # ---- merge the per-group results into one FusionResult (views, instances and rows renumbered batch-wide)
+    row_off = [np.zeros(1, np.int64)]
+    boxes, segc, b2d, lines = [], [], [], []
+    for (res, base), (meta, _, (v0, v1), (m0, m1)) in zip(results, metas):
+        row_off.append(res.row_off[1:] + base)
+        if res.boxes is not None and res.boxes.shape[0]:
+            bx = res.boxes.copy()
+            bx[:, 0] += v0
+            bx[:, 1] += m0
+            boxes.append(bx)
+            b2d.append(res.box2d)
+        if res.seg_counts is not None:
+            segc.append(res.seg_counts)
+        if res.label_lines is not None:
+            lines += res.label_lines
+    out = FusionResult(cloud=None, row_off=np.concatenate(row_off),
+                       counts_project=np.concatenate([r.counts_project for r, _ in results], 0),
+                       counts_densify=np.concatenate([r.counts_densify for r, _ in results], 0))
+    out.boxes = np.concatenate(boxes, 0) if boxes else np.zeros((0, _lib.BOX_DOUBLES))
+    out.box2d = np.concatenate(b2d, 0) if b2d else np.zeros((0, 4), np.float32)
+    out.seg_counts = np.concatenate(segc, 0) if segc else None
+    out.label_lines = lines if want_lines else None
+    out.cloud_host = hc[:row_base]
+    out.d2h_bytes = out.cloud_host.numel() * out.cloud_host.element_size() + out.boxes.nbytes
+    return out
 
 
 def _batch_stats(self, vb, res):

@@ -152,3 +152,23 @@ def test_lshape_fit_matches_oracle(seed, n):
         np.testing.assert_allclose(rect[k, 4:8], b, atol=1e-12)
         np.testing.assert_allclose(rect[k, 8:12], c, atol=1e-9)
         assert abs(rect[k, 12] - th) < 1e-9 and int(rect[k, 15]) == int(sel.sum())
+
+
+@pytest.mark.parametrize('chunks', [1, 2, 3])
+def test_run_host_pipelined_equals_resident(chunks):
+    """The end-to-end call (pinned host buffers in, frame groups pipelined over three streams, cloud + boxes back on
+    the host) returns exactly what the device-resident call returns."""
+    frs = [helpers.small_frame(s, 'nuscenes', scale=0.25, n_cams=2) for s in (3, 4, 5)]
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames(frs, pipe.device)
+    ref = pipe.run(vb, cloud_dtype=torch.float16)
+    ref_cloud = ref.cloud.cpu().numpy()
+    hb = pipeline.HostBatch.from_device(vb)
+    for _ in range(2):                      # second call re-uses the staging buffers
+        res = pipe.run_host(hb, cloud_dtype=torch.float16, chunks=chunks)
+        assert np.array_equal(res.cloud_host.numpy(), ref_cloud)
+        assert np.array_equal(res.row_off, ref.row_off)
+        assert np.array_equal(res.boxes, ref.boxes)
+        assert np.array_equal(res.seg_counts, ref.seg_counts)
+        assert res.label_lines == ref.label_lines
+        assert res.d2h_bytes == ref_cloud.nbytes + ref.boxes.nbytes
