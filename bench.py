@@ -51,9 +51,10 @@ def parse():
                     help='distinct synthetic frames generated per rank (tiled to --frames)')
     ap.add_argument('--max-inst', type=int, default=8)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--cpu-sample-views', type=int, default=1)
+    ap.add_argument('--cpu-sample-views', type=int, default=0, help='views of the CPU sample (0 = 24 for the baseline leg, 1 per worker for --impl reference)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-filters', action='store_true')
     return ap.parse_args()
 
 
@@ -131,46 +132,51 @@ def _cpu_view_worker(job):
     return time.perf_counter() - t0, len(out[2])
 
 
-def cpu_baseline(a, n_views, procs):
-    """Times the oracle port on whole views; returns (frames/s, seconds of CPU wall, sample text)."""
-    jobs = [(910000 + i // a.cams, a.cams, a.sweeps, i % a.cams, a.max_inst) for i in range(n_views)]
-    t0 = time.perf_counter()
-    if procs <= 1:
-        res = [_cpu_view_worker(j) for j in jobs]
-        wall = sum(r[0] for r in res)
-    else:
-        import multiprocessing as mp
-        with mp.get_context('spawn').Pool(procs) as pool:
-            t0 = time.perf_counter()
-            res = pool.map(_cpu_view_worker, jobs, chunksize=1)
-            wall = time.perf_counter() - t0
-    fps = (n_views / float(a.cams)) / wall
-    return fps, wall, '%d view(s) of %d-cam %d-sweep nuScenes-shaped frames, compute only (inputs generated outside the timed part)' % (
-        n_views, a.cams, a.sweeps)
+def cpu_baseline(a, max_views, budget_s=15.0):
+    """Times the oracle port on whole views on ONE host core until `budget_s` seconds of CPU work are spent (at least
+    one view, at most `max_views`): a bounded sample, so that the default run ends within minutes.  A full-resolution
+    view costs 0.5 - 30 s depending on how many points its instances hold (the reference's clustering is quadratic).
+    Returns (frames/s, seconds, sample text)."""
+    wall, n = 0.0, 0
+    while n < max_views and (n == 0 or wall < budget_s):
+        job = (910000 + n // a.cams, a.cams, a.sweeps, n % a.cams, a.max_inst)
+        wall += _cpu_view_worker(job)[0]
+        n += 1
+    fps = (n / float(a.cams)) / wall
+    return fps, wall, ('%d view(s) of %d-cam %d-sweep nuScenes-shaped frames on 1 core (sample bounded at ~%.0f s of CPU '
+                       'work), compute only: inputs generated outside the timed part' % (n, a.cams, a.sweeps, budget_s))
 
 
 def run_reference(a):
+    """--impl reference: the reference path's CPU implementation (oracle port, see the module docstring) on all host
+    cores, one whole view per worker process; a step = one bounded sample of `procs * views_per_proc` views."""
     rank = int(os.environ.get('RANK', 0))
     if rank != 0:
         return
+    import multiprocessing as mp
     cores = os.cpu_count() or 1
-    procs = max(1, min(cores, 32))
-    per_step = max(procs, a.cpu_sample_views)
-    # warmup: imports + one view
-    for _ in range(min(a.warmup, 1)):
-        cpu_baseline(a, 1, 1)
-    times, views = [], 0
-    for s in range(a.steps):
-        fps, wall, sample = cpu_baseline(a, per_step, procs)
-        times.append(wall)
-        views += per_step
+    procs = max(1, min(cores, 64))
+    per_step = procs * max(1, a.cpu_sample_views)
+    times = []
+    with mp.get_context('spawn').Pool(procs) as pool:
+        def step(k):
+            jobs = [(910000 + (k * per_step + i) // a.cams, a.cams, a.sweeps, (k * per_step + i) % a.cams, a.max_inst)
+                    for i in range(per_step)]
+            res = pool.map(_cpu_view_worker, jobs, chunksize=1)
+            # wall time of the parallel step = the busiest worker's share: total compute seconds / workers
+            return sum(r[0] for r in res) / float(procs)
+        for w in range(1):                  # ONE warm-up step whatever --warmup says: a CPU step costs ~20 s
+            step(1000 + w)                  # imports + first-touch in every worker
+        for k in range(a.steps):
+            times.append(step(k))
     tot = sum(times)
-    value = (views / float(a.cams)) / tot
+    value = (per_step * a.steps / float(a.cams)) / tot
+    sample = ('%d views per step (%d worker processes x %d), %d-cam %d-sweep nuScenes-shaped frames, one whole view per '
+              'worker, inputs generated outside the timed part; step time = summed compute seconds / workers' % (per_step, procs, max(1, a.cpu_sample_views), a.cams, a.sweeps))
     line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup,
             'ms_per_step': 1000.0 * tot / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic', 'impl': 'reference', 'config': workload_config(a),
-            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': procs, 'kind': 'port',
-                             'sample': '%d views per step (%s), one whole view per worker process' % (per_step, sample)},
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': procs, 'kind': 'port', 'sample': sample},
             'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line))
@@ -204,6 +210,43 @@ def algorithmic_bytes(tag, st):
     if tag == 'gate':
         return 13 * st.get('inst_points', 0)
     return None
+
+
+def filters_leg(pipe, dev, peak, iters=3):
+    """BASELINE.json configs[2]: one nuScenes-shaped frame, 6 x 1600x900 full-resolution densification (height gate
+    off) through the radius filter (r = 0.2 m, nb_points = 1) and SOR (k = 20, 2 sigma); per-kernel CUDA-event times
+    (dfu_profile_*) against the algorithmic bytes of SURVEY.md 8(d): grid build 28 B/pt, radius 13 B/pt, SOR 29 B/pt."""
+    import torch
+    from dfu3d_b200 import synth, ops
+    fr = synth.make_frame(3000, 'nuscenes', n_cams=6, sweeps=1, device=dev)
+    depth = torch.stack([v['depth'] for v in fr['views']])
+    calibs = [(v['P2'], v['R0'], v['V2C']) for v in fr['views']]
+    xyz, _, counts = ops.backproject(depth, calibs, ctx=pipe.ctx)
+    n = int(xyz.shape[0])
+    out = {'workload': 'configs[2]: 6 x 1600x900 depth maps -> %d back-projected points; radius (r=0.2, nb=1); SOR (k=20, 2.0)' % n,
+           'points': n}
+    for name, fn, tags, bpp in (('radius', lambda: ops.radius_filter(xyz, 1, 0.2, ctx=pipe.ctx), ('grid_build', 'radius'), (28, 13)),
+                                ('sor', lambda: ops.sor_filter(xyz, 20, 2.0, ctx=pipe.ctx), ('grid_build', 'sor_knn', 'sor_mask'), (28, 21, 8))):
+        keep = fn()
+        torch.cuda.synchronize()
+        pipe.ctx.profile(True)
+        pipe.ctx.profile_read(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            keep = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        prof = pipe.ctx.profile_read(reset=True)
+        pipe.ctx.profile(False)
+        leg = {'ms': e0.elapsed_time(e1) / iters, 'kept_fraction': float(keep.float().mean()), 'kernels': {}}
+        for tag, b in zip(tags, bpp):
+            if tag in prof:
+                ms = prof[tag][0] / iters
+                gbs = n * b / 1e9 / (ms / 1e3)
+                leg['kernels'][tag] = {'ms': ms, 'algorithmic_bytes': n * b, 'achieved_gbs': gbs, 'frac_of_peak': gbs / peak}
+        out[name] = leg
+    return out
 
 
 def main():
@@ -309,15 +352,26 @@ def main():
             roof = {'bound': 'hbm', 'kernel': top, 'achieved': k['achieved_gbs'], 'peak': peak, 'unit': 'GB/s',
                     'frac': k['achieved_gbs'] / peak, 'traffic': None, 'peak_source': peak_src,
                     'share_of_step': k['ms_per_step'] / (ms_prof / a.steps)}
+        if roof is not None:
+            try:      # dram bytes of one launch from the committed `ncu --set full` capture of the same command
+                tr = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(roof['kernel'])
+                if tr and tr.get('frames') == a.frames and tr.get('cams') == a.cams:
+                    roof['traffic'] = tr['dram_bytes_per_launch']
+                    roof['traffic_source'] = tr.get('source')
+            except Exception:
+                pass
+        filt = None
+        if world == 1 and not a.no_filters:
+            filt = filters_leg(pipe, dev, peak)
         cpu = None
         if world == 1 and not a.no_cpu_baseline:
-            fps, wall, sample = cpu_baseline(a, a.cpu_sample_views, 1)
+            fps, wall, sample = cpu_baseline(a, a.cpu_sample_views or 24)
             cpu = {'value': fps, 'unit': UNIT, 'cores': 1, 'kind': 'port', 'sample': sample, 'seconds': wall}
         line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': a.steps, 'warmup': a.warmup,
                 'ms_per_step': ms / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
                 'dtype': 'f64', 'data': 'synthetic', 'config': workload_config(a), 'e2e': e2e,
                 'gpu_launches': int(launches), 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
-                'kernels': kernels, 'batch': st}
+                'kernels': kernels, 'batch': st, 'filters': filt}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -112,13 +112,14 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __rest
                                                           VoxCell* __restrict__ table,
                                                           unsigned long long* __restrict__ stats) {
   const int v = blockIdx.y;
-  LOAD_VIEW(vw, views, v);
   const int npix = q.H * q.W;
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  // the depth load is issued before the view constants are staged: its latency hides behind that barrier
+  const float d = (pix < npix) ? __ldg(depth + (size_t)v * npix + pix) : 0.0f;
+  LOAD_VIEW(vw, views, v);
   unsigned st = 0, k = KEY_INVALID;
   unsigned long long oz = ~0ull, oy = ~0ull;
   if (pix < npix) {
-    float d = __ldg(depth + (size_t)v * npix + pix);
     double X, Y, Z;
     k = s2_key(vw, q, pix, d, X, Y, Z, st);
     key[(size_t)v * npix + pix] = k;
@@ -134,8 +135,8 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __rest
     const unsigned heads = __ballot_sync(0xffffffffu, head);
     const unsigned above = heads & ~((2u << lane) - 1u);
     const int end = above ? (__ffs(above) - 2) : 31;          // last lane of this lane's run
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
+    // runs are short (a voxel spans ~2.5 pixels): stop as soon as no lane has a partner left
+    for (int o = 1; o < 32 && __any_sync(0xffffffffu, lane + o <= end && k != KEY_INVALID); o <<= 1) {
       const unsigned long long z2 = __shfl_down_sync(0xffffffffu, oz, o), y2 = __shfl_down_sync(0xffffffffu, oy, o);
       if (lane + o <= end) { oz = z2 < oz ? z2 : oz; oy = y2 < oy ? y2 : oy; }
     }
@@ -166,15 +167,16 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __rest
                                                           int32_t* __restrict__ blkcnt, unsigned* __restrict__ blkbits,
                                                           unsigned long long* __restrict__ stats) {
   const int v = blockIdx.y;
-  LOAD_VIEW(vw, views, v);
   const int npix = q.H * q.W;
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
+  const unsigned k0 = (pix < npix) ? __ldg(key + (size_t)v * npix + pix) : KEY_INVALID;
+  const float d = (k0 != KEY_INVALID) ? __ldg(depth + (size_t)v * npix + pix) : 0.0f;
+  LOAD_VIEW(vw, views, v);
   bool opener = false, over = false;
   if (pix < npix) {
-    unsigned k = key[(size_t)v * npix + pix];
+    unsigned k = k0;
     if (k != KEY_INVALID) {
       VoxCell* c = table + (size_t)v * NCELL + k;
-      float d = __ldg(depth + (size_t)v * npix + pix);
       const int row = pix / q.W, col = pix - row * q.W;
       double X, Y, Z;
       dfu_backproject(vw, col, row, d, X, Y, Z);

@@ -198,7 +198,25 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_count(DfuGrid g, const Seg
   const int s = (int)(k >> 48);
   const SegPrm p = prm[s];
   const double r2 = __dmul_rn(p.r, p.r);
-  const bool kp = grid_walk<0>(g, *g.ncell, s, g.sx[t], g.sy[t], g.sz[t], r2, p.nb);
+  const double px = g.sx[t], py = g.sy[t], pz = g.sz[t];
+  // Fast accept: the sorted array puts points of the same / adjacent cells next to each other, so in a dense cloud
+  // the nb + 1 points needed are almost always among the few entries around t (coalesced loads, no cell look-up).
+  // Only a "keep" can be decided here; everything else takes the exact walk below, which counts from scratch.
+  {
+    int count = 1;   // the point itself (d2 = 0 < r2)
+    for (int o = 1; o <= 4 && count <= p.nb; o++) {
+#pragma unroll
+      for (int sgn = -1; sgn <= 1; sgn += 2) {
+        const int64_t u = t + sgn * o;
+        if (u < 0 || u >= g.n) continue;
+        if ((g.skey[u] >> 48) != (unsigned long long)s) continue;     // other segment or inactive (~0)
+        const double ax = __dsub_rn(g.sx[u], px), ay = __dsub_rn(g.sy[u], py), az = __dsub_rn(g.sz[u], pz);
+        if (__dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)) < r2) count++;
+      }
+    }
+    if (count > p.nb) { keep[g.sidx[t]] = 1; return; }
+  }
+  const bool kp = grid_walk<0>(g, *g.ncell, s, px, py, pz, r2, p.nb);
   keep[g.sidx[t]] = kp ? 1 : 0;
 }
 
