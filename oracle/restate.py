@@ -217,28 +217,47 @@ def cluster_adaptive(ox, oy, R0=3.0, Rd=0.001):
     uniq, cfirst, cinv = np.unique(ckey, return_index=True, return_inverse=True)
     # every point is within R0 of all points of its own cell (cell diagonal < R0) -> star edges
     rows = [np.arange(n)]; cols = [cfirst[cinv]]
-    # one representative test per pair of nearby cells is NOT enough (need "exists a pair"), so
-    # enumerate candidate pairs between different cells through the KD-tree, cell pair by cell pair
-    tree = cKDTree(P)
-    pairs = tree.query_pairs(rmax * (1 + 1e-12) + 1e-12, output_type='ndarray') if n <= 6000 else None
-    if pairs is not None:
+    # one representative test per pair of nearby cells is NOT enough (need "exists a pair")
+    if n <= 3000:
+        tree = cKDTree(P)
+        pairs = tree.query_pairs(rmax * (1 + 1e-12) + 1e-12, output_type='ndarray')
         i, j = pairs[:, 0], pairs[:, 1]
         d = np.sqrt((ox[i] - ox[j]) ** 2 + (oy[i] - oy[j]) ** 2)
         okp = (d <= R[i]) | (d <= R[j])
         rows.append(i[okp]); cols.append(j[okp])
     else:
-        # large inputs: only cross-cell candidates, processed in chunks of query points
-        for s in range(0, n, 2048):
-            idx = np.arange(s, min(n, s + 2048))
-            nb = tree.query_ball_point(P[idx], rmax * (1 + 1e-12) + 1e-12)
-            for a, lst in zip(idx, nb):
-                lst = np.asarray(lst, np.int64)
-                lst = lst[cinv[lst] != cinv[a]]
-                if lst.size == 0:
-                    continue
-                d = np.sqrt((ox[a] - ox[lst]) ** 2 + (oy[a] - oy[lst]) ** 2)
-                okp = (d <= R[a]) | (d <= R[lst])
-                rows.append(np.full(int(okp.sum()), a)); cols.append(lst[okp])
+        # large inputs: cell pair by cell pair, "does ANY pair connect the two cells" with early exit, skipping cell
+        # pairs that are already in one component (same graph, far fewer distance evaluations than all pairs)
+        order = np.argsort(cinv, kind='stable')
+        cstart = np.r_[0, np.cumsum(np.bincount(cinv, minlength=uniq.size))]
+        ccoord = cell[cfirst]
+        parent = np.arange(uniq.size)
+
+        def find(a):
+            while parent[a] != a:
+                parent[a] = parent[parent[a]]
+                a = parent[a]
+            return a
+        reach = int(np.ceil(rmax / side)) + 1
+        ctree = cKDTree(ccoord.astype(np.float64))
+        for ca, cb in ctree.query_pairs(reach * np.sqrt(2.0) + 1e-9, output_type='ndarray'):
+            ra, rb = find(ca), find(cb)
+            if ra == rb:
+                continue
+            ia = order[cstart[ca]:cstart[ca + 1]]
+            ib = order[cstart[cb]:cstart[cb + 1]]
+            hit = None
+            for s0 in range(0, ia.size, 256):
+                a_ = ia[s0:s0 + 256]
+                d = np.sqrt((ox[a_][:, None] - ox[ib][None, :]) ** 2 + (oy[a_][:, None] - oy[ib][None, :]) ** 2)
+                okp = (d <= R[a_][:, None]) | (d <= R[ib][None, :])
+                if okp.any():
+                    u, w = np.argwhere(okp)[0]
+                    hit = (a_[u], ib[w])
+                    break
+            if hit is not None:
+                parent[ra] = rb
+                rows.append(np.array([hit[0]])); cols.append(np.array([hit[1]]))
     rr = np.concatenate(rows); cc = np.concatenate(cols)
     g = coo_matrix((np.ones(rr.size, np.int8), (rr, cc)), shape=(n, n))
     nc, lab = connected_components(g, directed=False)
