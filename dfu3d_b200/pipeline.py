@@ -37,6 +37,19 @@ class FusionConfig:
     cluster_Rd: float = 0.001              # rectangle_fitting.py:37
     label_names: list = field(default_factory=lambda: list(NUSC_NAMES))
     allow_voxel_overflow: bool = False
+    instances: bool = True                 # False: the per-instance / GenerateAnns stage is not run
+
+    @staticmethod
+    def preset(name):
+        """Literal sets of the reference's loader variants (SURVEY.md 8(a) "Variants").
+        'nuscenes' = my_loader.py (what vis_utils.py:14 imports); 'kitti' = my_loader_KittiPandasetWaymo.py: pixel
+        bounds 1216x352 (:709), plane gate range x, y in (-30, 80) (:470); its GenerateAnns call is commented out
+        (:831), so the preset stops after the fused cloud."""
+        if name == 'nuscenes':
+            return FusionConfig()
+        if name == 'kitti':
+            return FusionConfig(bounds=(1216, 352), plane_range=(-30.0, 80.0, -30.0, 80.0), instances=False)
+        raise KeyError(name)
 
     def instance_schedule(self, cls_name):
         """Per-class filter schedule of my_loader.py:581-599.
@@ -223,7 +236,7 @@ class FusionPipeline(object):
         cloud = torch.empty((int(row_off[-1]), 8), dtype=cloud_dtype, device=self.device)
         self.ctx.check(self.lib.dfu_fuse_emit_cloud(self.ctx.h, _lib.dptr(cloud), dt, cloud.shape[0], _lib.hptr(row_off)))
         res = FusionResult(cloud=cloud, row_off=row_off, counts_project=cp, counts_densify=cd)
-        if instances:
+        if instances and cfg.instances:
             self.run_instances(vb, res, want_lines=want_lines)
         return res
 

@@ -389,8 +389,14 @@ def ball_gate(pseudo, lidar, C=0.1):
     return keep
 
 
+PRESETS = {   # SURVEY.md 8(a) "Variants": literals of my_loader.py vs my_loader_KittiPandasetWaymo.py
+    'nuscenes': dict(bounds=(1600, 900), only_range=((-54, 54), (-54, 54)), instances=True),       # my_loader.py:471,526
+    'kitti': dict(bounds=(1216, 352), only_range=((-30, 80), (-30, 80)), instances=False),         # ..Waymo.py:470,709; GenerateAnns call commented out (:831)
+}
+
+
 def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes, boxes2d, plane,
-                      bounds=(1600, 900), return_debug=False):
+                      bounds=(1600, 900), return_debug=False, only_range=((-54, 54), (-54, 54)), instances=True):
     """Restatement of my_loader.py:502-617 (nuScenes preset).  ``lidar`` is already FOV culled
     (vis_utils.py:152-154); ``plane`` replaces the unseeded RANSAC of :511 (Q8).  Returns
     (all_points [N+M',8] float64, label lines, records, debug dict)."""
@@ -398,7 +404,7 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
     masks = np.asarray(masks)
     n_inst = masks.shape[0]
     rows, cols, p_lidar = backproject(depth, calib)
-    lidar_mask = lidar[above_plane(lidar[:, :3], plane)]
+    lidar_mask = lidar[above_plane(lidar[:, :3], plane, only_range=only_range)]
     lidar_mask, lab, px, py, inb = inherit_labels(lidar_mask, calib, masks, bounds)
     M = rows.shape[0]
     new_p = np.zeros((M, 8))
@@ -413,7 +419,7 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
     lines, recs = [], []
     dbg = dict(pix0=pix0, rep_z_pix=pix0[rep_z], rep_y_pix=pix0[rep_y], overflow=overflow, inst=[],
                lidar_mask=lidar_mask, lab=lab, px=px, py=py, inb=inb)
-    for i in range(n_inst):
+    for i in range(n_inst if instances else 0):
         cls_name = thing_classes[int(classes[i])]
         mrow = masks[i][rows, cols][low]
         P = new_p0[rep_y][mrow[rep_y] > 0][:, :3]
@@ -442,7 +448,7 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
     return all_points, lines, recs
 
 
-def run_view(inp, plane=None, return_debug=False):
+def run_view(inp, plane=None, return_debug=False, preset='nuscenes'):
     """vis_utils.save_depth_as_points (vis_utils.py:142-166) minus file I/O, on the dict layout of
     dfu3d_b200.synth.view_as_reference_inputs."""
     calib = Calib(inp['P2'], inp['R0'], inp['V2C'])
@@ -454,5 +460,5 @@ def run_view(inp, plane=None, return_debug=False):
     depth = np.array(inp['depth'], np.float32).reshape(H, W, 1)
     pl = inp['plane'] if plane is None else plane
     out = depth2pointsrgbpm(depth, image, calib, lidar, inp['thing_classes'], inp['masks'], inp['classes'],
-                            inp['boxes2d'], pl, return_debug=return_debug)
+                            inp['boxes2d'], pl, return_debug=return_debug, **PRESETS[preset])
     return (fov,) + tuple(out)

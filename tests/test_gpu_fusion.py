@@ -53,3 +53,31 @@ def test_project_and_densify_match_oracle(seed, shape, scale):
     # coordinates: 1e-5 relative (north star); colours / flags exact
     np.testing.assert_allclose(cloud[nF:, :3], allp[nF:, :3], rtol=1e-5, atol=1e-9)
     assert np.array_equal(cloud[nF:, 3:], allp[nF:, 3:])
+
+
+def test_kitti_preset_matches_oracle():
+    """The 'kitti' literal set (my_loader_KittiPandasetWaymo.py:470,709): plane-gate range (-30, 80)^2, pixel bounds
+    1216x352, no GenerateAnns; a sweep that reaches beyond x = 54 m and behind x = -30 m makes the ranges matter."""
+    fr = helpers.small_frame(12, 'kitti', scale=0.5)
+    inp = synth.view_as_reference_inputs(fr, 0)
+    from oracle import restate
+    fov, allp, lines, recs, dbg = restate.run_view(inp, return_debug=True, preset='kitti')
+    fov_n, allp_n, _, _ = restate.run_view(inp, preset='nuscenes')
+    pipe = pipeline.FusionPipeline(0, config=pipeline.FusionConfig.preset('kitti'))
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, cloud_dtype=torch.float64)
+    assert res.boxes is None and lines == []
+    N = fr['lidar'].shape[0]
+    pix, flags, label = helpers.emit_project(pipe, N)
+    lid_fov = inp['lidar'][fov]
+    above = restate.above_plane(lid_fov[:, :3], inp['plane'], only_range=((-30, 80), (-30, 80)))
+    assert np.array_equal(((flags[fov] & 2) != 0), above)
+    assert not np.array_equal(above, restate.above_plane(lid_fov[:, :3], inp['plane'])), 'ranges must differ on this sweep'
+    sel = np.nonzero(fov)[0][above]
+    assert np.array_equal((flags[sel] & 4) != 0, dbg['inb'])
+    cloud = res.cloud.cpu().numpy()
+    assert cloud.shape == allp.shape
+    nF = int(fov.sum())
+    assert np.array_equal(cloud[:nF], allp[:nF])
+    np.testing.assert_allclose(cloud[nF:, :3], allp[nF:, :3], rtol=1e-5, atol=1e-9)
+    assert np.array_equal(cloud[nF:, 3:], allp[nF:, 3:])
