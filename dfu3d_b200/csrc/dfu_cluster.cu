@@ -245,56 +245,84 @@ __device__ __forceinline__ void fit_project(double x, double y, double cs, doubl
   c2 = __dadd_rn(__dmul_rn(x, -sn), __dmul_rn(y, cs));     // X @ [-sin, cos]   (:125)
 }
 
-// one warp per (cluster, angle): variance criterion (rectangle_fitting.py:83-111), np.var = mean((d - mean(d))^2)
+// Reductions over a GROUP of G threads (G = 32: one warp, shuffles only; G = 256: one block, shuffles + shared memory).
+// Clusters of a few hundred points get a warp per (cluster, angle); the few clusters with more than FIT_BIG points
+// get a block, so that the kernel's duration is not the serial walk of one warp through the largest cluster.
+#define FIT_BIG 2048
+template <int G, int OP> __device__ __forceinline__ double group_reduce(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double w = __shfl_xor_sync(0xffffffffu, v, o);
+    v = OP == 0 ? fmin(v, w) : (OP == 1 ? fmax(v, w) : v + w);
+  }
+  if (G == 32) return v;
+  __shared__ double sh[8];
+  __syncthreads();                       // previous use of sh is over
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double r = sh[0];
+#pragma unroll
+  for (int i = 1; i < 8; i++) r = OP == 0 ? fmin(r, sh[i]) : (OP == 1 ? fmax(r, sh[i]) : r + sh[i]);
+  return r;
+}
+
+// one group per (cluster, angle): variance criterion (rectangle_fitting.py:83-111), np.var = mean((d - mean(d))^2)
+template <int G>
 __global__ void __launch_bounds__(256) k_fit_cost(const double* __restrict__ cx, const double* __restrict__ cy,
                                                   const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
                                                   int na, double* __restrict__ cost) {
-  const long long w = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+  const long long w = ((long long)blockIdx.x * 256 + threadIdx.x) / G;
+  const int lane = threadIdx.x % G;
   if (w >= (long long)K * na) return;
   const int k = (int)(w / na), a = (int)(w % na);
-  const double cs = angles[2 * a], sn = angles[2 * a + 1];
   const int p0 = coff[k], p1 = coff[k + 1];
+  if ((G == 32) != (p1 - p0 <= FIT_BIG)) return;        // uniform per group (and per block when G = 256)
+  const double cs = angles[2 * a], sn = angles[2 * a + 1];
   double mn1 = INFINITY, mx1 = -INFINITY, mn2 = INFINITY, mx2 = -INFINITY;
-  for (int p = p0 + lane; p < p1; p += 32) {
+  for (int p = p0 + lane; p < p1; p += G) {
     double c1, c2;
     fit_project(cx[p], cy[p], cs, sn, c1, c2);
     mn1 = fmin(mn1, c1); mx1 = fmax(mx1, c1); mn2 = fmin(mn2, c2); mx2 = fmax(mx2, c2);
   }
-  mn1 = warp_min(mn1); mx1 = warp_max(mx1); mn2 = warp_min(mn2); mx2 = warp_max(mx2);
+  mn1 = group_reduce<G, 0>(mn1); mx1 = group_reduce<G, 1>(mx1); mn2 = group_reduce<G, 0>(mn2); mx2 = group_reduce<G, 1>(mx2);
   double s1 = 0, s2 = 0, n1 = 0, n2 = 0;
-  for (int p = p0 + lane; p < p1; p += 32) {
+  for (int p = p0 + lane; p < p1; p += G) {
     double c1, c2;
     fit_project(cx[p], cy[p], cs, sn, c1, c2);
     const double D1 = fmin(fabs(mx1 - c1), fabs(c1 - mn1)), D2 = fmin(fabs(mx2 - c2), fabs(c2 - mn2));
     if (D1 < D2) { s1 += D1; n1 += 1; } else { s2 += D2; n2 += 1; }
   }
-  s1 = warp_sum(s1); s2 = warp_sum(s2); n1 = warp_sum(n1); n2 = warp_sum(n2);
+  s1 = group_reduce<G, 2>(s1); s2 = group_reduce<G, 2>(s2); n1 = group_reduce<G, 2>(n1); n2 = group_reduce<G, 2>(n2);
   const double m1 = n1 > 0 ? s1 / n1 : 0.0, m2 = n2 > 0 ? s2 / n2 : 0.0;
   double q1 = 0, q2 = 0;
-  for (int p = p0 + lane; p < p1; p += 32) {
+  for (int p = p0 + lane; p < p1; p += G) {
     double c1, c2;
     fit_project(cx[p], cy[p], cs, sn, c1, c2);
     const double D1 = fmin(fabs(mx1 - c1), fabs(c1 - mn1)), D2 = fmin(fabs(mx2 - c2), fabs(c2 - mn2));
     if (D1 < D2) { const double e = D1 - m1; q1 += e * e; } else { const double e = D2 - m2; q2 += e * e; }
   }
-  q1 = warp_sum(q1); q2 = warp_sum(q2);
+  q1 = group_reduce<G, 2>(q1); q2 = group_reduce<G, 2>(q2);
   if (lane == 0) {
     const double V1 = n1 > 0 ? -(q1 / n1) : 0.0, V2 = n2 > 0 ? -(q2 / n2) : 0.0;
     cost[(long long)k * na + a] = V1 + V2;
   }
 }
 
-// one warp per cluster: first maximum (rectangle_fitting.py:135-136), runner-up, rectangle at the best angle (:138-157)
+// one group per cluster: first maximum (rectangle_fitting.py:135-136), runner-up, rectangle at the best angle (:138-157)
+template <int G>
 __global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ cx, const double* __restrict__ cy,
                                                     const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
                                                     int na, const double* __restrict__ cost, double* __restrict__ rect) {
-  const int k = (int)(((long long)blockIdx.x * 256 + threadIdx.x) >> 5);
-  const int lane = threadIdx.x & 31;
+  const int k = (int)(((long long)blockIdx.x * 256 + threadIdx.x) / G);
+  const int lane = threadIdx.x % G;
   if (k >= K) return;
+  const int p0 = coff[k], p1 = coff[k + 1];
+  if ((G == 32) != (p1 - p0 <= FIT_BIG)) return;
+  // every warp of the group scans the (<= 96) costs redundantly: identical result in each, no cross-warp exchange
+  const int wl = threadIdx.x & 31;
   double best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int a = lane; a < na; a += 32) {
+  for (int a = wl; a < na; a += 32) {
     const double c = cost[(long long)k * na + a];
     if (c > best) { best = c; bi = a; }      // ascending a per lane: keeps the first maximum of the lane
   }
@@ -305,19 +333,18 @@ __global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ c
     if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
   }
   double run = -INFINITY;
-  for (int a = lane; a < na; a += 32)
+  for (int a = wl; a < na; a += 32)
     if (a != bi) run = fmax(run, cost[(long long)k * na + a]);
   run = warp_max(run);
   if (bi == 0x7fffffff) bi = 0;               // all costs NaN: the reference keeps theta = None; flagged by best = -inf
   const double cs = angles[2 * bi], sn = angles[2 * bi + 1];
-  const int p0 = coff[k], p1 = coff[k + 1];
   double mn1 = INFINITY, mx1 = -INFINITY, mn2 = INFINITY, mx2 = -INFINITY;
-  for (int p = p0 + lane; p < p1; p += 32) {
+  for (int p = p0 + lane; p < p1; p += G) {
     double c1, c2;
     fit_project(cx[p], cy[p], cs, sn, c1, c2);
     mn1 = fmin(mn1, c1); mx1 = fmax(mx1, c1); mn2 = fmin(mn2, c2); mx2 = fmax(mx2, c2);
   }
-  mn1 = warp_min(mn1); mx1 = warp_max(mx1); mn2 = warp_min(mn2); mx2 = warp_max(mx2);
+  mn1 = group_reduce<G, 0>(mn1); mx1 = group_reduce<G, 1>(mx1); mn2 = group_reduce<G, 0>(mn2); mx2 = group_reduce<G, 1>(mx2);
   if (lane == 0) {
     double* r = rect + (long long)k * 16;
     r[0] = cs; r[1] = -sn; r[2] = cs; r[3] = -sn;
@@ -352,9 +379,13 @@ int dfu_fit_clusters(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, con
   k_fit_gather<<<nb, 256, 0, st>>>(scop, order, x, y, n, K, cx, cy, coff);
   DFU_LAUNCH_CHECK(ctx);
   const long long nw = (long long)K * na;
-  k_fit_cost<<<(unsigned)((nw * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost);
+  k_fit_cost<32><<<(unsigned)((nw * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost);
   DFU_LAUNCH_CHECK(ctx);
-  k_fit_finish<<<(unsigned)(((long long)K * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
+  k_fit_cost<256><<<(unsigned)nw, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost);      // blocks of small clusters exit at once
+  DFU_LAUNCH_CHECK(ctx);
+  k_fit_finish<32><<<(unsigned)(((long long)K * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
+  DFU_LAUNCH_CHECK(ctx);
+  k_fit_finish<256><<<(unsigned)K, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }

@@ -112,11 +112,18 @@ __global__ void __launch_bounds__(I_THREADS) k_inst_gather(InstTables T, const u
   }
 }
 
+// cnt[s] += 1 for every lane with s >= 0, one atomic per distinct segment in the warp (points of a segment are
+// contiguous, so a warp almost always holds one or two segments: per-lane atomics would serialise on one address)
+__device__ __forceinline__ void seg_warp_add(int32_t* __restrict__ cnt, int s) {
+  const unsigned m = __match_any_sync(0xffffffffu, s);
+  if (s >= 0 && (threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(cnt + s, __popc(m));
+}
+
 // per-segment count of kept points
 __global__ void __launch_bounds__(I_THREADS) k_seg_count(const int32_t* __restrict__ seg, const uint8_t* __restrict__ keep,
                                                          int64_t np, int32_t* __restrict__ cnt) {
   const int64_t i = (int64_t)blockIdx.x * I_THREADS + threadIdx.x;
-  if (i < np && keep[i]) atomicAdd(cnt + seg[i], 1);
+  seg_warp_add(cnt, (i < np && keep[i]) ? seg[i] : -1);
 }
 
 __global__ void __launch_bounds__(I_THREADS) k_ref_active(const int32_t* __restrict__ seg, const uint8_t* __restrict__ keep,
@@ -130,12 +137,14 @@ __global__ void __launch_bounds__(I_THREADS) k_fuse_flags(const int32_t* __restr
                                                           const uint8_t* __restrict__ gate, const int32_t* __restrict__ cnt1,
                                                           int64_t np, int32_t* __restrict__ flag, int32_t* __restrict__ cnt2) {
   const int64_t i = (int64_t)blockIdx.x * I_THREADS + threadIdx.x;
-  if (i >= np) return;
-  const int s = seg[i];
-  int f = keep[i];
-  if (f && (s & 1) && cnt1[s - 1] > 0) f = gate[i];
-  flag[i] = f;
-  if (f) atomicAdd(cnt2 + s, 1);
+  int s = -1, f = 0;
+  if (i < np) {
+    s = seg[i];
+    f = keep[i];
+    if (f && (s & 1) && cnt1[s - 1] > 0) f = gate[i];
+    flag[i] = f;
+  }
+  seg_warp_add(cnt2, f ? s : -1);
 }
 
 __global__ void __launch_bounds__(I_THREADS) k_fuse_scatter(const int64_t* __restrict__ flagscan /*exclusive, [np+1]*/,
@@ -146,15 +155,35 @@ __global__ void __launch_bounds__(I_THREADS) k_fuse_scatter(const int64_t* __res
                                                             double* __restrict__ fy, double* __restrict__ fz,
                                                             int32_t* __restrict__ finst, unsigned long long* __restrict__ zmax) {
   const int64_t i = (int64_t)blockIdx.x * I_THREADS + threadIdx.x;
-  if (i >= np) return;
-  const int s = seg[i];
-  int f = keep[i];
-  if (f && (s & 1) && cnt1[s - 1] > 0) f = gate[i];
-  if (!f) return;
-  const int64_t o = flagscan[i];
-  fx[o] = px[i]; fy[o] = py[i]; fz[o] = pz[i];
-  finst[o] = s >> 1;
-  atomicMax(zmax + (s >> 1), dfu_order_f64(pz[i]));
+  int g = -1;
+  unsigned long long zb = 0ull;
+  if (i < np) {
+    const int s = seg[i];
+    int f = keep[i];
+    if (f && (s & 1) && cnt1[s - 1] > 0) f = gate[i];
+    if (f) {
+      const int64_t o = flagscan[i];
+      const double z = pz[i];
+      fx[o] = px[i]; fy[o] = py[i]; fz[o] = z;
+      finst[o] = s >> 1;
+      g = s >> 1;
+      zb = dfu_order_f64(z);
+    }
+  }
+  // max z per instance: the warp almost always holds ONE instance -> shuffle reduction + one atomic
+  const unsigned have = __ballot_sync(0xffffffffu, g >= 0);
+  if (have == 0u) return;
+  const int g0 = __shfl_sync(0xffffffffu, g, __ffs(have) - 1);
+  if (__all_sync(0xffffffffu, g < 0 || g == g0)) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long ob = __shfl_xor_sync(0xffffffffu, zb, o);
+      zb = ob > zb ? ob : zb;
+    }
+    if ((threadIdx.x & 31) == 0) atomicMax(zmax + g0, zb);
+  } else if (g >= 0) {
+    atomicMax(zmax + g, zb);
+  }
 }
 
 // inst_off [G+1] in the fused array = flagscan at the instance's first pair (segment 2g)

@@ -167,6 +167,28 @@ __global__ void __launch_bounds__(256) k_pack_masks(const dfu_view* __restrict__
   labelmap[(int64_t)v * HW + p] = w;
 }
 
+// uint8 masks, H*W a multiple of 16: one thread per 16 pixels, 128-bit loads of every mask plane, four 128-bit stores
+__global__ void __launch_bounds__(256) k_pack_masks_v16(const dfu_view* __restrict__ views, const uint8_t* __restrict__ masks,
+                                                        int HW, uint32_t* __restrict__ labelmap) {
+  const int v = blockIdx.y;
+  const int n = views[v].n_inst;
+  const int64_t moff = (int64_t)views[v].inst_off * HW;
+  const int p = (blockIdx.x * 256 + threadIdx.x) * 16;
+  if (p >= HW) return;
+  uint32_t w[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) w[i] = 0;
+  for (int j = 0; j < n; j++) {
+    const uint4 m = __ldg(reinterpret_cast<const uint4*>(masks + moff + (int64_t)j * HW + p));
+    const uint32_t q[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+    for (int i = 0; i < 16; i++) w[i] |= (((q[i >> 2] >> (8 * (i & 3))) & 0xffu) ? 1u : 0u) << j;
+  }
+  uint4* out = reinterpret_cast<uint4*>(labelmap + (int64_t)v * HW + p);
+#pragma unroll
+  for (int i = 0; i < 4; i++) out[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+}
+
 // ---------------------------------------------------------------- sparse depth (load_depth_input)
 // last point in input order wins on duplicate pixels (numpy fancy assignment, my_loader.py:117):
 // pass 1 atomicMax of the row index per pixel, pass 2 writes the depth of the winning row.
@@ -230,6 +252,8 @@ extern "C" int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view*
   DFU_PROF(ctx, (cudaStream_t)stream, PT_PACK_MASKS);
   if (is_f32)
     k_pack_masks<float><<<grid, 256, 0, (cudaStream_t)stream>>>(views_dev, (const float*)masks, HW, labelmap);
+  else if ((HW & 15) == 0 && (((uintptr_t)masks | (uintptr_t)labelmap) & 15) == 0)
+    k_pack_masks_v16<<<dim3((HW / 16 + 255) / 256, V), 256, 0, (cudaStream_t)stream>>>(views_dev, (const uint8_t*)masks, HW, labelmap);
   else
     k_pack_masks<uint8_t><<<grid, 256, 0, (cudaStream_t)stream>>>(views_dev, (const uint8_t*)masks, HW, labelmap);
   DFU_LAUNCH_CHECK(ctx);
