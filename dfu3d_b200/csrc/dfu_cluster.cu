@@ -23,6 +23,14 @@ __global__ void k_cluster_cellsize(const double* __restrict__ R0, double* __rest
   if (i < ninst) cell[i] = R0[i] / sqrt(2.0) * (1.0 - 1e-9);
 }
 
+__global__ void __launch_bounds__(256) k_cluster_aux_init(CellAux* __restrict__ aux, int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= n) return;
+  CellAux a;
+  a.minx = ~0ull; a.maxx = 0ull; a.miny = ~0ull; a.maxy = 0ull; a.maxR = 0ull;
+  aux[t] = a;
+}
+
 __global__ void __launch_bounds__(256) k_cluster_aux(DfuGrid g, const double* __restrict__ R0, const double* __restrict__ Rd,
                                                      double* __restrict__ sR, CellAux* __restrict__ aux,
                                                      int32_t* __restrict__ parent, int32_t* __restrict__ rootmin) {
@@ -178,11 +186,10 @@ int dfu_cluster_points(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, c
   DfuGrid g;
   int rc = dfu_grid_build(ctx, st, sb, x, y, nullptr, inst, nullptr, n, ninst, cellv, &g);
   if (rc) return rc;
-  // aux: min fields start at ~0, max fields at 0
-  DFU_CUDA(ctx, cudaMemsetAsync(aux, 0, m * sizeof(CellAux), st));
-  DFU_CUDA(ctx, cudaMemset2DAsync(&aux[0].minx, sizeof(CellAux), 0xFF, 8, m, st));
-  DFU_CUDA(ctx, cudaMemset2DAsync(&aux[0].miny, sizeof(CellAux), 0xFF, 8, m, st));
+  // aux: min fields start at ~0, max fields at 0 (a kernel: strided cudaMemset2D over 2.5 M rows costs milliseconds)
   const unsigned nb = (unsigned)((n + 255) / 256);
+  k_cluster_aux_init<<<nb, 256, 0, st>>>(aux, n);
+  DFU_LAUNCH_CHECK(ctx);
   k_cluster_aux<<<nb, 256, 0, st>>>(g, R0_dev, Rd_dev, sR, aux, parent, rootmin);
   DFU_LAUNCH_CHECK(ctx);
   const int grid = 148 * 8;
@@ -270,13 +277,15 @@ template <int G, int OP> __device__ __forceinline__ double group_reduce(double v
 template <int G>
 __global__ void __launch_bounds__(256) k_fit_cost(const double* __restrict__ cx, const double* __restrict__ cy,
                                                   const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
-                                                  int na, double* __restrict__ cost) {
-  const long long w = ((long long)blockIdx.x * 256 + threadIdx.x) / G;
+                                                  int na, double* __restrict__ cost, const int32_t* __restrict__ big) {
   const int lane = threadIdx.x % G;
-  if (w >= (long long)K * na) return;
-  const int k = (int)(w / na), a = (int)(w % na);
+  const long long nunits = G == 32 ? (long long)K * na : (long long)big[0] * na;
+  // G = 32: one warp per (cluster, angle), large clusters skipped; G = 256: persistent blocks over the listed ones
+  for (long long w = G == 32 ? ((long long)blockIdx.x * 256 + threadIdx.x) / 32 : blockIdx.x; w < nunits;
+       w += G == 32 ? nunits : gridDim.x) {
+  const int k = G == 32 ? (int)(w / na) : big[1 + w / na], a = (int)(w % na);
   const int p0 = coff[k], p1 = coff[k + 1];
-  if ((G == 32) != (p1 - p0 <= FIT_BIG)) return;        // uniform per group (and per block when G = 256)
+  if (G == 32 && p1 - p0 > FIT_BIG) return;
   const double cs = angles[2 * a], sn = angles[2 * a + 1];
   double mn1 = INFINITY, mx1 = -INFINITY, mn2 = INFINITY, mx2 = -INFINITY;
   for (int p = p0 + lane; p < p1; p += G) {
@@ -306,18 +315,28 @@ __global__ void __launch_bounds__(256) k_fit_cost(const double* __restrict__ cx,
     const double V1 = n1 > 0 ? -(q1 / n1) : 0.0, V2 = n2 > 0 ? -(q2 / n2) : 0.0;
     cost[(long long)k * na + a] = V1 + V2;
   }
+  }
+}
+
+// big[0] = number of clusters with more than FIT_BIG points, big[1..] = their ids (any order)
+__global__ void __launch_bounds__(256) k_fit_big_list(const int32_t* __restrict__ coff, int K, int32_t* __restrict__ big) {
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  if (k < K && coff[k + 1] - coff[k] > FIT_BIG) big[1 + atomicAdd(big, 1)] = k;
 }
 
 // one group per cluster: first maximum (rectangle_fitting.py:135-136), runner-up, rectangle at the best angle (:138-157)
 template <int G>
 __global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ cx, const double* __restrict__ cy,
                                                     const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
-                                                    int na, const double* __restrict__ cost, double* __restrict__ rect) {
-  const int k = (int)(((long long)blockIdx.x * 256 + threadIdx.x) / G);
+                                                    int na, const double* __restrict__ cost, double* __restrict__ rect,
+                                                    const int32_t* __restrict__ big) {
   const int lane = threadIdx.x % G;
-  if (k >= K) return;
+  const int nunits = G == 32 ? K : big[0];
+  for (int w = G == 32 ? (int)(((long long)blockIdx.x * 256 + threadIdx.x) / 32) : blockIdx.x; w < nunits;
+       w += G == 32 ? nunits : gridDim.x) {
+  const int k = G == 32 ? w : big[1 + w];
   const int p0 = coff[k], p1 = coff[k + 1];
-  if ((G == 32) != (p1 - p0 <= FIT_BIG)) return;
+  if (G == 32 && p1 - p0 > FIT_BIG) return;
   // every warp of the group scans the (<= 96) costs redundantly: identical result in each, no cross-warp exchange
   const int wl = threadIdx.x & 31;
   double best = -INFINITY;
@@ -352,6 +371,7 @@ __global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ c
     r[8] = mn1; r[9] = mn2; r[10] = mx1; r[11] = mx2;
     r[12] = atan2(sn, cs); r[13] = best; r[14] = run; r[15] = (double)(p1 - p0);
   }
+  }
 }
 
 // rect_dev [K][16].  K must be the host copy of *ClusterOut.ncluster.
@@ -379,13 +399,17 @@ int dfu_fit_clusters(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, con
   k_fit_gather<<<nb, 256, 0, st>>>(scop, order, x, y, n, K, cx, cy, coff);
   DFU_LAUNCH_CHECK(ctx);
   const long long nw = (long long)K * na;
-  k_fit_cost<32><<<(unsigned)((nw * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost);
+  DFU_SLOT(ctx, big, int32_t*, sb + 7, ((size_t)K + 1) * 4);
+  DFU_CUDA(ctx, cudaMemsetAsync(big, 0, 4, st));
+  k_fit_big_list<<<(K + 255) / 256, 256, 0, st>>>(coff, K, big);
   DFU_LAUNCH_CHECK(ctx);
-  k_fit_cost<256><<<(unsigned)nw, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost);      // blocks of small clusters exit at once
+  k_fit_cost<32><<<(unsigned)((nw * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, big);
   DFU_LAUNCH_CHECK(ctx);
-  k_fit_finish<32><<<(unsigned)(((long long)K * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
+  k_fit_cost<256><<<148 * 4, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, big);       // persistent over the big clusters
   DFU_LAUNCH_CHECK(ctx);
-  k_fit_finish<256><<<(unsigned)K, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
+  k_fit_finish<32><<<(unsigned)(((long long)K * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev, big);
+  DFU_LAUNCH_CHECK(ctx);
+  k_fit_finish<256><<<148, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev, big);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }

@@ -153,6 +153,15 @@ int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const
 // MODE 1: any reference point with sqrt(d2) < maxdist                             -> keep
 // The squared distance is ((dx*dx + dy*dy) + dz*dz) with separately rounded products, as numpy evaluates
 // ((a - b) ** 2).sum(-1) (oracle/fakes.py: radius_outlier_mask; oracle/restate.py: ball_gate).
+// first index in a[lo..hi) with a[i] >= v
+__device__ __forceinline__ int grid_lb(const unsigned long long* __restrict__ a, int lo, int hi, unsigned long long v) {
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(a + mid) < v) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
 template <int MODE>
 __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, double px, double py, double pz, double lim,
                                           int nb) {
@@ -162,14 +171,19 @@ __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, do
   const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
   if (cx < 0 || cy < 0 || cz < 0) return false;   // far outside the reference bounding box (or an empty segment)
   int count = 0;
+  // all 27 cells lie in the three x-rows cx-1 .. cx+1 = ONE range of the cell table: two searches over the whole
+  // table, then every column search runs inside that (much shorter) range
+  const int xr0 = grid_lb(g.ukey, 0, ncell, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
+  const int xr1 = grid_lb(g.ukey, xr0, ncell, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));   // cell coordinates never exceed 65534
+  if (xr1 <= xr0) return false;
   // the query's own (x, y) column first: with a small nb the walk usually ends there
   for (int o = 0; o < 9; o++) {
     const int dx = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) / 3 - 1), dy = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) % 3 - 1);
     const int ex = cx + dx, ey = cy + dy;
     if (ex < 1 || ey < 1) continue;
     const int zlo = cz - 1 < 1 ? 1 : cz - 1;
-    const int c0 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, zlo));
-    const int c1 = dfu_lower_bound_u64(g.ukey, ncell, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
+    const int c0 = grid_lb(g.ukey, xr0, xr1, dfu_grid_key(s, ex, ey, zlo));
+    const int c1 = grid_lb(g.ukey, c0, xr1, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
     if (c1 <= c0) continue;
     const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
     for (int j = lo; j < hi; j++) {
