@@ -62,7 +62,7 @@ def workload_config(a):
     return {'workload': 'configs[3]: full pipeline (S1 projection+label inheritance, S2 densification+angular dedup, '
                         'radius filters, BallQuery gate, clustering, box fitting, fp16 cloud emit)',
             'frames_per_step_per_gpu': a.frames, 'cams_per_frame': a.cams, 'sweeps': a.sweeps,
-            'lidar_pts_per_frame': 34720 * a.sweeps, 'image': '1600x900', 'max_instances_per_view': a.max_inst,
+            'lidar_rays_per_frame': 34720 * a.sweeps, 'lidar_note': 'rays without a return (sky) and 2 % dropouts are not in the sweep: ~246 k rows per frame', 'image': '1600x900', 'max_instances_per_view': a.max_inst,
             'distinct_frames': min(a.distinct, a.frames), 'l2': 'inputs per step >> 126 MB L2 (no flush needed)',
             'parallelism': 'frame-wise sharding, 1 process per GPU, no collective'}
 
