@@ -204,7 +204,8 @@ __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, do
 
 // one thread per SORTED position: neighbouring threads walk the same cells (broadcast loads)
 __global__ void __launch_bounds__(G_THREADS) k_radius_count(DfuGrid g, const SegPrm* __restrict__ prm,
-                                                            uint8_t* __restrict__ keep) {
+                                                            uint8_t* __restrict__ keep, int32_t* __restrict__ todo,
+                                                            int32_t* __restrict__ ntodo) {
   const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (t >= g.n) return;
   const unsigned long long k = g.skey[t];
@@ -230,8 +231,57 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_count(DfuGrid g, const Seg
     }
     if (count > p.nb) { keep[g.sidx[t]] = 1; return; }
   }
-  const bool kp = grid_walk<0>(g, *g.ncell, s, px, py, pz, r2, p.nb);
-  keep[g.sidx[t]] = kp ? 1 : 0;
+  // undecided: queue the sorted position for the warp-per-point walk (k_radius_walk).  A per-thread walk here would
+  // make nearly every warp wait for its one outlier lane to scan cells that hold thousands of points.
+  todo[atomicAdd(ntodo, 1)] = (int32_t)t;
+}
+
+// Phase 2 of the radius filter: one WARP per undecided point.  The lanes stride over the points of each of the 9
+// (x, y) columns around the query (coalesced loads of the sorted SoA) and stop as soon as the count exceeds nb.
+__global__ void __launch_bounds__(G_THREADS) k_radius_walk(DfuGrid g, const SegPrm* __restrict__ prm,
+                                                           const int32_t* __restrict__ todo, const int32_t* __restrict__ ntodo,
+                                                           uint8_t* __restrict__ keep) {
+  const int lane = threadIdx.x & 31;
+  const int nw = (gridDim.x * G_THREADS) >> 5;
+  const int ncell = *g.ncell, nt = *ntodo;
+  for (int e = (blockIdx.x * G_THREADS + threadIdx.x) >> 5; e < nt; e += nw) {
+    const int t = todo[e];
+    const int s = (int)(g.skey[t] >> 48);
+    const SegPrm p = prm[s];
+    const double r2 = __dmul_rn(p.r, p.r);
+    const double px = g.sx[t], py = g.sy[t], pz = g.sz[t];
+    const double c = g.cell[s];
+    const int cx = dfu_cell_coord(px, dfu_unorder_f64(g.segmin[3 * s + 0]), c);
+    const int cy = dfu_cell_coord(py, dfu_unorder_f64(g.segmin[3 * s + 1]), c);
+    const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
+    bool kp = false;
+    if (cx >= 0 && cy >= 0 && cz >= 0) {
+      const int xr0 = grid_lb(g.ukey, 0, ncell, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
+      const int xr1 = grid_lb(g.ukey, xr0, ncell, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));
+      int count = 0;
+      for (int o = 0; o < 9 && !kp; o++) {
+        const int ex = cx + o / 3 - 1, ey = cy + o % 3 - 1;
+        if (ex < 1 || ey < 1) continue;
+        const int zlo = cz - 1 < 1 ? 1 : cz - 1;
+        const int c0 = grid_lb(g.ukey, xr0, xr1, dfu_grid_key(s, ex, ey, zlo));
+        const int c1 = grid_lb(g.ukey, c0, xr1, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
+        if (c1 <= c0) continue;
+        const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
+        for (int j0 = lo; j0 < hi && !kp; j0 += 32) {
+          const int j = j0 + lane;
+          bool in = false;
+          if (j < hi) {
+            const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
+                         az = __dsub_rn(__ldg(g.sz + j), pz);
+            in = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)) < r2;
+          }
+          count += __popc(__ballot_sync(0xffffffffu, in));
+          kp = count > p.nb;
+        }
+      }
+    }
+    if (lane == 0) keep[g.sidx[t]] = kp ? 1 : 0;
+  }
 }
 
 __global__ void __launch_bounds__(G_THREADS) k_seg_active(const int32_t* __restrict__ seg, const int64_t* __restrict__ seg_off,
@@ -265,7 +315,13 @@ int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, cons
   }
   {
     DFU_PROF(ctx, st, PT_RADIUS);
-    k_radius_count<<<(unsigned)((n + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(g, prm_dev, keep);
+    // the unsorted-key buffer of the grid build is free after the sort: it holds the list of undecided points
+    int32_t* todo = (int32_t*)ctx->slot[sb + 1];
+    int32_t* ntodo = g.ncell + 2;
+    DFU_CUDA(ctx, cudaMemsetAsync(ntodo, 0, 4, st));
+    k_radius_count<<<(unsigned)((n + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(g, prm_dev, keep, todo, ntodo);
+    DFU_LAUNCH_CHECK(ctx);
+    k_radius_walk<<<148 * 8, G_THREADS, 0, st>>>(g, prm_dev, todo, ntodo, keep);
     DFU_LAUNCH_CHECK(ctx);
   }
   return DFU_OK;

@@ -29,7 +29,10 @@ __global__ void __launch_bounds__(256) k_rows_to_soa(const double* __restrict__ 
 __global__ void __launch_bounds__(256) k_count_keep(const int32_t* __restrict__ seg, const uint8_t* __restrict__ keep, int64_t n,
                                                     int32_t* __restrict__ cnt) {
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (i < n && keep[i]) atomicAdd(cnt + seg[i], 1);
+  // one atomic per distinct segment in the warp (segments are contiguous: per-lane atomics would hit one address)
+  const int s = (i < n && keep[i]) ? seg[i] : -1;
+  const unsigned m = __match_any_sync(0xffffffffu, s);
+  if (s >= 0 && (threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(cnt + s, __popc(m));
 }
 
 static int check_grid_err(dfu_ctx* ctx, cudaStream_t st, int sb, const char* what) {
