@@ -262,7 +262,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        os.environ['NCCL_DEBUG'] = os.environ.get('DFU_NCCL_DEBUG', 'WARN')    # keep stdout to the ONE JSON line
+        os.environ['NCCL_DEBUG'] = os.environ.get('DFU_NCCL_DEBUG', 'NONE')    # WARN still prints the version banner on stdout: keep stdout to the ONE JSON line
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
     pipe = pipeline.FusionPipeline(local)
