@@ -264,7 +264,18 @@ def main():
     if world > 1:
         os.environ['NCCL_DEBUG'] = os.environ.get('DFU_NCCL_DEBUG', 'NONE')    # WARN still prints the version banner on stdout: keep stdout to the ONE JSON line
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-        dist.init_process_group('nccl', device_id=dev)
+        # NCCL writes its banner to fd 1 when the communicator is created (first collective): keep it off stdout
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group('nccl', device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     pipe = pipeline.FusionPipeline(local)
 
     # ---- synthetic batch, generated on the device (identical generator for the CPU arm)
