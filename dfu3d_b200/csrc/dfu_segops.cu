@@ -215,11 +215,12 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_count(DfuGrid g, const Seg
   const double r2 = __dmul_rn(p.r, p.r);
   const double px = g.sx[t], py = g.sy[t], pz = g.sz[t];
   // Fast accept: the sorted array puts points of the same / adjacent cells next to each other, so in a dense cloud
-  // the nb + 1 points needed are almost always among the few entries around t (coalesced loads, no cell look-up).
+  // the nb + 1 points needed are almost always among the nb + 2 entries on each side of t (coalesced loads, no cell look-up).
   // Only a "keep" can be decided here; everything else takes the exact walk below, which counts from scratch.
   {
     int count = 1;   // the point itself (d2 = 0 < r2)
-    for (int o = 1; o <= 4 && count <= p.nb; o++) {
+    const int reach = p.nb + 2 < 4 ? 4 : (p.nb + 2 > 48 ? 48 : p.nb + 2);   // entries examined on each side
+    for (int o = 1; o <= reach && count <= p.nb; o++) {
 #pragma unroll
       for (int sgn = -1; sgn <= 1; sgn += 2) {
         const int64_t u = t + sgn * o;
