@@ -187,7 +187,7 @@ __device__ __forceinline__ unsigned sor_compact3(unsigned long long x) {
   return (unsigned)x;
 }
 
-#define SOR_LEAF 32
+#define SOR_LEAF 96   /* measured on the config-3 cloud: 4: 50.6 ms, 16: 35.7, 32: 30.0, 64: 27.0, 128: 26.7, 256: 28.1, 2048: 48.6 */
 #define SOR_STACK 136
 
 __global__ void __launch_bounds__(SOR_THREADS) k_sor_knn(const unsigned long long* __restrict__ skey, const int32_t* __restrict__ sidx,
