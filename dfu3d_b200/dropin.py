@@ -496,3 +496,20 @@ class MyLoader():
         points = np.fromfile(str(os.path.join(self.root_path, 'velodyne', file_idx + '.bin')), dtype=np.float32).reshape(-1, 4)
         image = np.array(_imread(os.path.join(self.root_path, 'image_2', file_idx + '.png')), dtype=np.int32)
         return load_depth_input(calib, image, points)
+
+
+# ---- GT-database tooling: the consumer of the pseudo-boxes ---------------------------------------
+def points_in_boxes_cpu(points, boxes):
+    """pcdet/ops/roiaware_pool3d/roiaware_pool3d_utils.py:9-25 — same name, argument order, asserts and return
+    (int32 [num_boxes, num_points]; numpy in -> numpy out, tensor in -> tensor out); computed on the GPU."""
+    assert boxes.shape[1] == 7
+    assert points.shape[1] == 3
+    return ops.points_in_boxes(points, boxes)
+
+
+def crop_gt_points(points, gt_boxes):
+    """The loop body of create_groundtruth_database (pcdet/datasets/kitti/kitti_dataset.py:310-318) for every box of a
+    frame: returns the list of `gt_points` arrays (float32 [k_i, C], xyz relative to the box centre) the reference writes
+    to `<idx>_<name>_<i>.bin`, and the [M+1] offsets of their concatenation (create_integrated_database.py:26-45)."""
+    rows, off = ops.crop_boxes(np.ascontiguousarray(points, np.float32), gt_boxes)
+    return [rows[off[i]:off[i + 1]] for i in range(len(off) - 1)], off

@@ -154,3 +154,48 @@ def backproject(depth, calibs, min_depth=0.001, max_z=None, ctx=None):
     ctx.check(ctx.lib.dfu_backproject_sync(ctx.h, ctx.stream, V, _lib.hptr(views), _lib.hptr(prm), _lib.dptr(d), gate,
                                            _lib.dptr(xyz), _lib.dptr(pix), xyz.shape[0], _lib.hptr(counts)))
     return _out(xyz[:M], as_np), _out(pix[:M], as_np), counts
+
+
+def _dev_f32(ctx, a, cols=None):
+    if isinstance(a, torch.Tensor):
+        t, was_np = a.to(device=ctx.device, dtype=torch.float32), False
+    else:
+        t, was_np = torch.from_numpy(np.ascontiguousarray(np.asarray(a, np.float32))).to(ctx.device), True
+    if cols is not None:
+        t = t.reshape(-1, cols)
+    return t.contiguous(), was_np
+
+
+def points_in_boxes(points, boxes, ctx=None):
+    """roiaware_pool3d_utils.points_in_boxes_cpu (pcdet/ops/roiaware_pool3d/roiaware_pool3d_utils.py:9-25): points
+    [N, C >= 3] float32, boxes [M, 7] = x y z dx dy dz heading -> int32 [M, N]."""
+    ctx = ctx or _lib.default_context(0)
+    b, _ = _dev_f32(ctx, boxes, 7)
+    p, as_np = _dev_f32(ctx, points)
+    assert p.dim() == 2 and p.shape[1] >= 3
+    out = torch.empty((b.shape[0], p.shape[0]), dtype=torch.int32, device=ctx.device)   # every element is written
+    ctx.check(ctx.lib.dfu_points_in_boxes(ctx.h, ctx.stream, _lib.dptr(p) if p.numel() else None, p.shape[1], p.shape[0],
+                                          _lib.dptr(b) if b.numel() else None, b.shape[0], _lib.dptr(out) if out.numel() else None))
+    return _out(out, as_np)
+
+
+def crop_boxes(points, boxes, ctx=None):
+    """create_groundtruth_database's per-box crop (pcdet/datasets/kitti/kitti_dataset.py:310-319) for all boxes at once:
+    returns (rows [total, C] float32: the points inside box 0, then box 1, ... in point order, xyz minus the box centre;
+    offsets [M+1] int64) — the `global_data_offset` layout of tools/process_tools/create_integrated_database.py.
+    float64 boxes (what the annotation pickles hold) keep their float64 centres for the subtraction, as numpy does."""
+    ctx = ctx or _lib.default_context(0)
+    b, _ = _dev_f32(ctx, boxes, 7)
+    p, as_np = _dev_f32(ctx, points)
+    M, (n, Cc) = b.shape[0], p.shape
+    off = np.zeros(M + 1, np.int64)
+    c64 = None
+    if (boxes.dtype == torch.float64) if isinstance(boxes, torch.Tensor) else (np.asarray(boxes).dtype == np.float64):
+        c64 = (boxes if isinstance(boxes, torch.Tensor) else torch.from_numpy(np.asarray(boxes))).reshape(-1, 7)[:, :3]
+        c64 = c64.to(ctx.device).contiguous()
+    args = (ctx.h, ctx.stream, _lib.dptr(p) if p.numel() else None, Cc, n, _lib.dptr(b) if b.numel() else None, M,
+            _lib.dptr(c64) if c64 is not None and c64.numel() else None)
+    ctx.check(ctx.lib.dfu_crop_boxes_sync(*args, None, 0, _lib.hptr(off)))
+    rows = torch.empty((max(int(off[-1]), 1), Cc), dtype=torch.float32, device=ctx.device)
+    ctx.check(ctx.lib.dfu_crop_boxes_sync(*args, _lib.dptr(rows), rows.shape[0], _lib.hptr(off)))
+    return _out(rows[:int(off[-1])], as_np), off

@@ -226,6 +226,23 @@ int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host
                            int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int n_angles,
                            double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host);
 
+/* ---- GT-database tooling (the consumer of the pseudo-boxes) ---------------------------------------------
+ * points-in-rotated-boxes with the arithmetic of the reference's CPU routine
+ * (pcdet/ops/roiaware_pool3d/src/roiaware_pool3d.cpp:121-168, called by
+ * pcdet/datasets/kitti/kitti_dataset.py:310-312): points float [n][C] (xyz first, C >= 3), boxes float [M][7]
+ * = x y z dx dy dz heading (centre).  out_mask int32 [M][n], 1 = inside. */
+int dfu_points_in_boxes(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* boxes, int M,
+                        int32_t* out_mask);
+
+/* The per-box crop of create_groundtruth_database (kitti_dataset.py:314-319: rows inside box i in point order, xyz
+ * shifted by the box centre) for all boxes at once, concatenated box by box = the integrated database layout of
+ * tools/process_tools/create_integrated_database.py:26-45 (offsets_host [M+1] are its global_data_offset pairs).
+ * out_rows float [capacity][C]; out_rows == NULL: size query (offsets only).  centres64 (nullable, device double
+ * [M][3]): the annotation's float64 box centres — numpy's in-place `float32 -= float64` of :318 subtracts in double
+ * and rounds once; without it the float32 centres of `boxes` are subtracted in float32. */
+int dfu_crop_boxes_sync(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* boxes, int M,
+                        const double* centres64, float* out_rows, int64_t capacity, int64_t* offsets_host);
+
 #ifdef __cplusplus
 }
 #endif

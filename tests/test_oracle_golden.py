@@ -9,7 +9,7 @@ import pytest
 
 from oracle import restate
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', '*.npz')))
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', '[nk]*_[a-z].npz')))
 
 
 def load_golden(path):
