@@ -26,6 +26,7 @@ struct dfu_ctx {
   cudaStream_t stream;
   int V;
   dfu_view* views_host;       // malloc'd copy
+  void* s2_consts;            // malloc'd float64 view constants of the densify passes (dfu_densify.cu)
   dfu_fusion_params prm;
   const void* lidar;
   const float* depth;
@@ -77,9 +78,9 @@ enum {
   SL_VIEWS = 0, SL_FLAGS, SL_PIX, SL_LABEL, SL_BLKCNT, SL_BLKOFF, SL_CUBTMP, SL_FLIST, SL_ALIST, SL_BLABEL,
   SL_KEY, SL_TABLE, SL_VOXCNT, SL_VOXOFF, SL_REPZ, SL_REPY, SL_REPY_XYZ, SL_REPY_LABEL, SL_REPZ_XYZ, SL_STATS,
   SL_SEGCNT, SL_SEGOFF, SL_IPARAMS, SL_ANGLES, SL_ISCRATCH_D, SL_ISCRATCH_I, SL_BOXES, SL_BOXCNT, SL_SEGOUT,
-  SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11, SL_VOXCELL
+  SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11, SL_VOXCELL, SL_WARPSTAT
 };
-static_assert(SL_VOXCELL < 44, "SL_* ids must stay below the operator slot ranges");
+static_assert(SL_WARPSTAT < 44, "SL_* ids must stay below the operator slot ranges");
 
 int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...);
 void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes);      // NULL on failure (error recorded)
@@ -136,6 +137,29 @@ __device__ __forceinline__ void dfu_backproject(const dfu_view& vw, int col, int
   double dd = (double)d;
   double xr = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)col, (double)vw.cu), dd), (double)vw.fu), (double)vw.tx);
   double yr = __dadd_rn(__ddiv_rn(__dmul_rn(__dsub_rn((double)row, (double)vw.cv), dd), (double)vw.fv), (double)vw.ty);
+  X = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 0, 4);
+  Y = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 1, 4);
+  Z = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 2, 4);
+}
+
+// a / d, correctly rounded, for a divisor whose correctly rounded reciprocal y = RN(1/d) is known (one per view):
+// two Markstein refinements (q faithful after the first, RN(a/d) after the second; exact remainders through FMA) —
+// 1 multiply + 4 FMA instead of the ~25-instruction generic DDIV sequence with its slow-path call.
+// Checked against __ddiv_rn on 2^32 operand pairs by tools/divcheck.cu.
+__device__ __forceinline__ double dfu_div_by(double a, double d, double y) {
+  double q = __dmul_rn(a, y);
+  double r = __fma_rn(-q, d, a);
+  q = __fma_rn(r, y, q);
+  r = __fma_rn(-q, d, a);
+  return __fma_rn(r, y, q);
+}
+
+// same result as dfu_backproject, with the per-view reciprocals rfu = RN(1/fu), rfv = RN(1/fv) supplied
+__device__ __forceinline__ void dfu_backproject_r(const dfu_view& vw, double rfu, double rfv, int col, int row, float d,
+                                                  double& X, double& Y, double& Z) {
+  double dd = (double)d;
+  double xr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)col, (double)vw.cu), dd), (double)vw.fu, rfu), (double)vw.tx);
+  double yr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)row, (double)vw.cv), dd), (double)vw.fv, rfv), (double)vw.ty);
   X = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 0, 4);
   Y = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 1, 4);
   Z = dfu_row4_f64(xr, yr, dd, 1.0, vw.inv44, 2, 4);

@@ -98,6 +98,7 @@ extern "C" void dfu_destroy(dfu_ctx* ctx) {
     free(ctx->prof_tag);
   }
   free(ctx->views_host);
+  free(ctx->s2_consts);
   free(ctx->cnt_project);
   free(ctx->off_project);
   free(ctx->cnt_vox);

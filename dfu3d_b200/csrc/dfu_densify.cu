@@ -43,16 +43,50 @@ static S2Prm make_s2(const dfu_fusion_params* p) {
   return s;
 }
 
+// Per-view float64 constants of the back-projection for passes A and B, in constant memory: the operands reach the
+// FP64 pipe straight from the constant bank (uniform per CTA), so no thread widens 18 float32 constants per pixel and
+// the CTA does not stage + barrier the view block.  Derived on the host from the float32 dfu_view (widening is exact;
+// the two reciprocals are IEEE divisions = correctly rounded, which dfu_div_by requires).  Batches with more views than
+// fit in the 64 KB bank run in chunks of S2_CVIEWS.
+#define S2_CVIEWS 400
+struct S2View { double cu, fu, tx, cv, fv, ty, rfu, rfv, m[3][4]; };   // m[j][k] = inv44[k][j]
+static_assert(sizeof(S2View) * S2_CVIEWS <= 64000, "constant bank");
+__constant__ S2View c_view[S2_CVIEWS];
+
+// c_view is one per device and process: users on different streams (several contexts) are ordered through an event
+// recorded behind the last kernel that read it, under a host mutex.
+#include <mutex>
+static std::mutex g_cview_mu;
+static cudaEvent_t g_cview_free[64];
+
+static void s2_view_consts(const dfu_view& w, S2View* o) {
+  o->cu = (double)w.cu; o->fu = (double)w.fu; o->tx = (double)w.tx;
+  o->cv = (double)w.cv; o->fv = (double)w.fv; o->ty = (double)w.ty;
+  o->rfu = 1.0 / (double)w.fu; o->rfv = 1.0 / (double)w.fv;
+  for (int j = 0; j < 3; j++)
+    for (int k = 0; k < 4; k++) o->m[j][k] = (double)w.inv44[k * 4 + j];
+}
+
+// dfu_backproject (calibration_kitti.py:134-144, :89-102) on the constant-bank view: identical operation order
+__device__ __forceinline__ void s2_backproject(const S2View& c, int col, int row, float d, double& X, double& Y, double& Z) {
+  const double dd = (double)d;
+  const double xr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)col, c.cu), dd), c.fu, c.rfu), c.tx);
+  const double yr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)row, c.cv), dd), c.fv, c.rfv), c.ty);
+  X = __dadd_rn(__fma_rn(dd, c.m[0][2], __fma_rn(yr, c.m[0][1], __dmul_rn(xr, c.m[0][0]))), c.m[0][3]);
+  Y = __dadd_rn(__fma_rn(dd, c.m[1][2], __fma_rn(yr, c.m[1][1], __dmul_rn(xr, c.m[1][0]))), c.m[1][3]);
+  Z = __dadd_rn(__fma_rn(dd, c.m[2][2], __fma_rn(yr, c.m[2][1], __dmul_rn(xr, c.m[2][0]))), c.m[2][3]);
+}
+
 // returns the table key of the pixel's point or KEY_INVALID; bit flags in *st: 1 valid pixel, 2 passes height gate,
 // 4 out-of-table (should not happen)
-__device__ __forceinline__ unsigned s2_key(const dfu_view& vw, const S2Prm& q, int pix, float d, double& X, double& Y,
+__device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int pix, float d, double& X, double& Y,
                                            double& Z, unsigned& st) {
   st = 0;
   // depth[depth<0.001]=0; nonzero(); depth>0   (my_loader.py:507-509)
   if (!(d >= q.min_depth)) return KEY_INVALID;
   st |= 1u;
   const int row = pix / q.W, col = pix - row * q.W;
-  dfu_backproject(vw, col, row, d, X, Y, Z);
+  s2_backproject(vw, col, row, d, X, Y, Z);
   if (!(Z < q.max_z)) return KEY_INVALID;  // new_p[:, 2] < 1.  (:540)
   st |= 2u;
   // ---- fast path: float32 angles with a proven error bound; the float64 evaluation below is only needed when an
@@ -100,42 +134,45 @@ __device__ __forceinline__ unsigned s2_key(const dfu_view& vw, const S2Prm& q, i
   return (unsigned)(it * NF + jf);
 }
 
+// stages the view constants in shared memory, with the correctly rounded reciprocals of fu and fv (dfu_div_by)
 #define LOAD_VIEW(vw, views, v)                                            \
   __shared__ dfu_view vw;                                                  \
+  __shared__ double vw##_rcp[2];                                           \
   for (int i_ = threadIdx.x; i_ < (int)(sizeof(dfu_view) / 4); i_ += blockDim.x) \
     ((uint32_t*)&vw)[i_] = ((const uint32_t*)((views) + (v)))[i_];       \
+  if (threadIdx.x == 64) vw##_rcp[0] = __drcp_rn((double)__ldg(&(views)[v].fu)); \
+  if (threadIdx.x == 96) vw##_rcp[1] = __drcp_rn((double)__ldg(&(views)[v].fv)); \
   __syncthreads();
 
-// pass A: keys + table atomics.  stats int64 [V][4]: valid pixels, gated points, (voxels), overflow | [V][4+]: table misses
-__global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __restrict__ views, S2Prm q,
-                                                          const float* __restrict__ depth, unsigned* __restrict__ key,
-                                                          VoxCell* __restrict__ table,
-                                                          unsigned long long* __restrict__ stats) {
-  const int v = blockIdx.y;
+// pass A: keys + table atomics.  No barrier: the view constants come from the constant bank and the per-warp counts
+// (valid pixels | gated points << 8 | table misses << 16) go to warpstat, one word per warp, summed by k_blk_reduce.
+// blockIdx.y = view inside the chunk that c_view currently holds; v0 = first view of the chunk.
+__global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, S2Prm q, const float* __restrict__ depth,
+                                                          unsigned* __restrict__ key, VoxCell* __restrict__ table,
+                                                          unsigned* __restrict__ warpstat) {
+  const S2View& vw = c_view[blockIdx.y];
+  const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
-  // the depth load is issued before the view constants are staged: its latency hides behind that barrier
-  const float d = (pix < npix) ? __ldg(depth + (size_t)v * npix + pix) : 0.0f;
-  LOAD_VIEW(vw, views, v);
+  const int lane = threadIdx.x & 31;
   unsigned st = 0, k = KEY_INVALID;
   unsigned long long oz = ~0ull, oy = ~0ull;
   if (pix < npix) {
+    const float d = __ldg(depth + (size_t)v * npix + pix);
     double X, Y, Z;
     k = s2_key(vw, q, pix, d, X, Y, Z, st);
     key[(size_t)v * npix + pix] = k;
     if (k != KEY_INVALID) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
   }
   // Neighbouring pixels of a row mostly fall into the same angular voxel (a voxel spans ~2.5 pixels), so each RUN of
-  // equal keys inside the warp is reduced with shuffles and only its first lane touches the table: the L2 atomic
-  // units, not the arithmetic, bound this kernel.
+  // equal keys inside the warp is reduced with shuffles and only its first lane touches the table.
   {
-    const int lane = threadIdx.x & 31;
     const unsigned kprev = __shfl_up_sync(0xffffffffu, k, 1);
     const bool head = (lane == 0) || (k != kprev);
     const unsigned heads = __ballot_sync(0xffffffffu, head);
     const unsigned above = heads & ~((2u << lane) - 1u);
     const int end = above ? (__ffs(above) - 2) : 31;          // last lane of this lane's run
-    // runs are short (a voxel spans ~2.5 pixels): stop as soon as no lane has a partner left
+    // runs are short: stop as soon as no lane has a partner left
     for (int o = 1; o < 32 && __any_sync(0xffffffffu, lane + o <= end && k != KEY_INVALID); o <<= 1) {
       const unsigned long long z2 = __shfl_down_sync(0xffffffffu, oz, o), y2 = __shfl_down_sync(0xffffffffu, oy, o);
       if (lane + o <= end) { oz = z2 < oz ? z2 : oz; oy = y2 < oy ? y2 : oy; }
@@ -148,52 +185,73 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(const dfu_view* __rest
       atomicMin(&c->miny, oy);
     }
   }
-  int n1 = __syncthreads_count(st & 1u);
-  int n2 = __syncthreads_count(st & 2u);
-  int n4 = __syncthreads_count(st & 4u);
-  if (threadIdx.x == 0) {
-    if (n1) atomicAdd(stats + v * 8 + 0, (unsigned long long)n1);
-    if (n2) atomicAdd(stats + v * 8 + 1, (unsigned long long)n2);
-    if (n4) atomicAdd(stats + v * 8 + 4, (unsigned long long)n4);
-  }
+  const unsigned n1 = __popc(__ballot_sync(0xffffffffu, st & 1u)), n2 = __popc(__ballot_sync(0xffffffffu, st & 2u)),
+                 n4 = __popc(__ballot_sync(0xffffffffu, st & 4u));
+  if (lane == 0)
+    warpstat[((size_t)v * gridDim.x + blockIdx.x) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = n1 | (n2 << 8) | (n4 << 16);
 }
 
-// pass B: arg-min resolution; per block the number of voxel-opening pixels and their bitmap (one ballot per warp).
-// The voxel ordinal is the rank of the opening pixel in (view, pixel) order = exclusive scan of the block counts + the
-// rank inside the bitmap, so no further pass over the pixels is needed: pass C runs one thread per VOXEL.
-__global__ void __launch_bounds__(S2_THREADS) k_densify_b(const dfu_view* __restrict__ views, S2Prm q,
-                                                          const float* __restrict__ depth,
+// pass B: arg-min resolution and the bitmap of voxel-opening pixels (one ballot per warp).  The voxel ordinal is the
+// rank of the opening pixel in (view, pixel) order = exclusive scan of the block counts (k_blk_reduce) + the rank
+// inside the bitmap, so no further pass over the pixels is needed: pass C runs one thread per VOXEL.  No barrier.
+__global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, S2Prm q, const float* __restrict__ depth,
                                                           const unsigned* __restrict__ key, VoxCell* __restrict__ table,
-                                                          int32_t* __restrict__ blkcnt, unsigned* __restrict__ blkbits,
+                                                          unsigned* __restrict__ blkbits,
                                                           unsigned long long* __restrict__ stats) {
-  const int v = blockIdx.y;
+  const S2View& vw = c_view[blockIdx.y];
+  const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
   const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
-  const unsigned k0 = (pix < npix) ? __ldg(key + (size_t)v * npix + pix) : KEY_INVALID;
-  const float d = (k0 != KEY_INVALID) ? __ldg(depth + (size_t)v * npix + pix) : 0.0f;
-  LOAD_VIEW(vw, views, v);
-  bool opener = false, over = false;
-  if (pix < npix) {
-    unsigned k = k0;
-    if (k != KEY_INVALID) {
-      VoxCell* c = table + (size_t)v * NCELL + k;
-      const int row = pix / q.W, col = pix - row * q.W;
-      double X, Y, Z;
-      dfu_backproject(vw, col, row, d, X, Y, Z);
-      if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
-      if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
-      opener = (c->first == (unsigned)pix);
-      over = opener && (c->cnt + 1u > (unsigned)q.max_per_voxel);
-    }
+  const unsigned k = (pix < npix) ? __ldg(key + (size_t)v * npix + pix) : KEY_INVALID;
+  bool opener = false;
+  if (k != KEY_INVALID) {
+    const float d = __ldg(depth + (size_t)v * npix + pix);
+    VoxCell* c = table + (size_t)v * NCELL + k;
+    const int row = pix / q.W, col = pix - row * q.W;
+    double X, Y, Z;
+    s2_backproject(vw, col, row, d, X, Y, Z);
+    if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
+    if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
+    opener = (c->first == (unsigned)pix);
+    if (opener && (c->cnt + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
   }
   const unsigned bal = __ballot_sync(0xffffffffu, opener);
-  const int b = v * gridDim.x + blockIdx.x;
-  if ((threadIdx.x & 31) == 0) blkbits[(size_t)b * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
-  int n = __syncthreads_count(opener);
-  int no = __syncthreads_count(over);
+  if ((threadIdx.x & 31) == 0)
+    blkbits[((size_t)v * gridDim.x + blockIdx.x) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
+}
+
+// one thread per pixel block: openers of the block (popcount of its bitmap words) for the scan, and the per-view sums
+// of pass A's per-warp counts.  stats int64 [V][8]: 0 valid pixels, 1 gated points, 3 overflowing voxels, 4 table misses
+__global__ void __launch_bounds__(256) k_blk_reduce(int bpv, const unsigned* __restrict__ blkbits,
+                                                    const unsigned* __restrict__ warpstat, int32_t* __restrict__ blkcnt,
+                                                    unsigned long long* __restrict__ stats) {
+  const int v = blockIdx.y;
+  const int b = blockIdx.x * 256 + threadIdx.x;
+  unsigned n1 = 0, n2 = 0, n4 = 0;
+  if (b < bpv) {
+    const uint4* bb = reinterpret_cast<const uint4*>(blkbits + ((size_t)v * bpv + b) * (S2_THREADS / 32));
+    const uint4* ws = reinterpret_cast<const uint4*>(warpstat + ((size_t)v * bpv + b) * (S2_THREADS / 32));
+    int n = 0;
+#pragma unroll
+    for (int h = 0; h < S2_THREADS / 128; h++) {
+      const uint4 m = __ldg(bb + h), w = __ldg(ws + h);
+      n += __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
+      const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int j = 0; j < 4; j++) { n1 += ww[j] & 255u; n2 += (ww[j] >> 8) & 255u; n4 += (ww[j] >> 16) & 255u; }
+    }
+    blkcnt[(size_t)v * bpv + b] = n;
+  }
+  __shared__ unsigned sacc[3];
+  if (threadIdx.x < 3) sacc[threadIdx.x] = 0;
+  __syncthreads();
+  n1 = __reduce_add_sync(0xffffffffu, n1); n2 = __reduce_add_sync(0xffffffffu, n2); n4 = __reduce_add_sync(0xffffffffu, n4);
+  if ((threadIdx.x & 31) == 0) { atomicAdd(&sacc[0], n1); atomicAdd(&sacc[1], n2); atomicAdd(&sacc[2], n4); }
+  __syncthreads();
   if (threadIdx.x == 0) {
-    blkcnt[b] = n;
-    if (no) atomicAdd(stats + v * 8 + 3, (unsigned long long)no);
+    if (sacc[0]) atomicAdd(stats + v * 8 + 0, (unsigned long long)sacc[0]);
+    if (sacc[1]) atomicAdd(stats + v * 8 + 1, (unsigned long long)sacc[1]);
+    if (sacc[2]) atomicAdd(stats + v * 8 + 4, (unsigned long long)sacc[2]);
   }
 }
 
@@ -334,7 +392,9 @@ __global__ void __launch_bounds__(256) k_emit_cloud(const dfu_view* __restrict__
     if (image == nullptr) { R = G = B = 0; }
     else if (q.image_is_i32) { const int* im = (const int*)image; R = im[ip]; G = im[ip + 1]; B = im[ip + 2]; }
     else { const uint8_t* im = (const uint8_t*)image; R = im[ip]; G = im[ip + 1]; B = im[ip + 2]; }
-    o[4] = __ddiv_rn((double)R, 3.0); o[5] = __ddiv_rn((double)G, 3.0); o[6] = __ddiv_rn((double)B, 3.0);  // image/3 (:539)
+    const double third = 0x1.5555555555555p-2;   // RN(1/3)
+    o[4] = dfu_div_by((double)R, 3.0, third); o[5] = dfu_div_by((double)G, 3.0, third);   // image/3 (:539)
+    o[6] = dfu_div_by((double)B, 3.0, third);
     o[7] = 1.0;
   }
   T* dst = out + t * 8;
@@ -360,9 +420,9 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
   DFU_SLOT(ctx, blkbits, unsigned*, SL_VOXCELL, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
   DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
-  dim3 grid(bpv, V);
+  DFU_SLOT(ctx, warpstat, unsigned*, SL_WARPSTAT, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
   {
-    DFU_PROF(ctx, st, PT_DENSIFY_A);
+    DFU_PROF(ctx, st, PT_MISC);
     const size_t tbytes = (size_t)V * NCELL * sizeof(VoxCell);
     if (ctx->table_clean_ptr != (void*)table || ctx->table_clean_bytes < tbytes) {
       // first use, or the slot was re-allocated: the whole allocation becomes the clean region
@@ -371,16 +431,36 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     ctx->table_clean_ptr = nullptr;   // dirty until pass C has been queued
     ctx->table_clean_bytes = 0;
     DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
-    k_densify_a<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, stats);
-    DFU_LAUNCH_CHECK(ctx);
   }
-  {
-    DFU_PROF(ctx, st, PT_DENSIFY_B);
-    k_densify_b<<<grid, S2_THREADS, 0, st>>>(vd, q, ctx->depth, key, table, blkcnt, blkbits, stats);
-    DFU_LAUNCH_CHECK(ctx);
+  // float64 view constants (host copy owned by the context: it must outlive the asynchronous symbol copies)
+  ctx->s2_consts = realloc(ctx->s2_consts, sizeof(S2View) * (size_t)V);
+  if (!ctx->s2_consts) return dfu_set_err(ctx, DFU_ERR_CUDA, "out of host memory");
+  S2View* hc = (S2View*)ctx->s2_consts;
+  for (int v = 0; v < V; v++) s2_view_consts(ctx->views_host[v], hc + v);
+  for (int v0 = 0; v0 < V; v0 += S2_CVIEWS) {
+    const int nv = V - v0 < S2_CVIEWS ? V - v0 : S2_CVIEWS;
+    dim3 grid(bpv, nv);
+    std::lock_guard<std::mutex> lock(g_cview_mu);
+    cudaEvent_t& ev = g_cview_free[ctx->device & 63];
+    if (!ev) DFU_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    DFU_CUDA(ctx, cudaStreamWaitEvent(st, ev, 0));
+    DFU_CUDA(ctx, cudaMemcpyToSymbolAsync(c_view, hc + v0, sizeof(S2View) * (size_t)nv, 0, cudaMemcpyHostToDevice, st));
+    {
+      DFU_PROF(ctx, st, PT_DENSIFY_A);
+      k_densify_a<<<grid, S2_THREADS, 0, st>>>(v0, q, ctx->depth, key, table, warpstat);
+      DFU_LAUNCH_CHECK(ctx);
+    }
+    {
+      DFU_PROF(ctx, st, PT_DENSIFY_B);
+      k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, q, ctx->depth, key, table, blkbits, stats);
+      DFU_LAUNCH_CHECK(ctx);
+    }
+    DFU_CUDA(ctx, cudaEventRecord(ev, st));
   }
   {
     DFU_PROF(ctx, st, PT_MISC);
+    k_blk_reduce<<<dim3((bpv + 255) / 256, V), 256, 0, st>>>(bpv, blkbits, warpstat, blkcnt, stats);
+    DFU_LAUNCH_CHECK(ctx);
     int rc = dfu_exclusive_sum_i32(ctx, st, blkcnt, blkoff, (int64_t)V * bpv);
     if (rc) return rc;
     k_vox_view_offsets<<<(V + 1 + 127) / 128, 128, 0, st>>>(blkoff, V, bpv, voxoff);
@@ -526,7 +606,7 @@ __global__ void __launch_bounds__(S2_THREADS) k_bp_count(const dfu_view* __restr
       if (gate) {
         const int row = pix / q.W, col = pix - row * q.W;
         double X, Y, Z;
-        dfu_backproject(vw, col, row, d, X, Y, Z);
+        dfu_backproject_r(vw, vw_rcp[0], vw_rcp[1], col, row, d, X, Y, Z);
         ok = Z < q.max_z;
       }
     }
@@ -550,7 +630,7 @@ __global__ void __launch_bounds__(S2_THREADS) k_bp_scatter(const dfu_view* __res
     const float d = __ldg(depth + (size_t)v * npix + pix);
     if (d >= q.min_depth) {
       const int row = pix / q.W, col = pix - row * q.W;
-      dfu_backproject(vw, col, row, d, X, Y, Z);
+      dfu_backproject_r(vw, vw_rcp[0], vw_rcp[1], col, row, d, X, Y, Z);
       ok = !gate || Z < q.max_z;
     }
   }
