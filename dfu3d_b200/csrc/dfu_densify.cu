@@ -34,12 +34,14 @@ struct S2Prm {
   int H, W, Hm, Wm, image_is_i32, max_per_voxel;
   float min_depth;
   double max_z, min_theta;
+  double rW;   // RN(1 / W): row = floor((pix + 0.5) * rW) is exact for pix < 2^31, W < 2^20 (error 2^-21 << 0.5 / W)
 };
 
 static S2Prm make_s2(const dfu_fusion_params* p) {
   S2Prm s;
   s.H = p->H; s.W = p->W; s.Hm = p->Hm; s.Wm = p->Wm; s.image_is_i32 = p->image_is_i32;
   s.max_per_voxel = p->max_per_voxel; s.min_depth = p->min_depth; s.max_z = p->max_z; s.min_theta = p->min_theta;
+  s.rW = 1.0 / (double)p->W;
   return s;
 }
 
@@ -68,10 +70,18 @@ static void s2_view_consts(const dfu_view& w, S2View* o) {
 }
 
 // dfu_backproject (calibration_kitti.py:134-144, :89-102) on the constant-bank view: identical operation order
-__device__ __forceinline__ void s2_backproject(const S2View& c, int col, int row, float d, double& X, double& Y, double& Z) {
+// pixel index -> (row, col) as float64 values (the back-projection needs them as float64 anyway): one conversion, one
+// FMA, one floor, one FMA instead of an integer division by a run-time W and two conversions
+__device__ __forceinline__ void s2_rowcol(const S2Prm& q, int pix, double& row, double& col) {
+  const double p = (double)pix;
+  row = floor(__fma_rn(p, q.rW, 0.5 * q.rW));
+  col = __fma_rn(-row, (double)q.W, p);       // exact: integers below 2^53
+}
+
+__device__ __forceinline__ void s2_backproject(const S2View& c, double col, double row, float d, double& X, double& Y, double& Z) {
   const double dd = (double)d;
-  const double xr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)col, c.cu), dd), c.fu, c.rfu), c.tx);
-  const double yr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn((double)row, c.cv), dd), c.fv, c.rfv), c.ty);
+  const double xr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn(col, c.cu), dd), c.fu, c.rfu), c.tx);
+  const double yr = __dadd_rn(dfu_div_by(__dmul_rn(__dsub_rn(row, c.cv), dd), c.fv, c.rfv), c.ty);
   X = __dadd_rn(__fma_rn(dd, c.m[0][2], __fma_rn(yr, c.m[0][1], __dmul_rn(xr, c.m[0][0]))), c.m[0][3]);
   Y = __dadd_rn(__fma_rn(dd, c.m[1][2], __fma_rn(yr, c.m[1][1], __dmul_rn(xr, c.m[1][0]))), c.m[1][3]);
   Z = __dadd_rn(__fma_rn(dd, c.m[2][2], __fma_rn(yr, c.m[2][1], __dmul_rn(xr, c.m[2][0]))), c.m[2][3]);
@@ -85,7 +95,8 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
   // depth[depth<0.001]=0; nonzero(); depth>0   (my_loader.py:507-509)
   if (!(d >= q.min_depth)) return KEY_INVALID;
   st |= 1u;
-  const int row = pix / q.W, col = pix - row * q.W;
+  double row, col;
+  s2_rowcol(q, pix, row, col);
   s2_backproject(vw, col, row, d, X, Y, Z);
   if (!(Z < q.max_z)) return KEY_INVALID;  // new_p[:, 2] < 1.  (:540)
   st |= 2u;
@@ -147,77 +158,92 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
 // pass A: keys + table atomics.  No barrier: the view constants come from the constant bank and the per-warp counts
 // (valid pixels | gated points << 8 | table misses << 16) go to warpstat, one word per warp, summed by k_blk_reduce.
 // blockIdx.y = view inside the chunk that c_view currently holds; v0 = first view of the chunk.
-__global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, S2Prm q, const float* __restrict__ depth,
+#define S2_TILES 4   /* 256-pixel tiles per CTA: the next tile's depth is in flight while this one is computed */
+__global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
                                                           unsigned* __restrict__ key, VoxCell* __restrict__ table,
                                                           unsigned* __restrict__ warpstat) {
   const S2View& vw = c_view[blockIdx.y];
   const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
-  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  unsigned st = 0, k = KEY_INVALID;
-  unsigned long long oz = ~0ull, oy = ~0ull;
-  if (pix < npix) {
-    const float d = __ldg(depth + (size_t)v * npix + pix);
-    double X, Y, Z;
-    k = s2_key(vw, q, pix, d, X, Y, Z, st);
-    key[(size_t)v * npix + pix] = k;
-    if (k != KEY_INVALID) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
-  }
-  // Neighbouring pixels of a row mostly fall into the same angular voxel (a voxel spans ~2.5 pixels), so each RUN of
-  // equal keys inside the warp is reduced with shuffles and only its first lane touches the table.
-  {
-    const unsigned kprev = __shfl_up_sync(0xffffffffu, k, 1);
-    const bool head = (lane == 0) || (k != kprev);
-    const unsigned heads = __ballot_sync(0xffffffffu, head);
-    const unsigned above = heads & ~((2u << lane) - 1u);
-    const int end = above ? (__ffs(above) - 2) : 31;          // last lane of this lane's run
-    // runs are short: stop as soon as no lane has a partner left
-    for (int o = 1; o < 32 && __any_sync(0xffffffffu, lane + o <= end && k != KEY_INVALID); o <<= 1) {
-      const unsigned long long z2 = __shfl_down_sync(0xffffffffu, oz, o), y2 = __shfl_down_sync(0xffffffffu, oy, o);
-      if (lane + o <= end) { oz = z2 < oz ? z2 : oz; oy = y2 < oy ? y2 : oy; }
+  const float* dv = depth + (size_t)v * npix;
+  int pix = blockIdx.x * (S2_TILES * S2_THREADS) + threadIdx.x;
+  float dn = (pix < npix) ? __ldg(dv + pix) : 0.0f;
+#pragma unroll 1
+  for (int j = 0; j < S2_TILES; j++, pix += S2_THREADS) {
+    const int blk = blockIdx.x * S2_TILES + j;
+    if (blk >= bpv) break;
+    const float d = dn;
+    if (j + 1 < S2_TILES) dn = (pix + S2_THREADS < npix) ? __ldg(dv + pix + S2_THREADS) : 0.0f;
+    unsigned st = 0, k = KEY_INVALID;
+    unsigned long long oz = ~0ull, oy = ~0ull;
+    if (pix < npix) {
+      double X, Y, Z;
+      k = s2_key(vw, q, pix, d, X, Y, Z, st);
+      key[(size_t)v * npix + pix] = k;
+      if (k != KEY_INVALID) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
     }
-    if (head && k != KEY_INVALID) {
-      VoxCell* c = table + (size_t)v * NCELL + k;
-      atomicMin(&c->first, (unsigned)pix);                    // pixels ascend inside a run: the head is its minimum
-      atomicAdd(&c->cnt, (unsigned)(end - lane + 1));
-      atomicMin(&c->minz, oz);
-      atomicMin(&c->miny, oy);
+    // Neighbouring pixels of a row mostly fall into the same angular voxel (a voxel spans ~2.5 pixels), so each RUN of
+    // equal keys inside the warp is reduced with shuffles and only its first lane touches the table.
+    {
+      const unsigned kprev = __shfl_up_sync(0xffffffffu, k, 1);
+      const bool head = (lane == 0) || (k != kprev);
+      const unsigned heads = __ballot_sync(0xffffffffu, head);
+      const unsigned above = heads & ~((2u << lane) - 1u);
+      const int end = above ? (__ffs(above) - 2) : 31;          // last lane of this lane's run
+      // runs are short: stop as soon as no lane has a partner left
+      for (int o = 1; o < 32 && __any_sync(0xffffffffu, lane + o <= end && k != KEY_INVALID); o <<= 1) {
+        const unsigned long long z2 = __shfl_down_sync(0xffffffffu, oz, o), y2 = __shfl_down_sync(0xffffffffu, oy, o);
+        if (lane + o <= end) { oz = z2 < oz ? z2 : oz; oy = y2 < oy ? y2 : oy; }
+      }
+      if (head && k != KEY_INVALID) {
+        VoxCell* c = table + (size_t)v * NCELL + k;
+        atomicMin(&c->first, (unsigned)pix);                    // pixels ascend inside a run: the head is its minimum
+        atomicAdd(&c->cnt, (unsigned)(end - lane + 1));
+        atomicMin(&c->minz, oz);
+        atomicMin(&c->miny, oy);
+      }
     }
+    const unsigned n1 = __popc(__ballot_sync(0xffffffffu, st & 1u)), n2 = __popc(__ballot_sync(0xffffffffu, st & 2u)),
+                   n4 = __popc(__ballot_sync(0xffffffffu, st & 4u));
+    if (lane == 0) warpstat[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = n1 | (n2 << 8) | (n4 << 16);
   }
-  const unsigned n1 = __popc(__ballot_sync(0xffffffffu, st & 1u)), n2 = __popc(__ballot_sync(0xffffffffu, st & 2u)),
-                 n4 = __popc(__ballot_sync(0xffffffffu, st & 4u));
-  if (lane == 0)
-    warpstat[((size_t)v * gridDim.x + blockIdx.x) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = n1 | (n2 << 8) | (n4 << 16);
 }
 
 // pass B: arg-min resolution and the bitmap of voxel-opening pixels (one ballot per warp).  The voxel ordinal is the
 // rank of the opening pixel in (view, pixel) order = exclusive scan of the block counts (k_blk_reduce) + the rank
 // inside the bitmap, so no further pass over the pixels is needed: pass C runs one thread per VOXEL.  No barrier.
-__global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, S2Prm q, const float* __restrict__ depth,
+__global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
                                                           const unsigned* __restrict__ key, VoxCell* __restrict__ table,
                                                           unsigned* __restrict__ blkbits,
                                                           unsigned long long* __restrict__ stats) {
   const S2View& vw = c_view[blockIdx.y];
   const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
-  const int pix = blockIdx.x * S2_THREADS + threadIdx.x;
-  const unsigned k = (pix < npix) ? __ldg(key + (size_t)v * npix + pix) : KEY_INVALID;
-  bool opener = false;
-  if (k != KEY_INVALID) {
-    const float d = __ldg(depth + (size_t)v * npix + pix);
-    VoxCell* c = table + (size_t)v * NCELL + k;
-    const int row = pix / q.W, col = pix - row * q.W;
-    double X, Y, Z;
-    s2_backproject(vw, col, row, d, X, Y, Z);
-    if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
-    if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
-    opener = (c->first == (unsigned)pix);
-    if (opener && (c->cnt + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
+  const unsigned* kv = key + (size_t)v * npix;
+  int pix = blockIdx.x * (S2_TILES * S2_THREADS) + threadIdx.x;
+  unsigned kn = (pix < npix) ? __ldg(kv + pix) : KEY_INVALID;
+#pragma unroll 1
+  for (int j = 0; j < S2_TILES; j++, pix += S2_THREADS) {
+    const int blk = blockIdx.x * S2_TILES + j;
+    if (blk >= bpv) break;
+    const unsigned k = kn;
+    if (j + 1 < S2_TILES) kn = (pix + S2_THREADS < npix) ? __ldg(kv + pix + S2_THREADS) : KEY_INVALID;
+    bool opener = false;
+    if (k != KEY_INVALID) {
+      const float d = __ldg(depth + (size_t)v * npix + pix);
+      VoxCell* c = table + (size_t)v * NCELL + k;
+      double row, col, X, Y, Z;
+      s2_rowcol(q, pix, row, col);
+      s2_backproject(vw, col, row, d, X, Y, Z);
+      if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
+      if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
+      opener = (c->first == (unsigned)pix);
+      if (opener && (c->cnt + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, opener);
+    if ((threadIdx.x & 31) == 0) blkbits[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
   }
-  const unsigned bal = __ballot_sync(0xffffffffu, opener);
-  if ((threadIdx.x & 31) == 0)
-    blkbits[((size_t)v * gridDim.x + blockIdx.x) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
 }
 
 // one thread per pixel block: openers of the block (popcount of its bitmap words) for the scan, and the per-view sums
@@ -439,7 +465,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   for (int v = 0; v < V; v++) s2_view_consts(ctx->views_host[v], hc + v);
   for (int v0 = 0; v0 < V; v0 += S2_CVIEWS) {
     const int nv = V - v0 < S2_CVIEWS ? V - v0 : S2_CVIEWS;
-    dim3 grid(bpv, nv);
+    dim3 grid((bpv + S2_TILES - 1) / S2_TILES, nv);
     std::lock_guard<std::mutex> lock(g_cview_mu);
     cudaEvent_t& ev = g_cview_free[ctx->device & 63];
     if (!ev) DFU_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -447,12 +473,12 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     DFU_CUDA(ctx, cudaMemcpyToSymbolAsync(c_view, hc + v0, sizeof(S2View) * (size_t)nv, 0, cudaMemcpyHostToDevice, st));
     {
       DFU_PROF(ctx, st, PT_DENSIFY_A);
-      k_densify_a<<<grid, S2_THREADS, 0, st>>>(v0, q, ctx->depth, key, table, warpstat);
+      k_densify_a<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, warpstat);
       DFU_LAUNCH_CHECK(ctx);
     }
     {
       DFU_PROF(ctx, st, PT_DENSIFY_B);
-      k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, q, ctx->depth, key, table, blkbits, stats);
+      k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats);
       DFU_LAUNCH_CHECK(ctx);
     }
     DFU_CUDA(ctx, cudaEventRecord(ev, st));
