@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'csrc', 'libdfu3d.so')
+# DFU3D_LIB: another build of the same library (kernel tuning variants, tools/variants.py)
+LIB_PATH = os.environ.get('DFU3D_LIB') or os.path.join(_HERE, 'csrc', 'libdfu3d.so')
 
 MAX_INSTANCES = 32
 BOX_DOUBLES = 24

@@ -78,9 +78,9 @@ enum {
   SL_VIEWS = 0, SL_FLAGS, SL_PIX, SL_LABEL, SL_BLKCNT, SL_BLKOFF, SL_CUBTMP, SL_FLIST, SL_ALIST, SL_BLABEL,
   SL_KEY, SL_TABLE, SL_VOXCNT, SL_VOXOFF, SL_REPZ, SL_REPY, SL_REPY_XYZ, SL_REPY_LABEL, SL_REPZ_XYZ, SL_STATS,
   SL_SEGCNT, SL_SEGOFF, SL_IPARAMS, SL_ANGLES, SL_ISCRATCH_D, SL_ISCRATCH_I, SL_BOXES, SL_BOXCNT, SL_SEGOUT,
-  SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11, SL_VOXCELL, SL_WARPSTAT
+  SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11, SL_VOXCELL, SL_WARPSTAT, SL_AMBQ
 };
-static_assert(SL_WARPSTAT < 44, "SL_* ids must stay below the operator slot ranges");
+static_assert(SL_AMBQ < 44, "SL_* ids must stay below the operator slot ranges");
 
 int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...);
 void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes);      // NULL on failure (error recorded)

@@ -19,6 +19,8 @@
 #define NF 1572
 #define NCELL (NT * NF)
 #define KEY_INVALID 0xFFFFFFFFu
+#define KEY_AMBIG 0xFFFFFFFEu   /* pass A only: resolved by k_densify_amb before pass B */
+#define S2_NQ 64                /* sub-queues of ambiguous pixels (spreads the counter atomics) */
 #define S2_EPS 2e-6f   /* rad: twice the error bound of the float32 angle evaluation in s2_key */
 
 struct __align__(32) VoxCell {
@@ -87,8 +89,33 @@ __device__ __forceinline__ void s2_backproject(const S2View& c, double col, doub
   Z = __dadd_rn(__fma_rn(dd, c.m[2][2], __fma_rn(yr, c.m[2][1], __dmul_rn(xr, c.m[2][0]))), c.m[2][3]);
 }
 
-// returns the table key of the pixel's point or KEY_INVALID; bit flags in *st: 1 valid pixel, 2 passes height gate,
-// 4 out-of-table (should not happen)
+// to_sphere_coords (:166-180) + spconv v1 voxel coordinates with float32 constants (oracle/fakes.py), float64 as numpy
+// evaluates them.  Returns the table key or KEY_INVALID; *miss: inside the voxel range but outside the table window.
+__device__ __noinline__ unsigned s2_key_exact(const S2Prm& q, double X, double Y, double Z, bool& miss) {
+  miss = false;
+  double r = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(X, X), __dmul_rn(Y, Y)), __dmul_rn(Z, Z)));
+  double theta = acos(__ddiv_rn(Z, r));
+  double fan = atan(__ddiv_rn(Y, X));
+  if (!(theta > q.min_theta)) return KEY_INVALID;
+  const double vs = (double)0.002f;
+  double cr = floor(__ddiv_rn(__dadd_rn(r, 100.0), 200.0));
+  double ct = floor(__ddiv_rn(__dadd_rn(theta, 5.0), vs));
+  double cf = floor(__ddiv_rn(__dadd_rn(fan, 5.0), vs));
+  if (!(cr >= 0.0 && cr < 1.0 && ct >= 0.0 && ct < 5000.0 && cf >= 0.0 && cf < 5000.0)) return KEY_INVALID;
+  int it = (int)ct - CT0, jf = (int)cf - CF0;
+  if (it < 0 || it >= NT || jf < 0 || jf >= NF) {
+    miss = true;
+    return KEY_INVALID;
+  }
+  return (unsigned)(it * NF + jf);
+}
+
+// Pass A's key: the table key of the pixel's point, KEY_INVALID, or KEY_AMBIG when the float32 angles lie within
+// S2_EPS of a bin edge (or of the theta gate) and the float64 evaluation has to decide (~0.4 % of the points: those go
+// to a queue and are resolved densely by k_densify_amb instead of stalling 31 idle lanes of this warp).
+// bit flags in st: 1 valid pixel, 2 passes height gate, 4 out-of-table (should not happen).
+// atan2f(rho, z) equals acos(z / r) on [0, pi] and is well conditioned everywhere; CUDA's atan2f / atanf are accurate to
+// 3 / 1 ulp, the float32 inputs carry <= 2 ulp: |error| < 1e-6 rad, half of S2_EPS.
 __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int pix, float d, double& X, double& Y,
                                            double& Z, unsigned& st) {
   st = 0;
@@ -100,44 +127,20 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
   s2_backproject(vw, col, row, d, X, Y, Z);
   if (!(Z < q.max_z)) return KEY_INVALID;  // new_p[:, 2] < 1.  (:540)
   st |= 2u;
-  // ---- fast path: float32 angles with a proven error bound; the float64 evaluation below is only needed when an
-  // angle lies within S2_EPS of a bin edge (or of the theta gate), i.e. for ~0.4 % of the points.  atan2f(rho, z)
-  // equals acos(z / r) on [0, pi] and is well conditioned everywhere; CUDA's atan2f / atanf are accurate to 3 / 1 ulp,
-  // the float32 inputs carry <= 2 ulp: |error| < 1e-6 rad, half of S2_EPS.
-  {
-    const float Xf = (float)X, Yf = (float)Y, Zf = (float)Z;
-    const float rho = sqrtf(__fmaf_rn(Xf, Xf, Yf * Yf));
-    const float rf = sqrtf(__fmaf_rn(rho, rho, Zf * Zf));
-    const float th = atan2f(rho, Zf);
-    const float fa = atanf(__fdividef(Yf, Xf));
-    const double inv_vs = 1.0 / (double)0.002f;
-    const double tt = ((double)th + 5.0) * inv_vs, tf = ((double)fa + 5.0) * inv_vs;
-    const double ft = tt - floor(tt), ff = tf - floor(tf);
-    const double D = (double)S2_EPS * inv_vs;
-    const bool sure = (rf < 99.0f) && (rf > 1e-3f) && (fabsf(Xf) > 1e-6f) && (fabsf(th - (float)q.min_theta) > S2_EPS) &&
-                      (ft > D) && (ft < 1.0 - D) && (ff > D) && (ff < 1.0 - D);
-    if (sure) {
-      if (!(th > (float)q.min_theta)) return KEY_INVALID;
-      const int it = (int)tt - CT0, jf = (int)tf - CF0;
-      if (it < 0 || it >= NT || jf < 0 || jf >= NF) {
-        st |= 4u;
-        return KEY_INVALID;
-      }
-      return (unsigned)(it * NF + jf);
-    }
-  }
-  // ---- exact path: to_sphere_coords (:166-180) in float64
-  double r = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(X, X), __dmul_rn(Y, Y)), __dmul_rn(Z, Z)));
-  double theta = acos(__ddiv_rn(Z, r));
-  double fan = atan(__ddiv_rn(Y, X));
-  if (!(theta > q.min_theta)) return KEY_INVALID;
-  // spconv v1 voxel coordinates with float32 constants (oracle/fakes.py)
-  const double vs = (double)0.002f;
-  double cr = floor(__ddiv_rn(__dadd_rn(r, 100.0), 200.0));
-  double ct = floor(__ddiv_rn(__dadd_rn(theta, 5.0), vs));
-  double cf = floor(__ddiv_rn(__dadd_rn(fan, 5.0), vs));
-  if (!(cr >= 0.0 && cr < 1.0 && ct >= 0.0 && ct < 5000.0 && cf >= 0.0 && cf < 5000.0)) return KEY_INVALID;
-  int it = (int)ct - CT0, jf = (int)cf - CF0;
+  const float Xf = (float)X, Yf = (float)Y, Zf = (float)Z;
+  const float rho = sqrtf(__fmaf_rn(Xf, Xf, Yf * Yf));
+  const float rf = sqrtf(__fmaf_rn(rho, rho, Zf * Zf));
+  const float th = atan2f(rho, Zf);
+  const float fa = atanf(__fdividef(Yf, Xf));
+  const double inv_vs = 1.0 / (double)0.002f;
+  const double tt = ((double)th + 5.0) * inv_vs, tf = ((double)fa + 5.0) * inv_vs;
+  const double ft = tt - floor(tt), ff = tf - floor(tf);
+  const double D = (double)S2_EPS * inv_vs;
+  const bool sure = (rf < 99.0f) && (rf > 1e-3f) && (fabsf(Xf) > 1e-6f) && (fabsf(th - (float)q.min_theta) > S2_EPS) &&
+                    (ft > D) && (ft < 1.0 - D) && (ff > D) && (ff < 1.0 - D);
+  if (!sure) return KEY_AMBIG;
+  if (!(th > (float)q.min_theta)) return KEY_INVALID;
+  const int it = (int)tt - CT0, jf = (int)tf - CF0;
   if (it < 0 || it >= NT || jf < 0 || jf >= NF) {
     st |= 4u;
     return KEY_INVALID;
@@ -158,10 +161,17 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
 // pass A: keys + table atomics.  No barrier: the view constants come from the constant bank and the per-warp counts
 // (valid pixels | gated points << 8 | table misses << 16) go to warpstat, one word per warp, summed by k_blk_reduce.
 // blockIdx.y = view inside the chunk that c_view currently holds; v0 = first view of the chunk.
-#define S2_TILES 4   /* 256-pixel tiles per CTA: the next tile's depth is in flight while this one is computed */
-__global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
+#ifndef S2_TILES
+#define S2_TILES 8
+#endif
+#ifndef S2_MINB
+#define S2_MINB 6
+#endif
+/* S2_TILES 256-pixel tiles per CTA: the next tile's depth is in flight while this one is computed */
+__global__ void __launch_bounds__(S2_THREADS, S2_MINB) k_densify_a(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
                                                           unsigned* __restrict__ key, VoxCell* __restrict__ table,
-                                                          unsigned* __restrict__ warpstat) {
+                                                          unsigned* __restrict__ warpstat, uint2* __restrict__ ambq,
+                                                          unsigned* __restrict__ ambcnt, unsigned capq) {
   const S2View& vw = c_view[blockIdx.y];
   const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
@@ -181,7 +191,21 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, int bpv, S2Prm
       double X, Y, Z;
       k = s2_key(vw, q, pix, d, X, Y, Z, st);
       key[(size_t)v * npix + pix] = k;
-      if (k != KEY_INVALID) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
+      if (k < KEY_AMBIG) { oz = dfu_order_f64(Z); oy = dfu_order_f64(Y); }
+    }
+    {
+      const unsigned amb = __ballot_sync(0xffffffffu, k == KEY_AMBIG);
+      if (amb) {
+        const int qi = (blockIdx.x + blockIdx.y) & (S2_NQ - 1);
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(ambcnt + qi, (unsigned)__popc(amb));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (k == KEY_AMBIG) {
+          const unsigned slot = base + dfu_warp_excl(amb, lane);
+          if (slot < capq) ambq[(size_t)qi * capq + slot] = make_uint2((unsigned)v, (unsigned)pix);
+          k = KEY_INVALID;      // not part of any run below
+        }
+      }
     }
     // Neighbouring pixels of a row mostly fall into the same angular voxel (a voxel spans ~2.5 pixels), so each RUN of
     // equal keys inside the warp is reduced with shuffles and only its first lane touches the table.
@@ -207,6 +231,49 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_a(int v0, int bpv, S2Prm
     const unsigned n1 = __popc(__ballot_sync(0xffffffffu, st & 1u)), n2 = __popc(__ballot_sync(0xffffffffu, st & 2u)),
                    n4 = __popc(__ballot_sync(0xffffffffu, st & 4u));
     if (lane == 0) warpstat[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = n1 | (n2 << 8) | (n4 << 16);
+  }
+}
+
+// The ambiguous pixels of pass A, one thread each: exact float64 key, key array patched, table atomics.  Normally they
+// come from the sub-queues; if any sub-queue overflowed (pathological input), the key array is scanned for KEY_AMBIG
+// instead.  grid (S2_NQ, S2_AMB_Y).
+#define S2_AMB_Y 16
+__device__ __forceinline__ void s2_resolve_amb(const dfu_view* __restrict__ views, const S2Prm& q, int v, int pix, int npix,
+                                               const float* __restrict__ depth, unsigned* __restrict__ key,
+                                               VoxCell* __restrict__ table, unsigned long long* __restrict__ stats) {
+  const int row = pix / q.W, col = pix - row * q.W;
+  double X, Y, Z;
+  dfu_backproject(views[v], col, row, __ldg(depth + (size_t)v * npix + pix), X, Y, Z);
+  bool miss;
+  const unsigned k = s2_key_exact(q, X, Y, Z, miss);
+  key[(size_t)v * npix + pix] = k;
+  if (miss) atomicAdd(stats + v * 8 + 4, 1ull);
+  if (k != KEY_INVALID) {
+    VoxCell* c = table + (size_t)v * NCELL + k;
+    atomicMin(&c->first, (unsigned)pix);
+    atomicAdd(&c->cnt, 1u);
+    atomicMin(&c->minz, dfu_order_f64(Z));
+    atomicMin(&c->miny, dfu_order_f64(Y));
+  }
+}
+
+__global__ void __launch_bounds__(256) k_densify_amb(const dfu_view* __restrict__ views, S2Prm q, int V,
+                                                     const float* __restrict__ depth, unsigned* __restrict__ key,
+                                                     VoxCell* __restrict__ table, const uint2* __restrict__ ambq,
+                                                     const unsigned* __restrict__ ambcnt, unsigned capq,
+                                                     unsigned long long* __restrict__ stats) {
+  const int npix = q.H * q.W;
+  const int over = __syncthreads_or(threadIdx.x < S2_NQ && ambcnt[threadIdx.x] > capq);
+  if (!over) {
+    const unsigned n = ambcnt[blockIdx.x];
+    for (unsigned i = blockIdx.y * 256 + threadIdx.x; i < n; i += S2_AMB_Y * 256) {
+      const uint2 e = ambq[(size_t)blockIdx.x * capq + i];
+      s2_resolve_amb(views, q, (int)e.x, (int)e.y, npix, depth, key, table, stats);
+    }
+  } else {
+    const int64_t total = (int64_t)V * npix;
+    for (int64_t g = ((int64_t)blockIdx.y * S2_NQ + blockIdx.x) * 256 + threadIdx.x; g < total; g += (int64_t)S2_NQ * S2_AMB_Y * 256)
+      if (key[g] == KEY_AMBIG) s2_resolve_amb(views, q, (int)(g / npix), (int)(g % npix), npix, depth, key, table, stats);
   }
 }
 
@@ -447,6 +514,10 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, blkbits, unsigned*, SL_VOXCELL, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
   DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
   DFU_SLOT(ctx, warpstat, unsigned*, SL_WARPSTAT, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
+  // queue of pixels whose float32 angles are too close to a bin edge: 1/64 of the pixels (8x the expected 0.2 %)
+  const unsigned capq = (unsigned)(((int64_t)V * npix / 64 + S2_NQ - 1) / S2_NQ + 64);
+  DFU_SLOT(ctx, ambq, uint2*, SL_AMBQ, (size_t)S2_NQ * capq * sizeof(uint2) + S2_NQ * sizeof(unsigned));
+  unsigned* ambcnt = (unsigned*)(ambq + (size_t)S2_NQ * capq);
   {
     DFU_PROF(ctx, st, PT_MISC);
     const size_t tbytes = (size_t)V * NCELL * sizeof(VoxCell);
@@ -457,6 +528,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     ctx->table_clean_ptr = nullptr;   // dirty until pass C has been queued
     ctx->table_clean_bytes = 0;
     DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
+    DFU_CUDA(ctx, cudaMemsetAsync(ambcnt, 0, S2_NQ * sizeof(unsigned), st));
   }
   // float64 view constants (host copy owned by the context: it must outlive the asynchronous symbol copies)
   ctx->s2_consts = realloc(ctx->s2_consts, sizeof(S2View) * (size_t)V);
@@ -473,14 +545,31 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     DFU_CUDA(ctx, cudaMemcpyToSymbolAsync(c_view, hc + v0, sizeof(S2View) * (size_t)nv, 0, cudaMemcpyHostToDevice, st));
     {
       DFU_PROF(ctx, st, PT_DENSIFY_A);
-      k_densify_a<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, warpstat);
+      k_densify_a<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, warpstat, ambq, ambcnt, capq);
       DFU_LAUNCH_CHECK(ctx);
     }
-    {
+    if (v0 + nv >= V) {   // all keys written: resolve the queued pixels before the first pass B
+      DFU_PROF(ctx, st, PT_DENSIFY_A);
+      k_densify_amb<<<dim3(S2_NQ, S2_AMB_Y), 256, 0, st>>>(vd, q, V, ctx->depth, key, table, ambq, ambcnt, capq, stats);
+      DFU_LAUNCH_CHECK(ctx);
+    }
+    if (V <= S2_CVIEWS) {
       DFU_PROF(ctx, st, PT_DENSIFY_B);
       k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats);
       DFU_LAUNCH_CHECK(ctx);
     }
+    DFU_CUDA(ctx, cudaEventRecord(ev, st));
+  }
+  for (int v0 = 0; V > S2_CVIEWS && v0 < V; v0 += S2_CVIEWS) {   // several chunks: pass B needs its constants again
+    const int nv = V - v0 < S2_CVIEWS ? V - v0 : S2_CVIEWS;
+    dim3 grid((bpv + S2_TILES - 1) / S2_TILES, nv);
+    std::lock_guard<std::mutex> lock(g_cview_mu);
+    cudaEvent_t& ev = g_cview_free[ctx->device & 63];
+    DFU_CUDA(ctx, cudaStreamWaitEvent(st, ev, 0));
+    DFU_CUDA(ctx, cudaMemcpyToSymbolAsync(c_view, hc + v0, sizeof(S2View) * (size_t)nv, 0, cudaMemcpyHostToDevice, st));
+    DFU_PROF(ctx, st, PT_DENSIFY_B);
+    k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats);
+    DFU_LAUNCH_CHECK(ctx);
     DFU_CUDA(ctx, cudaEventRecord(ev, st));
   }
   {
