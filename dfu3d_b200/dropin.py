@@ -513,3 +513,35 @@ def crop_gt_points(points, gt_boxes):
     to `<idx>_<name>_<i>.bin`, and the [M+1] offsets of their concatenation (create_integrated_database.py:26-45)."""
     rows, off = ops.crop_boxes(np.ascontiguousarray(points, np.float32), gt_boxes)
     return [rows[off[i]:off[i + 1]] for i in range(len(off) - 1)], off
+
+
+# ---- consumer side of the 8-column cloud (SURVEY.md 8(f) f3) ---------------------------------------------------------
+def mask_points_by_range(points, limit_range):
+    """pcdet/utils/common_utils.py:78-81 (x and y only, inclusive): boolean mask, host arithmetic on the caller's array —
+    the fused device version is ops.split_cloud(cloud, point_cloud_range)."""
+    return (points[:, 0] >= limit_range[0]) & (points[:, 0] <= limit_range[3]) \
+        & (points[:, 1] >= limit_range[1]) & (points[:, 1] <= limit_range[4])
+
+
+class VoxelGeneratorWrapper():
+    """pcdet/datasets/processor/data_processor_virtual.py:16-58 — same constructor keywords and `generate(points)`
+    -> (voxels [V, max_points, C], coordinates [V, 3] zyx, num_points [V]); the spconv call is replaced by the GPU
+    voxeliser (dfu_voxelize_sync).  numpy in -> numpy out, CUDA tensor in -> CUDA tensors out."""
+
+    def __init__(self, vsize_xyz, coors_range_xyz, num_point_features, max_num_points_per_voxel, max_num_voxels):
+        self.vsize_xyz = vsize_xyz
+        self.coors_range_xyz = coors_range_xyz
+        self.num_point_features = num_point_features
+        self.max_num_points_per_voxel = max_num_points_per_voxel
+        self.max_num_voxels = max_num_voxels
+
+    def generate(self, points):
+        assert points.shape[1] == self.num_point_features
+        return ops.voxelize(points, self.vsize_xyz, self.coors_range_xyz, self.max_num_points_per_voxel, self.max_num_voxels)
+
+
+def split_modalities(points, point_cloud_range=None):
+    """The `points[:, -1] == 2` / `== 1` split of pcdet/datasets/dataset_virtual.py:270-296: returns (points, points_mm)
+    = (LiDAR rows, pseudo rows) in input order; with `point_cloud_range` the x/y mask of
+    mask_points_and_boxes_outside_range (data_processor_virtual.py:69-77) is applied to both in the same pass."""
+    return ops.split_cloud(points, point_cloud_range)

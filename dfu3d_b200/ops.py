@@ -199,3 +199,37 @@ def crop_boxes(points, boxes, ctx=None):
     rows = torch.empty((max(int(off[-1]), 1), Cc), dtype=torch.float32, device=ctx.device)
     ctx.check(ctx.lib.dfu_crop_boxes_sync(*args, _lib.dptr(rows), rows.shape[0], _lib.hptr(off)))
     return _out(rows[:int(off[-1])], as_np), off
+
+
+def split_cloud(cloud, point_cloud_range=None, ctx=None):
+    """The modality split the detector's dataset does on the 8-column cloud (pcdet/datasets/dataset_virtual.py:270-296)
+    with the x/y range mask of mask_points_and_boxes_outside_range: returns (lidar_rows, pseudo_rows), input order."""
+    ctx = ctx or _lib.default_context(0)
+    c, as_np = _dev_f32(ctx, cloud)
+    n, Cc = c.shape
+    o0 = torch.empty((max(n, 1), Cc), dtype=torch.float32, device=ctx.device)
+    o1 = torch.empty((max(n, 1), Cc), dtype=torch.float32, device=ctx.device)
+    cnt = np.zeros(2, np.int64)
+    rg = None if point_cloud_range is None else np.ascontiguousarray(np.asarray(point_cloud_range, np.float32).reshape(6))
+    ctx.check(ctx.lib.dfu_split_cloud_sync(ctx.h, ctx.stream, _lib.dptr(c) if n else None, Cc, n,
+                                           _lib.hptr(rg) if rg is not None else None, _lib.dptr(o0), _lib.dptr(o1), _lib.hptr(cnt)))
+    return _out(o0[:int(cnt[0])], as_np), _out(o1[:int(cnt[1])], as_np)
+
+
+def voxelize(points, voxel_size, point_cloud_range, max_points_per_voxel, max_voxels, ctx=None):
+    """VoxelGeneratorWrapper.generate (pcdet/datasets/processor/data_processor_virtual.py:16-58): returns
+    (voxels [V, max_points, C] float32, coordinates [V, 3] int32 (z, y, x), num_points [V] int32)."""
+    ctx = ctx or _lib.default_context(0)
+    p, as_np = _dev_f32(ctx, points)
+    n, Cc = p.shape
+    vs = np.ascontiguousarray(np.asarray(voxel_size, np.float32).reshape(3))
+    rg = np.ascontiguousarray(np.asarray(point_cloud_range, np.float32).reshape(6))
+    vox = torch.empty((max_voxels, max_points_per_voxel, Cc), dtype=torch.float32, device=ctx.device)
+    coords = torch.empty((max_voxels, 3), dtype=torch.int32, device=ctx.device)
+    num = torch.empty((max_voxels,), dtype=torch.int32, device=ctx.device)
+    nv = np.zeros(1, np.int64)
+    ctx.check(ctx.lib.dfu_voxelize_sync(ctx.h, ctx.stream, _lib.dptr(p) if n else None, Cc, n, _lib.hptr(vs), _lib.hptr(rg),
+                                        int(max_points_per_voxel), int(max_voxels), _lib.dptr(vox), _lib.dptr(coords),
+                                        _lib.dptr(num), _lib.hptr(nv)))
+    v = int(nv[0])
+    return _out(vox[:v], as_np), _out(coords[:v], as_np), _out(num[:v], as_np)

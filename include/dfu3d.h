@@ -243,6 +243,22 @@ int dfu_points_in_boxes(dfu_ctx* ctx, void* stream, const float* points, int C, 
 int dfu_crop_boxes_sync(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* boxes, int M,
                         const double* centres64, float* out_rows, int64_t capacity, int64_t* offsets_host);
 
+/* ---- consumer side of the 8-column cloud (detector input) -----------------------------------------------
+ * Modality split of pcdet/datasets/dataset_virtual.py:270-296 (last column == 2: LiDAR rows, == 1: pseudo rows), each
+ * in input order, optionally with mask_points_by_range (pcdet/utils/common_utils.py:78-81 as applied by
+ * processor/data_processor_virtual.py:69-77: x, y inside [lo, hi], both ends inclusive).  cloud float [n][C];
+ * range_host float[6] = x y z lo, x y z hi, or NULL; out_* float [n][C] (capacity n rows each); counts_host[2]. */
+int dfu_split_cloud_sync(dfu_ctx* ctx, void* stream, const float* cloud, int C, int64_t n, const float* range_host,
+                         float* out_lidar, float* out_pseudo, int64_t* counts_host);
+
+/* Hard voxelisation of transform_points_to_voxels (processor/data_processor_virtual.py:133-185; VoxelGeneratorWrapper
+ * :16-58 -> spconv points_to_voxel): float32 bins floor((p - lo) / vsize), voxels numbered by first appearance, the
+ * first max_points points of a voxel in input order, voxels beyond max_voxels dropped.  voxels float
+ * [max_voxels][max_points][C] (zero padded), coords int32 [max_voxels][3] = z y x, num_points int32 [max_voxels]. */
+int dfu_voxelize_sync(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* voxel_size_host,
+                      const float* range_host, int max_points, int max_voxels, float* voxels, int32_t* coords,
+                      int32_t* num_points, int64_t* nvox_host);
+
 #ifdef __cplusplus
 }
 #endif
