@@ -515,8 +515,9 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, voxoff, int64_t*, SL_VOXOFF, (V + 1) * sizeof(int64_t));
   DFU_SLOT(ctx, warpstat, unsigned*, SL_WARPSTAT, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
   // queue of pixels whose float32 angles are too close to a bin edge: 1/64 of the pixels (8x the expected 0.2 %)
-  const unsigned capq = (unsigned)(((int64_t)V * npix / 64 + S2_NQ - 1) / S2_NQ + 64);
-  DFU_SLOT(ctx, ambq, uint2*, SL_AMBQ, (size_t)S2_NQ * capq * sizeof(uint2) + S2_NQ * sizeof(unsigned));
+  unsigned capq = (unsigned)(((int64_t)V * npix / 64 + S2_NQ - 1) / S2_NQ + 64);
+  if (const char* e = getenv("DFU3D_S2_CAPQ")) capq = (unsigned)atoi(e);   // test hook: forces the overflow (scan) path
+  DFU_SLOT(ctx, ambq, uint2*, SL_AMBQ, (size_t)S2_NQ * (capq + 1) * sizeof(uint2) + S2_NQ * sizeof(unsigned));
   unsigned* ambcnt = (unsigned*)(ambq + (size_t)S2_NQ * capq);
   {
     DFU_PROF(ctx, st, PT_MISC);

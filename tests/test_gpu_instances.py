@@ -172,3 +172,22 @@ def test_run_host_pipelined_equals_resident(chunks):
         assert np.array_equal(res.seg_counts, ref.seg_counts)
         assert res.label_lines == ref.label_lines
         assert res.d2h_bytes == ref_cloud.nbytes + ref.boxes.nbytes
+
+
+def test_densify_rare_paths_give_the_same_cloud(monkeypatch):
+    """(a) the queue of ambiguous pixels overflowing (pass A falls back to scanning the key array) and (b) a batch with
+    more views than the constant bank holds (passes A/B run in chunks) must not change a single row."""
+    frs = [helpers.small_frame(s, 'nuscenes', scale=0.25) for s in (3, 4, 5)]
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames(frs, pipe.device)
+    want = pipe.run(vb, cloud_dtype=torch.float64)
+    wcloud = want.cloud.cpu().numpy()
+    monkeypatch.setenv('DFU3D_S2_CAPQ', '0')
+    got = pipe.run(vb, cloud_dtype=torch.float64)
+    monkeypatch.delenv('DFU3D_S2_CAPQ')
+    assert np.array_equal(got.cloud.cpu().numpy(), wcloud) and np.array_equal(got.boxes, want.boxes)
+    many = pipeline.batch_from_frames(frs * 135, pipe.device)          # 405 views > S2_CVIEWS = 400
+    res = pipe.run(many, cloud_dtype=torch.float64, instances=False)
+    cloud = res.cloud.cpu().numpy()
+    for v in (0, 1, 2, 399, 400, 401, 404):
+        assert np.array_equal(cloud[res.row_off[v]:res.row_off[v + 1]], wcloud[want.row_off[v % 3]:want.row_off[v % 3 + 1]])
