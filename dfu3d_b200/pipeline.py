@@ -10,6 +10,8 @@ label text.
 import math
 from dataclasses import dataclass, field
 
+import os
+
 import numpy as np
 import torch
 
@@ -394,7 +396,7 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
     their sum.  Device staging buffers are double-buffered and kept between calls."""
     dev = self.device
     st = self.__dict__.setdefault('_stage', {})
-    metas = _chunk_metas(hb, chunks)
+    metas = _chunk_metas(hb, int(os.environ.get('DFU3D_HOST_CHUNKS', chunks)))
     main = torch.cuda.current_stream(dev)
     if 's_in' not in st:
         st['s_in'], st['s_out'] = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
