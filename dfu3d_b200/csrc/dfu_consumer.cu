@@ -17,6 +17,8 @@
 
 #define CS_THREADS 256
 #define VOX_NONE 0xFFFFFFFFu
+// own scratch slots (the pipeline's scratch of a bound fusion batch stays intact)
+enum { CS_BLKCNT = 214, CS_BLKOFF, CS_RANGE };
 
 // ---------------------------------------------------------------- split
 // pass 0: per-block counts of the two modalities; pass 1: ordered scatter
@@ -69,11 +71,11 @@ extern "C" int dfu_split_cloud_sync(dfu_ctx* ctx, void* stream, const float* clo
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t nblk = (n + CS_THREADS - 1) / CS_THREADS;
   if (nblk > 0x3fffffff) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_split_cloud_sync: too many rows");
-  DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, 2 * nblk * sizeof(int32_t));
-  DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, (2 * nblk + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, blkcnt, int32_t*, CS_BLKCNT, 2 * nblk * sizeof(int32_t));
+  DFU_SLOT(ctx, blkoff, int64_t*, CS_BLKOFF, (2 * nblk + 1) * sizeof(int64_t));
   float* range = nullptr;
   if (range_host) {
-    DFU_SLOT(ctx, rd, float*, SL_VOXOFF, 6 * sizeof(float));
+    DFU_SLOT(ctx, rd, float*, CS_RANGE, 6 * sizeof(float));
     DFU_CUDA(ctx, cudaMemcpyAsync(rd, range_host, 6 * sizeof(float), cudaMemcpyHostToDevice, st));
     range = rd;
   }

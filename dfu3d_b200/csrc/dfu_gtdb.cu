@@ -7,6 +7,9 @@
 #include "dfu_common.cuh"
 
 #define GT_THREADS 256
+// own scratch slots: a crop between two stages of a bound fusion batch must not touch the pipeline's scratch
+enum { GT_BLKCNT = 210, GT_BLKOFF, GT_BOXOFF };
+static_assert(GT_BOXOFF < DFU_NSLOTS, "slot ids");
 
 // Per-box constants.  The reference compares float values against double thresholds (`fabs(z - cz) > dz / 2.0`,
 // `fabs(local_x) < dx / 2.0 + MARGIN`): for a float a and a double T,  a > T <=> a > round_down_to_float(T)  and
@@ -144,9 +147,9 @@ extern "C" int dfu_crop_boxes_sync(dfu_ctx* ctx, void* stream, const float* poin
   cudaStream_t st = (cudaStream_t)stream;
   const int nblk = (int)((n + GT_THREADS - 1) / GT_THREADS);
   const int64_t nb = (int64_t)M * nblk;
-  DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, nb * sizeof(int32_t));
-  DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, (nb + 1) * sizeof(int64_t));
-  DFU_SLOT(ctx, boff, int64_t*, SL_VOXOFF, (size_t)(M + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, blkcnt, int32_t*, GT_BLKCNT, nb * sizeof(int32_t));
+  DFU_SLOT(ctx, blkoff, int64_t*, GT_BLKOFF, (nb + 1) * sizeof(int64_t));
+  DFU_SLOT(ctx, boff, int64_t*, GT_BOXOFF, (size_t)(M + 1) * sizeof(int64_t));
   dim3 grid(nblk, (M + GT_CHUNK - 1) / GT_CHUNK);
   k_points_in_boxes<<<grid, GT_THREADS, 0, st>>>(points, C, n, boxes, M, nullptr, blkcnt);
   DFU_LAUNCH_CHECK(ctx);
