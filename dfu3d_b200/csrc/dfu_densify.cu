@@ -9,6 +9,7 @@
 // min-z representative (la_sampling2) and the min-y representative (la_sampling20, quirk Q2) in a direct-address
 // table, and a fourth kernel gathers the representatives.
 #include <cuda_fp16.h>
+#include <cub/cub.cuh>
 #include "dfu_common.cuh"
 
 #define S2_THREADS 256
@@ -352,8 +353,17 @@ __global__ void __launch_bounds__(256) k_blk_reduce(int bpv, const unsigned* __r
 // the bitmap), read the representatives out of its cell, put the cell back to all-ones (so that the next batch
 // starts from a clean table without a 41 MB-per-view memset), and gather the min-y representative's xyz + label word
 // for the instance stage.
+// owner[first voxel of pixel block b] = b for every block that opens a voxel; an inclusive max-scan then gives every
+// voxel ordinal its pixel block (blkoff is monotone), replacing two dependent binary searches per voxel
+__global__ void __launch_bounds__(256) k_vox_owner(int64_t nblocks, const int32_t* __restrict__ blkcnt,
+                                                   const int64_t* __restrict__ blkoff, int32_t* __restrict__ owner) {
+  const int64_t b = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (b < nblocks && blkcnt[b] > 0) owner[blkoff[b]] = (int32_t)b;
+}
+struct S2MaxOp { __device__ __forceinline__ int32_t operator()(int32_t a, int32_t b) const { return a > b ? a : b; } };
+
 __global__ void __launch_bounds__(256) k_vox_finish(const dfu_view* __restrict__ views, S2Prm q, int V, int bpv,
-                                                    const int64_t* __restrict__ voxoff, const int64_t* __restrict__ blkoff,
+                                                    const int32_t* __restrict__ owner, const int64_t* __restrict__ blkoff,
                                                     const unsigned* __restrict__ blkbits, const unsigned* __restrict__ key,
                                                     const float* __restrict__ depth, const uint32_t* __restrict__ labelmap,
                                                     VoxCell* __restrict__ table, int32_t* __restrict__ repz,
@@ -361,18 +371,9 @@ __global__ void __launch_bounds__(256) k_vox_finish(const dfu_view* __restrict__
                                                     uint32_t* __restrict__ repy_label, int64_t total) {
   const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (t >= total) return;
-  int lo = 0, hi = V;
-  while (hi - lo > 1) {
-    int mid = (lo + hi) >> 1;
-    if (voxoff[mid] <= t) lo = mid; else hi = mid;
-  }
-  const int v = lo;
-  // last block of the view with blkoff[b] <= t
-  int64_t blo = (int64_t)v * bpv, bhi = blo + bpv;
-  while (bhi - blo > 1) {
-    const int64_t mid = (blo + bhi) >> 1;
-    if (__ldg(blkoff + mid) <= t) blo = mid; else bhi = mid;
-  }
+  // the pixel block that opens voxel t (k_vox_owner + max-scan): no search
+  const int64_t blo = __ldg(owner + t);
+  const int v = (int)(blo / bpv);
   int r = (int)(t - __ldg(blkoff + blo));
   const unsigned* bits = blkbits + (size_t)blo * (S2_THREADS / 32);
   int w = 0;
@@ -612,7 +613,17 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_SLOT(ctx, repy_label, uint32_t*, SL_REPY_LABEL, cap * sizeof(uint32_t));
   if (nvox > 0) {
     DFU_PROF(ctx, st, PT_DENSIFY_C);
-    k_vox_finish<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, bpv, voxoff, blkoff, blkbits, key, ctx->depth,
+    const int64_t nblocks = (int64_t)V * bpv;
+    DFU_SLOT(ctx, owner, int32_t*, SL_WARPSTAT, (size_t)nvox * sizeof(int32_t));   // pass A's per-warp counts are consumed
+    DFU_CUDA(ctx, cudaMemsetAsync(owner, 0, (size_t)nvox * sizeof(int32_t), st));
+    k_vox_owner<<<(unsigned)((nblocks + 255) / 256), 256, 0, st>>>(nblocks, blkcnt, blkoff, owner);
+    DFU_LAUNCH_CHECK(ctx);
+    size_t tb = 0;
+    DFU_CUDA(ctx, cub::DeviceScan::InclusiveScan(nullptr, tb, owner, owner, S2MaxOp(), nvox, st));
+    DFU_SLOT(ctx, tmp, void*, SL_CUBTMP, tb);
+    DFU_CUDA(ctx, cub::DeviceScan::InclusiveScan(tmp, tb, owner, owner, S2MaxOp(), nvox, st));
+    ctx->launches += 2;
+    k_vox_finish<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, bpv, owner, blkoff, blkbits, key, ctx->depth,
                                                                  ctx->labelmap, table, repz, repy, repy_xyz, repy_label, nvox);
     DFU_LAUNCH_CHECK(ctx);
   }
