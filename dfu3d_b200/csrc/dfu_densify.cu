@@ -160,7 +160,8 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
   __syncthreads();
 
 // pass A: keys + table atomics.  No barrier: the view constants come from the constant bank and the per-warp counts
-// (valid pixels | gated points << 8 | table misses << 16) go to warpstat, one word per warp, summed by k_blk_reduce.
+// (valid pixels | gated points << 10 | table misses << 20, accumulated over the CTA's tiles) go to warpstat, one word per
+// warp and CTA, summed by k_blk_reduce.
 // blockIdx.y = view inside the chunk that c_view currently holds; v0 = first view of the chunk.
 #ifndef S2_TILES
 #define S2_TILES 8
@@ -168,6 +169,7 @@ __device__ __forceinline__ unsigned s2_key(const S2View& vw, const S2Prm& q, int
 #ifndef S2_MINB
 #define S2_MINB 6
 #endif
+static_assert(S2_TILES >= 1 && S2_TILES <= 31, "10-bit per-warp count fields");
 /* S2_TILES 256-pixel tiles per CTA: the next tile's depth is in flight while this one is computed */
 __global__ void __launch_bounds__(S2_THREADS, S2_MINB) k_densify_a(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
                                                           unsigned* __restrict__ key, VoxCell* __restrict__ table,
@@ -180,6 +182,7 @@ __global__ void __launch_bounds__(S2_THREADS, S2_MINB) k_densify_a(int v0, int b
   const float* dv = depth + (size_t)v * npix;
   int pix = blockIdx.x * (S2_TILES * S2_THREADS) + threadIdx.x;
   float dn = (pix < npix) ? __ldg(dv + pix) : 0.0f;
+  unsigned acc = 0;
 #pragma unroll 1
   for (int j = 0; j < S2_TILES; j++, pix += S2_THREADS) {
     const int blk = blockIdx.x * S2_TILES + j;
@@ -229,10 +232,13 @@ __global__ void __launch_bounds__(S2_THREADS, S2_MINB) k_densify_a(int v0, int b
         atomicMin(&c->miny, oy);
       }
     }
-    const unsigned n1 = __popc(__ballot_sync(0xffffffffu, st & 1u)), n2 = __popc(__ballot_sync(0xffffffffu, st & 2u)),
-                   n4 = __popc(__ballot_sync(0xffffffffu, st & 4u));
-    if (lane == 0) warpstat[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = n1 | (n2 << 8) | (n4 << 16);
+    acc += (st & 1u) | ((st & 2u) << 9) | ((st & 4u) << 18);      // per-lane counts, 10-bit fields (<= S2_TILES each)
   }
+  // one word per warp and CTA, stored in the slot of the CTA's first tile: valid | gated << 10 | misses << 20
+  const unsigned a1 = __reduce_add_sync(0xffffffffu, acc & 1023u), a2 = __reduce_add_sync(0xffffffffu, (acc >> 10) & 1023u),
+                 a4 = __reduce_add_sync(0xffffffffu, (acc >> 20) & 1023u);
+  if (lane == 0)
+    warpstat[((size_t)v * bpv + (size_t)blockIdx.x * S2_TILES) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = a1 | (a2 << 10) | (a4 << 20);
 }
 
 // The ambiguous pixels of pass A, one thread each: exact float64 key, key array patched, table atomics.  Normally they
@@ -328,11 +334,14 @@ __global__ void __launch_bounds__(256) k_blk_reduce(int bpv, const unsigned* __r
     int n = 0;
 #pragma unroll
     for (int h = 0; h < S2_THREADS / 128; h++) {
-      const uint4 m = __ldg(bb + h), w = __ldg(ws + h);
+      const uint4 m = __ldg(bb + h);
       n += __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
-      const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+      if (b % S2_TILES == 0) {      // pass A stores its per-warp counts in the slot of each CTA's first tile
+        const uint4 w = __ldg(ws + h);
+        const unsigned ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-      for (int j = 0; j < 4; j++) { n1 += ww[j] & 255u; n2 += (ww[j] >> 8) & 255u; n4 += (ww[j] >> 16) & 255u; }
+        for (int j = 0; j < 4; j++) { n1 += ww[j] & 1023u; n2 += (ww[j] >> 10) & 1023u; n4 += (ww[j] >> 20) & 1023u; }
+      }
     }
     blkcnt[(size_t)v * bpv + b] = n;
   }
