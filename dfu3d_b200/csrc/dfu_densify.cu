@@ -458,6 +458,22 @@ template <> struct Cvt<double> { static __device__ __forceinline__ double f(doub
 template <> struct Cvt<float>  { static __device__ __forceinline__ float f(double v) { return (float)v; } };
 template <> struct Cvt<__half> { static __device__ __forceinline__ __half f(double v) { return __double2half(v); } };
 
+// one row = 8 values: written with 128-bit stores (cudaMalloc'd / torch buffers are 256 B aligned, rows are 16 / 32 / 64 B)
+__device__ __forceinline__ void emit_row(__half* dst, const double* o) {
+  __half2 h[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) h[j] = __halves2half2(__double2half(o[2 * j]), __double2half(o[2 * j + 1]));
+  *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(h);
+}
+__device__ __forceinline__ void emit_row(float* dst, const double* o) {
+  reinterpret_cast<float4*>(dst)[0] = make_float4((float)o[0], (float)o[1], (float)o[2], (float)o[3]);
+  reinterpret_cast<float4*>(dst)[1] = make_float4((float)o[4], (float)o[5], (float)o[6], (float)o[7]);
+}
+__device__ __forceinline__ void emit_row(double* dst, const double* o) {
+#pragma unroll
+  for (int j = 0; j < 4; j++) reinterpret_cast<double2*>(dst)[j] = make_double2(o[2 * j], o[2 * j + 1]);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) k_emit_cloud(const dfu_view* __restrict__ views, S2Prm q, int V,
                                                     const int64_t* __restrict__ rowoff /*[V+1]*/,
@@ -500,9 +516,7 @@ __global__ void __launch_bounds__(256) k_emit_cloud(const dfu_view* __restrict__
     o[6] = dfu_div_by((double)B, 3.0, third);
     o[7] = 1.0;
   }
-  T* dst = out + t * 8;
-#pragma unroll
-  for (int j = 0; j < 8; j++) dst[j] = Cvt<T>::f(o[j]);
+  emit_row(out + t * 8, o);
 }
 
 // ---------------------------------------------------------------- C ABI
@@ -663,6 +677,7 @@ extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t c
   rowoff_h[V] = tot;
   if (row_off_host) memcpy(row_off_host, rowoff_h, (V + 1) * sizeof(int64_t));
   if (!out) return DFU_OK;  // size query
+  if ((uintptr_t)out & 15) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_cloud: out must be 16-byte aligned");
   if (capacity_rows < tot) return dfu_set_err(ctx, DFU_ERR_CAPACITY, "cloud needs %lld rows, capacity %lld", (long long)tot, (long long)capacity_rows);
   if (tot == 0) return DFU_OK;
   DFU_SLOT(ctx, rowoff, int64_t*, SL_SEGOUT, (V + 1) * sizeof(int64_t));

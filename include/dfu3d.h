@@ -157,7 +157,7 @@ int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int allow_overflow
 /* Copy-out of the fused cloud (my_loader.py:611-617 + vis_utils.py:164): rows [x y z i*10 0 0 0 2]
  * for the FOV-culled LiDAR then [x y z 0 R/3 G/3 B/3 1] per angular voxel (first-appearance
  * order).  out is [sum over views (nF + nVox)][8]; dtype 0 = float64, 1 = float32, 2 = float16.
- * row_off_host [V+1] receives the first row of each view. */
+ * row_off_host [V+1] receives the first row of each view.   `out` must be 16-byte aligned (rows are written with 128-bit stores). */
 int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t capacity_rows, int64_t* row_off_host);
 
 /* Per-voxel debug / parity outputs: linear pixel index (row*W+col) of the min-z and min-y
