@@ -90,3 +90,29 @@ def test_empty_inputs():
     res = pipe.run(pipeline.batch_from_frames([fr], pipe.device), cloud_dtype=torch.float64)
     assert res.counts_densify[0].tolist() == [0, 0, 0, 0] and res.cloud.shape[0] == res.counts_project[0, 0]
     assert res.boxes.shape[0] == 0 and res.label_lines == [[]]
+
+
+def test_widened_rows_report_bad_arguments():
+    """GT-database and consumer entry points: bad arguments / too-small buffers are status codes with a message."""
+    ctx = _lib.default_context(0)
+    pts = torch.rand((100, 4), device='cuda')
+    boxes = torch.tensor([[0.5, 0.5, 0.5, 1.0, 1.0, 1.0, 0.3]], device='cuda')
+    mask = torch.empty((1, 100), dtype=torch.int32, device='cuda')
+    rc = ctx.lib.dfu_points_in_boxes(ctx.h, ctx.stream, _lib.dptr(pts), 2, 100, _lib.dptr(boxes), 1, _lib.dptr(mask))
+    assert rc != 0 and b'dfu_points_in_boxes' in ctx.lib.dfu_last_error(ctx.h)
+    off = np.zeros(2, np.int64)
+    rows = torch.empty((1, 4), device='cuda')
+    rc = ctx.lib.dfu_crop_boxes_sync(ctx.h, ctx.stream, _lib.dptr(pts), 4, 100, _lib.dptr(boxes), 1, None, _lib.dptr(rows), 1,
+                                     _lib.hptr(off))
+    assert rc == -3 and off[1] > 1 and b'capacity' in ctx.lib.dfu_last_error(ctx.h)     # reported, not truncated
+    with pytest.raises(RuntimeError, match='empty grid'):
+        ops.voxelize(pts.cpu().numpy(), [0.05, 0.05, 0.1], [0, 0, 0, 0, 1, 1], 5, 10)
+    # the cloud is written with 128-bit stores: a misaligned destination is refused
+    fr = helpers.small_frame(3, 'nuscenes', scale=0.25)
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, instances=False)
+    buf = torch.empty((res.cloud.shape[0] * 8 + 8,), dtype=torch.float16, device='cuda')
+    row_off = np.zeros(2, np.int64)
+    rc = ctx.lib.dfu_fuse_emit_cloud(pipe.ctx.h, buf.data_ptr() + 2, 2, res.cloud.shape[0], _lib.hptr(row_off))
+    assert rc != 0 and b'aligned' in ctx.lib.dfu_last_error(pipe.ctx.h)
