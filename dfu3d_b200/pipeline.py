@@ -201,7 +201,10 @@ class FusionPipeline(object):
         V = len(vb.view_sweep)
         Hm, Wm = vb.image.shape[1:3] if vb.image is not None else vb.masks.shape[1:3]
         views = self.build_views(vb) if views is None else views
-        vd = torch.from_numpy(views.view(np.uint8).reshape(V, -1)).to(self.device)
+        vd = getattr(vb, '_views_dev', None)            # device copy of the view constants, cached with the host one
+        if vd is None or vd.device != self.device or vd.shape[0] != V:
+            vd = torch.from_numpy(views.view(np.uint8).reshape(V, -1)).to(self.device)
+            vb._views_dev = vd
         lm = torch.empty((V, Hm, Wm), dtype=torch.int32, device=self.device)
         masks = vb.masks
         is_f32 = int(masks.dtype == torch.float32)
@@ -276,7 +279,7 @@ class FusionPipeline(object):
         tot = ip.shape[0]
         cap = capacity or max(64, 16 * tot)
         while True:
-            boxes = np.zeros((cap, _lib.BOX_DOUBLES), np.float64)
+            boxes = np.empty((cap, _lib.BOX_DOUBLES), np.float64)     # rows [0, nb) are written by the call
             nb = np.zeros(1, np.int64)
             segc = np.zeros((max(tot, 1), 6), np.int64)
             rc = self.lib.dfu_fuse_instances_sync(self.ctx.h, _lib.hptr(ip), tot, _lib.hptr(self._angles),
@@ -288,7 +291,10 @@ class FusionPipeline(object):
             break
         res.boxes = boxes[:int(nb[0])]
         res.seg_counts = segc[:tot]
-        b2 = np.concatenate([np.asarray(b, np.float32).reshape(-1, 4) for b in vb.boxes2d] + [np.zeros((0, 4), np.float32)], 0)
+        b2 = getattr(vb, '_boxes2d_flat', None)
+        if b2 is None or b2.shape[0] != tot:
+            b2 = np.concatenate([np.asarray(b, np.float32).reshape(-1, 4) for b in vb.boxes2d] + [np.zeros((0, 4), np.float32)], 0)
+            vb._boxes2d_flat = b2
         res.box2d = b2[res.boxes[:, 1].astype(np.int64)] if res.boxes.shape[0] else np.zeros((0, 4), np.float32)
         if want_lines:
             res.label_lines = [[] for _ in range(V)]
