@@ -305,15 +305,19 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, int bpv, S2Prm
     if (j + 1 < S2_TILES) kn = (pix + S2_THREADS < npix) ? __ldg(kv + pix + S2_THREADS) : KEY_INVALID;
     bool opener = false;
     if (k != KEY_INVALID) {
-      const float d = __ldg(depth + (size_t)v * npix + pix);
       VoxCell* c = table + (size_t)v * NCELL + k;
+      // minz / miny / first / cnt are final after pass A: the whole cell is fetched up front (two 128-bit loads, in
+      // flight together with the depth load) instead of field by field between the atomics
+      const ulonglong2 mm = *reinterpret_cast<const ulonglong2*>(c);            // minz, miny
+      const uint2 fc = *reinterpret_cast<const uint2*>(&c->first);              // first, cnt
+      const float d = __ldg(depth + (size_t)v * npix + pix);
       double row, col, X, Y, Z;
       s2_rowcol(q, pix, row, col);
       s2_backproject(vw, col, row, d, X, Y, Z);
-      if (dfu_order_f64(Z) == c->minz) atomicMin(&c->argz, (unsigned)pix);
-      if (dfu_order_f64(Y) == c->miny) atomicMin(&c->argy, (unsigned)pix);
-      opener = (c->first == (unsigned)pix);
-      if (opener && (c->cnt + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
+      if (dfu_order_f64(Z) == mm.x) atomicMin(&c->argz, (unsigned)pix);
+      if (dfu_order_f64(Y) == mm.y) atomicMin(&c->argy, (unsigned)pix);
+      opener = (fc.x == (unsigned)pix);
+      if (opener && (fc.y + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
     }
     const unsigned bal = __ballot_sync(0xffffffffu, opener);
     if ((threadIdx.x & 31) == 0) blkbits[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
