@@ -8,6 +8,7 @@
 // materialised: three passes over the depth map resolve, per angular voxel, the opening pixel, the point count, the
 // min-z representative (la_sampling2) and the min-y representative (la_sampling20, quirk Q2) in a direct-address
 // table, and a fourth kernel gathers the representatives.
+#include <mutex>
 #include <cuda_fp16.h>
 #include <cub/cub.cuh>
 #include "dfu_common.cuh"
@@ -60,7 +61,6 @@ __constant__ S2View c_view[S2_CVIEWS];
 
 // c_view is one per device and process: users on different streams (several contexts) are ordered through an event
 // recorded behind the last kernel that read it, under a host mutex.
-#include <mutex>
 static std::mutex g_cview_mu;
 static cudaEvent_t g_cview_free[64];
 
