@@ -515,6 +515,52 @@ def crop_gt_points(points, gt_boxes):
     return [rows[off[i]:off[i + 1]] for i in range(len(off) - 1)], off
 
 
+# ---- self-evolution glue: detector predictions -> refreshed pseudo-boxes ------------------------
+def boxes_iou_bev(boxes_a, boxes_b):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:31-42 — (N, 7) x (M, 7) -> (N, M) rotated BEV IoU."""
+    assert boxes_a.shape[1] == boxes_b.shape[1] == 7
+    return ops.boxes_iou(boxes_a, boxes_b, 'bev')
+
+
+boxes_bev_iou_cpu = boxes_iou_bev   # iou3d_nms_utils.py:12-28: same values (the arithmetic follows that CPU routine)
+
+
+def boxes_iou3d_gpu(boxes_a, boxes_b):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:45-77 — (N, 7) x (M, 7) -> (N, M) 3-D IoU."""
+    assert boxes_a.shape[1] == boxes_b.shape[1] == 7
+    return ops.boxes_iou(boxes_a, boxes_b, '3d')
+
+
+def nms_gpu(boxes, scores, thresh, pre_maxsize=None, **kwargs):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:120-136 — returns (kept indices into `boxes`, None)."""
+    assert boxes.shape[1] == 7
+    return ops.nms(boxes, scores, thresh, pre_maxsize=pre_maxsize), None
+
+
+def class_agnostic_nms(box_scores, box_preds, nms_config, score_thresh=None):
+    """pcdet/models/model_utils/model_nms_utils.py:6-27 — `nms_config` is the reference's EasyDict / a dict with
+    NMS_TYPE ('nms_gpu'), NMS_THRESH, NMS_PRE_MAXSIZE, NMS_POST_MAXSIZE; returns (selected indices, their scores).
+    Score mask, top-k, suppression and the post-max cut are one library call."""
+    cfg = dict(nms_config)
+    if cfg.get('NMS_TYPE', 'nms_gpu') != 'nms_gpu':
+        raise NotImplementedError('only NMS_TYPE nms_gpu (the one the DFU3D configs use) is on this path')
+    selected = ops.nms(box_preds, box_scores, cfg['NMS_THRESH'], pre_maxsize=cfg['NMS_PRE_MAXSIZE'],
+                       post_maxsize=cfg['NMS_POST_MAXSIZE'], score_thresh=score_thresh)
+    return selected, box_scores[selected]
+
+
+def refresh_pseudo_boxes(pred_boxes, pred_scores, score_thresh, nms_config, pred_labels=None):
+    """One self-evolution round for one frame (tools/cfgs/dataset_configs/nuscenes2kitti_dataset_centerpoint.yaml:13-17
+    `initial_pseudo_box` -> `refine_pseudo_box0/1`; tools/cfgs/kitti_models/centerpoint_nuscenes2kitti.yaml:83-93): the
+    detector's predictions above `score_thresh`, rotated-NMS-deduplicated, become the next round's pseudo-boxes.
+    Returns a dict with the kept `boxes_lidar`, `score`, (`pred_labels`) and `index` into the predictions."""
+    sel, sc = class_agnostic_nms(pred_scores, pred_boxes, nms_config, score_thresh=score_thresh)
+    out = {'boxes_lidar': pred_boxes[sel], 'score': sc, 'index': sel}
+    if pred_labels is not None:
+        out['pred_labels'] = pred_labels[sel]
+    return out
+
+
 # ---- consumer side of the 8-column cloud (SURVEY.md 8(f) f3) ---------------------------------------------------------
 def mask_points_by_range(points, limit_range):
     """pcdet/utils/common_utils.py:78-81 (x and y only, inclusive): boolean mask, host arithmetic on the caller's array —

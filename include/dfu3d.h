@@ -259,6 +259,23 @@ int dfu_voxelize_sync(dfu_ctx* ctx, void* stream, const float* points, int C, in
                       const float* range_host, int max_points, int max_voxels, float* voxels, int32_t* coords,
                       int32_t* num_points, int64_t* nvox_host);
 
+/* ---- self-evolution glue (detector predictions -> refreshed pseudo-boxes) -------------------------------
+ * Rotated bird's-eye-view box overlap of pcdet/ops/iou3d_nms (iou3d_nms_utils.py:31-42 boxes_iou_bev, :45-77
+ * boxes_iou3d_gpu; src/iou3d_nms_kernel.cu:128-234,279-293; float32 arithmetic in the order of the reference's CPU build
+ * src/iou3d_cpu.cpp:59-230).  boxes_* float [n][stride], stride >= 7, a row = x y z dx dy dz heading (+ ignored columns);
+ * out float [na][nb].  mode 0: BEV IoU, 1: BEV overlap area, 2: 3-D IoU. */
+int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes_a, int stride_a, int na, const float* boxes_b,
+                       int stride_b, int nb, int mode, float* out);
+
+/* class_agnostic_nms (pcdet/models/model_utils/model_nms_utils.py:6-27) with NMS_TYPE nms_gpu (iou3d_nms_utils.py:120-136,
+ * src/iou3d_nms_kernel.cu:295-339, src/iou3d_nms.cpp:137-183): rows with score >= score_thresh (all rows when
+ * use_score_thresh == 0), the pre_maxsize best by score (descending, ties by row index; < 0: no cut), greedy rotated-BEV
+ * suppression at IoU > iou_thresh, the first post_maxsize survivors (< 0: all).  keep_out int64 [>= min(n, post_maxsize)]
+ * (device) = indices into the ORIGINAL rows in score order; *n_keep_host = their number.  At most 65536 candidates. */
+int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
+                 int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
+                 int64_t* keep_out, int64_t* n_keep_host);
+
 #ifdef __cplusplus
 }
 #endif
