@@ -227,23 +227,50 @@ __global__ void __launch_bounds__(256) k_nms_mask(const BevBox* __restrict__ P, 
   }
 }
 
-// greedy pass of iou3d_nms.cpp:166-181 on the device: thread t owns removed-word t; the loop over boxes is uniform
+// greedy pass of iou3d_nms.cpp:166-181 on the device, 64 boxes (one mask word) at a time: thread 0 resolves the chunk
+// against its diagonal words (a 64-step register chain, the shared loads issued up front), then thread t > chunk ORs the
+// rows of the chunk's survivors into its own removed-word with independent loads.  Stops once post_max boxes are kept.
 __global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* __restrict__ mask, int n, int nw, int post_max,
                                                      const int32_t* __restrict__ order, int64_t* __restrict__ keep,
                                                      int32_t* __restrict__ nkeep) {
   __shared__ unsigned long long removed[1024];
+  __shared__ unsigned long long diag[64];
+  __shared__ unsigned long long survivors;
   const int t = threadIdx.x;
   removed[t] = 0ull;
-  __syncthreads();
   int cnt = 0;
-  for (int i = 0; i < n; i++) {
-    const int wi = i >> 6;
-    if ((removed[wi] >> (i & 63)) & 1ull) continue;          // same shared word for every thread: uniform branch
-    if (t == 0 && cnt < post_max) keep[cnt] = order[i];
-    cnt++;
-    __syncthreads();                                         // everyone has read removed[wi] before its owner updates it
-    if (t >= wi && t < nw) removed[t] |= mask[(int64_t)i * nw + t];
+  for (int c = 0; c < nw; c++) {
+    const int base = c * 64;
+    if (t < 64) diag[t] = (base + t < n) ? mask[(int64_t)(base + t) * nw + c] : ~0ull;
+    __syncthreads();                                         // diag ready; removed[c] final (written in chunk c - 1's phase 2)
+    if (t == 0) {
+      unsigned long long rem = removed[c], kb = 0ull;
+      const int lim = min(64, n - base);
+#pragma unroll
+      for (int b = 0; b < 64; b++) {
+        const bool alive = b < lim && !((rem >> b) & 1ull);
+        kb |= (unsigned long long)alive << b;
+        rem |= alive ? diag[b] : 0ull;
+      }
+      survivors = kb;
+    }
     __syncthreads();
+    const unsigned long long kb = survivors;
+    if (t < 64 && ((kb >> t) & 1ull)) {
+      const int pos = cnt + __popcll(kb & ((1ull << t) - 1ull));
+      if (pos < post_max) keep[pos] = order[base + t];
+    }
+    cnt += __popcll(kb);
+    if (cnt >= post_max) break;                              // uniform: the remaining boxes cannot enter keep[:post_max]
+    if (t > c && t < nw) {
+      unsigned long long acc = removed[t], bits = kb;
+      while (bits) {
+        const int b = __ffsll((long long)bits) - 1;
+        bits &= bits - 1ull;
+        acc |= mask[(int64_t)(base + b) * nw + t];
+      }
+      removed[t] = acc;
+    }
   }
   if (t == 0) *nkeep = min(cnt, post_max);
 }
