@@ -24,7 +24,7 @@ static_assert(EV_KEEP < 100, "slot ids");
 
 struct __align__(16) BevBox {
   float cx, cy, cosr, sinr;            // centre, cos / sin of +heading
-  float hxm, hym, area, pad;           // dx / 2 + 1e-2, dy / 2 + 1e-2 (check_in_box2d, :75-85), dx * dy
+  float hxm, hym, area, rad;           // dx / 2 + 1e-2, dy / 2 + 1e-2 (check_in_box2d, :75-85), dx * dy, reach (below)
   float px[4], py[4];                  // oriented corners (:135-163)
 };
 
@@ -43,7 +43,9 @@ __device__ __forceinline__ BevBox ev_prepare(const float* __restrict__ b) {
   g.hxm = ev_add(hx, 1e-2f);
   g.hym = ev_add(hy, 1e-2f);
   g.area = ev_mul(dx, dy);
-  g.pad = 0.f;
+  // every point the overlap routine can collect for this box (edge crossings, own corners, the other box's corners inside
+  // the 1e-2-inflated rectangle) lies within half a diagonal + 1e-2 * sqrt(2) of the centre; 0.03 leaves room for rounding
+  g.rad = sqrtf(hx * hx + hy * hy) + 0.03f;
   const float x1 = ev_sub(cx, hx), y1 = ev_sub(cy, hy), x2 = ev_add(cx, hx), y2 = ev_add(cy, hy);
   const float qx[4] = {x1, x2, x2, x1}, qy[4] = {y1, y1, y2, y2};
 #pragma unroll
@@ -97,6 +99,11 @@ __device__ __forceinline__ bool ev_inside(const BevBox& g, float x, float y) {
 // area of the intersection polygon (:128-220): crossing points of the 16 edge pairs, then the corners of one box inside
 // the other (b's corner k, then a's corner k), ordered by atan2 about their mean, fan-summed from the first point
 __device__ float ev_overlap(const BevBox& A, const BevBox& B) {
+  {  // centres further apart than the two reaches: the reference finds no crossing and no contained corner -> area 0
+     // (NaN / inf boxes fail the comparison and take the full routine)
+    const float ddx = A.cx - B.cx, ddy = A.cy - B.cy, reach = A.rad + B.rad;
+    if (ddx * ddx + ddy * ddy > reach * reach) return 0.f;
+  }
   float vx[EV_MAXPTS], vy[EV_MAXPTS];
   int cnt = 0;
   float sx = 0.f, sy = 0.f;
