@@ -163,9 +163,9 @@ __global__ void k_bev_prepare(const float* __restrict__ boxes, int stride, const
 // 2: 3-D IoU (boxes_iou3d_gpu, iou3d_nms_utils.py:45-77: float32 torch elementwise arithmetic around the BEV overlap)
 __global__ void __launch_bounds__(128) k_bev_pairs(const BevBox* __restrict__ A, const float* __restrict__ rawA, int sa, int na,
                                                    const BevBox* __restrict__ B, const float* __restrict__ rawB, int sb, int nb,
-                                                   int mode, float* __restrict__ out) {
+                                                   int mode, int paired, float* __restrict__ out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = blockIdx.y;
+  const int i = paired ? j : blockIdx.y;                 // paired: row i against row i only (paired_boxes_iou3d_gpu, :155-188)
   if (j >= nb || i >= na) return;
   const BevBox a = A[i], b = B[j];
   float r;
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(128) k_bev_pairs(const BevBox* __restrict__ A,
       r = __fdiv_rn(o3, fmaxf(ev_sub(ev_add(va, vb), o3), 1e-6f));
     }
   }
-  out[(int64_t)i * nb + j] = r;
+  out[paired ? (int64_t)j : (int64_t)i * nb + j] = r;
 }
 
 // order-preserving key of a score, inverted: an ascending stable radix sort yields descending scores, ties by index.
@@ -229,6 +229,43 @@ __global__ void __launch_bounds__(256) k_nms_mask(const BevBox* __restrict__ P, 
     const int ca = c0 + lane, cb = c0 + lane + 32;
     if (ca < n && ca > r) h0 = ev_iou_bev(a, cols[lane]) > thresh;          // iou3d_nms_kernel.cu:327-335 (start = row + 1)
     if (cb < n && cb > r) h1 = ev_iou_bev(a, cols[lane + 32]) > thresh;
+    const unsigned lo = __ballot_sync(0xffffffffu, h0), hi = __ballot_sync(0xffffffffu, h1);
+    if (lane == 0) mask[(int64_t)r * nw + ct] = ((unsigned long long)hi << 32) | lo;
+  }
+}
+
+// nms_normal_gpu (iou3d_nms_kernel.cu:341-400): the same suppression words from the axis-aligned overlap of the boxes'
+// x / y extents, heading ignored.  The only products are dx * dy and width * height (halving is exact), so the value does
+// not depend on FMA contraction and equals the reference's CUDA arithmetic.
+__device__ __forceinline__ float ev_iou_normal(const float4 a, const float4 b) {      // x y dx dy
+  const float ahx = a.z * 0.5f, ahy = a.w * 0.5f, bhx = b.z * 0.5f, bhy = b.w * 0.5f;
+  const float left = fmaxf(ev_sub(a.x, ahx), ev_sub(b.x, bhx)), right = fminf(ev_add(a.x, ahx), ev_add(b.x, bhx));
+  const float top = fmaxf(ev_sub(a.y, ahy), ev_sub(b.y, bhy)), bottom = fminf(ev_add(a.y, ahy), ev_add(b.y, bhy));
+  const float inter = ev_mul(fmaxf(ev_sub(right, left), 0.f), fmaxf(ev_sub(bottom, top), 0.f));
+  return __fdiv_rn(inter, fmaxf(ev_sub(ev_add(ev_mul(a.z, a.w), ev_mul(b.z, b.w)), inter), EV_EPS));
+}
+
+__global__ void __launch_bounds__(256) k_nms_mask_normal(const float* __restrict__ boxes, int stride, const int32_t* __restrict__ order,
+                                                         int n, float thresh, int nw, unsigned long long* __restrict__ mask) {
+  const int ct = blockIdx.x, rt = blockIdx.y;
+  if (ct < rt) return;
+  __shared__ float4 cols[64], rows[64];
+  const int c0 = ct * 64, r0 = rt * 64;
+  if (threadIdx.x < 128) {
+    const int k = threadIdx.x & 63, g = (threadIdx.x < 64 ? c0 : r0) + k;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (g < n) { const float* p = boxes + (int64_t)order[g] * stride; v = make_float4(p[0], p[1], p[3], p[4]); }
+    (threadIdx.x < 64 ? cols : rows)[k] = v;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int q = 0; q < 8; q++) {
+    const int r = r0 + 8 * w + q;
+    if (r >= n) break;
+    const float4 a = rows[8 * w + q];
+    const int ca = c0 + lane, cb = c0 + lane + 32;
+    const bool h0 = ca < n && ca > r && ev_iou_normal(a, cols[lane]) > thresh;
+    const bool h1 = cb < n && cb > r && ev_iou_normal(a, cols[lane + 32]) > thresh;
     const unsigned lo = __ballot_sync(0xffffffffu, h0), hi = __ballot_sync(0xffffffffu, h1);
     if (lane == 0) mask[(int64_t)r * nw + ct] = ((unsigned long long)hi << 32) | lo;
   }
@@ -285,11 +322,13 @@ __global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* _
 // ---------------------------------------------------------------- C ABI
 extern "C" int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes_a, int stride_a, int na, const float* boxes_b,
                                   int stride_b, int nb, int mode, float* out) {
-  if (!ctx || na < 0 || nb < 0 || stride_a < 7 || stride_b < 7 || mode < 0 || mode > 2 ||
+  const int paired = (mode & 4) != 0;
+  mode &= ~4;
+  if (!ctx || na < 0 || nb < 0 || stride_a < 7 || stride_b < 7 || mode < 0 || mode > 2 || (paired && na != nb) ||
       (na > 0 && nb > 0 && (!boxes_a || !boxes_b || !out)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_boxes_iou_sync: bad argument");
   if (na == 0 || nb == 0) return DFU_OK;
-  if (na > 65535) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_boxes_iou_sync: more than 65535 rows");
+  if (na > 65535 && !paired) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_boxes_iou_sync: more than 65535 rows");
   cudaStream_t st = (cudaStream_t)stream;
   DFU_SLOT(ctx, A, BevBox*, EV_A, (size_t)na * sizeof(BevBox));
   DFU_SLOT(ctx, B, BevBox*, EV_B, (size_t)nb * sizeof(BevBox));
@@ -298,16 +337,16 @@ extern "C" int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes
   DFU_LAUNCH_CHECK(ctx);
   k_bev_prepare<<<(nb + 127) / 128, 128, 0, st>>>(boxes_b, stride_b, nullptr, nb, B);
   DFU_LAUNCH_CHECK(ctx);
-  dim3 grid((nb + 127) / 128, na);
-  k_bev_pairs<<<grid, 128, 0, st>>>(A, boxes_a, stride_a, na, B, boxes_b, stride_b, nb, mode, out);
+  dim3 grid((nb + 127) / 128, paired ? 1 : na);
+  k_bev_pairs<<<grid, 128, 0, st>>>(A, boxes_a, stride_a, na, B, boxes_b, stride_b, nb, mode, paired, out);
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
   return DFU_OK;
 }
 
-extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
-                            int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
-                            int64_t* keep_out, int64_t* n_keep_host) {
+static int ev_nms(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n, int use_score_thresh,
+                  float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize, int64_t* keep_out,
+                  int64_t* n_keep_host, int normal) {
   if (!ctx || !n_keep_host || n < 0 || stride < 7 || (n > 0 && (!boxes || !scores || !keep_out)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_nms_sync: bad argument");
   *n_keep_host = 0;
@@ -336,12 +375,17 @@ extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int 
   if (m == 0) return DFU_OK;
   const int nw = (m + 63) / 64;
   if (nw > 1024) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_nms_sync: %d candidates, at most 65536 (set pre_maxsize)", m);
-  DFU_SLOT(ctx, P, BevBox*, EV_A, (size_t)m * sizeof(BevBox));
   DFU_SLOT(ctx, mask, unsigned long long*, EV_MASK, (size_t)m * nw * sizeof(unsigned long long));
-  k_bev_prepare<<<(m + 127) / 128, 128, 0, st>>>(boxes, stride, sidx, m, P);
-  DFU_LAUNCH_CHECK(ctx);
-  k_nms_mask<<<dim3(nw, nw), 256, 0, st>>>(P, m, iou_thresh, nw, mask);
-  DFU_LAUNCH_CHECK(ctx);
+  if (normal) {
+    k_nms_mask_normal<<<dim3(nw, nw), 256, 0, st>>>(boxes, stride, sidx, m, iou_thresh, nw, mask);
+    DFU_LAUNCH_CHECK(ctx);
+  } else {
+    DFU_SLOT(ctx, P, BevBox*, EV_A, (size_t)m * sizeof(BevBox));
+    k_bev_prepare<<<(m + 127) / 128, 128, 0, st>>>(boxes, stride, sidx, m, P);
+    DFU_LAUNCH_CHECK(ctx);
+    k_nms_mask<<<dim3(nw, nw), 256, 0, st>>>(P, m, iou_thresh, nw, mask);
+    DFU_LAUNCH_CHECK(ctx);
+  }
   const int post = post_maxsize < 0 ? m : post_maxsize;
   k_nms_reduce<<<1, 1024, 0, st>>>(mask, m, nw, post, sidx, keep_out, cnt + 1);
   DFU_LAUNCH_CHECK(ctx);
@@ -349,4 +393,18 @@ extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int 
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
   *n_keep_host = pin[1];
   return DFU_OK;
+}
+
+extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
+                            int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
+                            int64_t* keep_out, int64_t* n_keep_host) {
+  return ev_nms(ctx, stream, boxes, stride, scores, n, use_score_thresh, score_thresh, iou_thresh, pre_maxsize, post_maxsize,
+                keep_out, n_keep_host, 0);
+}
+
+extern "C" int dfu_nms_normal_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
+                                   int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize,
+                                   int post_maxsize, int64_t* keep_out, int64_t* n_keep_host) {
+  return ev_nms(ctx, stream, boxes, stride, scores, n, use_score_thresh, score_thresh, iou_thresh, pre_maxsize, post_maxsize,
+                keep_out, n_keep_host, 1);
 }

@@ -537,15 +537,34 @@ def nms_gpu(boxes, scores, thresh, pre_maxsize=None, **kwargs):
     return ops.nms(boxes, scores, thresh, pre_maxsize=pre_maxsize), None
 
 
+def nms_normal_gpu(boxes, scores, thresh, **kwargs):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:139-152 — axis-aligned suppression; (kept indices, None)."""
+    assert boxes.shape[1] == 7
+    return ops.nms(boxes, scores, thresh, normal=True), None
+
+
+def paired_boxes_iou3d_gpu(boxes_a, boxes_b):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:155-188 — (N, 7) x (N, 7) -> (N,) 3-D IoU of row i with row i."""
+    assert boxes_a.shape[0] == boxes_b.shape[0]
+    assert boxes_a.shape[1] == boxes_b.shape[1] == 7
+    return ops.boxes_iou(boxes_a, boxes_b, '3d', paired=True)
+
+
+def boxes_aligned_iou3d_gpu(boxes_a, boxes_b):
+    """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:80-117 — as paired_boxes_iou3d_gpu, shaped (N, 1)."""
+    return paired_boxes_iou3d_gpu(boxes_a, boxes_b).reshape(-1, 1)
+
+
 def class_agnostic_nms(box_scores, box_preds, nms_config, score_thresh=None):
     """pcdet/models/model_utils/model_nms_utils.py:6-27 — `nms_config` is the reference's EasyDict / a dict with
-    NMS_TYPE ('nms_gpu'), NMS_THRESH, NMS_PRE_MAXSIZE, NMS_POST_MAXSIZE; returns (selected indices, their scores).
+    NMS_TYPE ('nms_gpu' / 'nms_normal_gpu'), NMS_THRESH, NMS_PRE_MAXSIZE, NMS_POST_MAXSIZE; returns (selected indices, their scores).
     Score mask, top-k, suppression and the post-max cut are one library call."""
     cfg = dict(nms_config)
-    if cfg.get('NMS_TYPE', 'nms_gpu') != 'nms_gpu':
-        raise NotImplementedError('only NMS_TYPE nms_gpu (the one the DFU3D configs use) is on this path')
+    kind = cfg.get('NMS_TYPE', 'nms_gpu')
+    if kind not in ('nms_gpu', 'nms_normal_gpu'):
+        raise AttributeError("module 'iou3d_nms_utils' has no attribute %r" % kind)     # the reference's getattr fails so
     selected = ops.nms(box_preds, box_scores, cfg['NMS_THRESH'], pre_maxsize=cfg['NMS_PRE_MAXSIZE'],
-                       post_maxsize=cfg['NMS_POST_MAXSIZE'], score_thresh=score_thresh)
+                       post_maxsize=cfg['NMS_POST_MAXSIZE'], score_thresh=score_thresh, normal=kind == 'nms_normal_gpu')
     return selected, box_scores[selected]
 
 

@@ -201,25 +201,26 @@ def crop_boxes(points, boxes, ctx=None):
     return _out(rows[:int(off[-1])], as_np), off
 
 
-def boxes_iou(boxes_a, boxes_b, mode='bev', ctx=None):
+def boxes_iou(boxes_a, boxes_b, mode='bev', paired=False, ctx=None):
     """pcdet/ops/iou3d_nms/iou3d_nms_utils.py:31-42 (`boxes_iou_bev`, mode 'bev'), the `boxes_overlap_bev_gpu` area
     (mode 'overlap') and :45-77 (`boxes_iou3d_gpu`, mode '3d'): boxes [N, >= 7] / [M, >= 7] = x y z dx dy dz heading
-    -> float32 [N, M]."""
+    -> float32 [N, M]; paired=True (:80-117, :155-188): N == M, row i against row i only -> float32 [N]."""
     ctx = ctx or _lib.default_context(0)
     a, as_np = _dev_f32(ctx, boxes_a)
     b, _ = _dev_f32(ctx, boxes_b)
     assert a.dim() == 2 and b.dim() == 2 and a.shape[1] >= 7 and b.shape[1] >= 7
-    out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=ctx.device)   # every element is written
+    assert not paired or a.shape[0] == b.shape[0]
+    out = torch.empty((a.shape[0],) if paired else (a.shape[0], b.shape[0]), dtype=torch.float32, device=ctx.device)
     ctx.check(ctx.lib.dfu_boxes_iou_sync(ctx.h, ctx.stream, _lib.dptr(a) if a.numel() else None, a.shape[1], a.shape[0],
                                          _lib.dptr(b) if b.numel() else None, b.shape[1], b.shape[0],
-                                         {'bev': 0, 'overlap': 1, '3d': 2}[mode], _lib.dptr(out) if out.numel() else None))
+                                         {'bev': 0, 'overlap': 1, '3d': 2}[mode] | (4 if paired else 0), _lib.dptr(out) if out.numel() else None))
     return _out(out, as_np)
 
 
-def nms(boxes, scores, iou_thresh, pre_maxsize=None, post_maxsize=None, score_thresh=None, ctx=None):
+def nms(boxes, scores, iou_thresh, pre_maxsize=None, post_maxsize=None, score_thresh=None, normal=False, ctx=None):
     """class_agnostic_nms with NMS_TYPE nms_gpu (pcdet/models/model_utils/model_nms_utils.py:6-27,
     pcdet/ops/iou3d_nms/iou3d_nms_utils.py:120-136): int64 indices into `boxes` of the survivors, best score first
-    (equal scores: lower index first)."""
+    (equal scores: lower index first).  normal=True: NMS_TYPE nms_normal_gpu (:139-152), axis-aligned overlap."""
     ctx = ctx or _lib.default_context(0)
     b, as_np = _dev_f32(ctx, boxes)
     s, _ = _dev_f32(ctx, scores)
@@ -228,7 +229,7 @@ def nms(boxes, scores, iou_thresh, pre_maxsize=None, post_maxsize=None, score_th
     n = b.shape[0]
     keep = torch.empty((max(n, 1),), dtype=torch.int64, device=ctx.device)
     nk = np.zeros(1, np.int64)
-    ctx.check(ctx.lib.dfu_nms_sync(ctx.h, ctx.stream, _lib.dptr(b) if n else None, b.shape[1], _lib.dptr(s) if n else None, n,
+    ctx.check((ctx.lib.dfu_nms_normal_sync if normal else ctx.lib.dfu_nms_sync)(ctx.h, ctx.stream, _lib.dptr(b) if n else None, b.shape[1], _lib.dptr(s) if n else None, n,
                                    int(score_thresh is not None), float(score_thresh or 0.0), float(iou_thresh),
                                    -1 if pre_maxsize is None else int(pre_maxsize),
                                    -1 if post_maxsize is None else int(post_maxsize), _lib.dptr(keep), _lib.hptr(nk)))

@@ -263,7 +263,8 @@ int dfu_voxelize_sync(dfu_ctx* ctx, void* stream, const float* points, int C, in
  * Rotated bird's-eye-view box overlap of pcdet/ops/iou3d_nms (iou3d_nms_utils.py:31-42 boxes_iou_bev, :45-77
  * boxes_iou3d_gpu; src/iou3d_nms_kernel.cu:128-234,279-293; float32 arithmetic in the order of the reference's CPU build
  * src/iou3d_cpu.cpp:59-230).  boxes_* float [n][stride], stride >= 7, a row = x y z dx dy dz heading (+ ignored columns);
- * out float [na][nb].  mode 0: BEV IoU, 1: BEV overlap area, 2: 3-D IoU. */
+ * out float [na][nb].  mode 0: BEV IoU, 1: BEV overlap area, 2: 3-D IoU; mode | 4: paired (na == nb, row i against row i
+ * only, out float [na]: paired_boxes_iou3d_gpu / boxes_aligned_iou3d_gpu, iou3d_nms_utils.py:80-117,155-188). */
 int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes_a, int stride_a, int na, const float* boxes_b,
                        int stride_b, int nb, int mode, float* out);
 
@@ -275,6 +276,12 @@ int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes_a, int str
 int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
                  int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
                  int64_t* keep_out, int64_t* n_keep_host);
+
+/* The same with NMS_TYPE nms_normal_gpu (iou3d_nms_utils.py:139-152, src/iou3d_nms_kernel.cu:341-400): suppression by the
+ * axis-aligned overlap of the x / y extents, heading ignored. */
+int dfu_nms_normal_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
+                        int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
+                        int64_t* keep_out, int64_t* n_keep_host);
 
 #ifdef __cplusplus
 }

@@ -164,6 +164,18 @@ def restated_iou3d(boxes_a, boxes_b, overlap_bev=None):    # iou3d_nms_utils.py:
     return (o3 / np.maximum(va + vb - o3, F(1e-6))).astype(F)
 
 
+def restated_iou_normal(boxes_a, boxes_b):
+    """iou_normal of iou3d_nms_kernel.cu:341-353 (axis-aligned x / y extents, float32).  The reference has no CPU build of
+    it (CUDA only), so this restatement is unpinned; the value does not depend on FMA contraction (halving is exact)."""
+    a, b = np.asarray(boxes_a, F)[:, None, :], np.asarray(boxes_b, F)[None, :, :]
+    left = np.maximum(a[..., 0] - a[..., 3] / F(2), b[..., 0] - b[..., 3] / F(2))
+    right = np.minimum(a[..., 0] + a[..., 3] / F(2), b[..., 0] + b[..., 3] / F(2))
+    top = np.maximum(a[..., 1] - a[..., 4] / F(2), b[..., 1] - b[..., 4] / F(2))
+    bottom = np.minimum(a[..., 1] + a[..., 4] / F(2), b[..., 1] + b[..., 4] / F(2))
+    inter = np.maximum(right - left, F(0)) * np.maximum(bottom - top, F(0))
+    return (inter / np.maximum(a[..., 3] * a[..., 4] + b[..., 3] * b[..., 4] - inter, EPS)).astype(F)
+
+
 def restated_nms(iou_fn, boxes, scores, iou_thresh, pre_maxsize=None, post_maxsize=None, score_thresh=None,
                  return_margin=False):
     """Indices into `boxes` of the survivors.  iou_fn(a, b) -> IoU matrix (reference_iou_bev or restated_iou_bev).

@@ -112,3 +112,33 @@ def test_nms_properties_at_detector_scale():
     better = s[keep][None, :].astype(np.float64) >= s[dropped][:, None]
     assert np.all((cover & better).any(1))
     assert np.array_equal(ops.nms(b[keep], s[keep], thr), np.arange(len(keep)))
+
+
+@pytest.mark.parametrize('seed,n,thr,pre,post', [(31, 200, 0.1, None, None), (32, 130, 0.5, 64, 10), (33, 4500, 0.3, 4096, None)])
+def test_nms_normal_matches_the_restatement(seed, n, thr, pre, post):
+    b, s = ev.synth_boxes(n, seed=seed, extent=40.0)
+    want, margin = ev.restated_nms(ev.restated_iou_normal, b, s, thr, pre, post, None, return_margin=True)
+    got = ops.nms(b, s, thr, pre, post, normal=True)
+    print('candidates', n, 'kept', len(want), 'closest consulted IoU to the threshold', margin)
+    assert margin == 0.0 or np.array_equal(got, want)      # arithmetic is contraction-free: identical unless exactly tied
+    if pre is None and post is None:
+        k, none = dropin.nms_normal_gpu(b, s, thr)
+        assert none is None and np.array_equal(k, want)
+        sel, _ = dropin.class_agnostic_nms(s, b, {'NMS_TYPE': 'nms_normal_gpu', 'NMS_THRESH': thr, 'NMS_PRE_MAXSIZE': n,
+                                                  'NMS_POST_MAXSIZE': n})
+        assert np.array_equal(sel, want)
+
+
+def test_paired_iou3d_is_the_diagonal_of_the_matrix():
+    a, _ = ev.synth_boxes(300, seed=41)
+    b = a + np.random.default_rng(42).normal(0, 0.15, a.shape).astype(np.float32)
+    full = ops.boxes_iou(a, b, '3d')
+    got = dropin.paired_boxes_iou3d_gpu(a, b)
+    assert got.shape == (300,) and np.array_equal(got, np.diagonal(full))
+    assert (got > 0.2).sum() > 100
+    assert np.array_equal(dropin.boxes_aligned_iou3d_gpu(a, b), got.reshape(-1, 1))
+    want = np.array([ev.restated_iou3d(a[i:i + 1], b[i:i + 1])[0, 0] for i in range(40)], np.float32)
+    assert np.abs(got[:40] - want).max() <= TOL
+    assert ops.boxes_iou(a, b, 'bev', paired=True).shape == (300,)
+    with pytest.raises(AssertionError):
+        dropin.paired_boxes_iou3d_gpu(a, b[:10])
