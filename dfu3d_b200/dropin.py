@@ -568,6 +568,23 @@ def class_agnostic_nms(box_scores, box_preds, nms_config, score_thresh=None):
     return selected, box_scores[selected]
 
 
+def multi_classes_nms(cls_scores, box_preds, nms_config, score_thresh=None):
+    """pcdet/models/model_utils/model_nms_utils.py:28-66 (MULTI_CLASSES_NMS: True in
+    tools/cfgs/kitti_models/centerpoint_nuscenes2kitti.yaml:88): per class k, class_agnostic_nms on column k of
+    `cls_scores` (N, num_class); returns (pred_scores, pred_labels = k per row, pred_boxes) concatenated class by class."""
+    is_t = isinstance(cls_scores, torch.Tensor)
+    pred_scores, pred_labels, pred_boxes = [], [], []
+    for k in range(cls_scores.shape[1]):
+        col = cls_scores[:, k].contiguous() if is_t else np.ascontiguousarray(cls_scores[:, k])
+        sel, sc = class_agnostic_nms(col, box_preds, nms_config, score_thresh=score_thresh)
+        pred_scores.append(sc)
+        pred_labels.append(torch.full((len(sel),), k, dtype=torch.long, device=sel.device) if is_t
+                           else np.full(len(sel), k, np.int64))
+        pred_boxes.append(box_preds[sel])
+    cat = (lambda xs: torch.cat(xs, dim=0)) if is_t else (lambda xs: np.concatenate(xs, 0))
+    return cat(pred_scores), cat(pred_labels), cat(pred_boxes)
+
+
 def refresh_pseudo_boxes(pred_boxes, pred_scores, score_thresh, nms_config, pred_labels=None):
     """One self-evolution round for one frame (tools/cfgs/dataset_configs/nuscenes2kitti_dataset_centerpoint.yaml:13-17
     `initial_pseudo_box` -> `refine_pseudo_box0/1`; tools/cfgs/kitti_models/centerpoint_nuscenes2kitti.yaml:83-93): the

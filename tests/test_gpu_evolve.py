@@ -142,3 +142,18 @@ def test_paired_iou3d_is_the_diagonal_of_the_matrix():
     assert ops.boxes_iou(a, b, 'bev', paired=True).shape == (300,)
     with pytest.raises(AssertionError):
         dropin.paired_boxes_iou3d_gpu(a, b[:10])
+
+
+def test_multi_classes_nms_is_the_per_class_loop():
+    b, _ = ev.synth_boxes(240, seed=51)
+    cls = np.random.default_rng(52).uniform(0, 1, (240, 3)).astype(np.float32)
+    cfg = {'NMS_TYPE': 'nms_gpu', 'NMS_THRESH': 0.6, 'NMS_PRE_MAXSIZE': 1000, 'NMS_POST_MAXSIZE': 83, 'MULTI_CLASSES_NMS': True}
+    sc, lab, bx = dropin.multi_classes_nms(cls, b, cfg, score_thresh=0.1)
+    want_s, want_l, want_b = [], [], []
+    for k in range(3):
+        keep = ev.restated_nms(ev.restated_iou_bev, b, cls[:, k], 0.6, 1000, 83, 0.1)
+        want_s.append(cls[keep, k]); want_l.append(np.full(len(keep), k)); want_b.append(b[keep])
+    assert np.array_equal(sc, np.concatenate(want_s)) and np.array_equal(lab, np.concatenate(want_l))
+    assert np.array_equal(bx, np.concatenate(want_b))
+    ts, tl, tb = dropin.multi_classes_nms(torch.from_numpy(cls).cuda(), torch.from_numpy(b).cuda(), cfg, score_thresh=0.1)
+    assert tl.dtype == torch.long and np.array_equal(ts.cpu().numpy(), sc) and np.array_equal(tb.cpu().numpy(), bx)
