@@ -152,8 +152,11 @@ __device__ __forceinline__ float ev_iou_bev(const BevBox& A, const BevBox& B) { 
 
 // ---------------------------------------------------------------- kernels
 // one thread per box; order (nullable) gathers rows of the score-sorted candidates
+// ndev (nullable): device-side count, the effective n is min(*ndev, n) — lets the NMS run without reading the number of
+// score-passing candidates back to the host
 __global__ void k_bev_prepare(const float* __restrict__ boxes, int stride, const int32_t* __restrict__ order, int n,
-                              BevBox* __restrict__ out) {
+                              const int32_t* __restrict__ ndev, BevBox* __restrict__ out) {
+  if (ndev) n = min(n, *ndev);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   out[i] = ev_prepare(boxes + (int64_t)(order ? order[i] : i) * stride);
@@ -207,10 +210,12 @@ __global__ void k_nms_keys(const float* __restrict__ scores, int n, int use_thre
 // suppression words: bit c of mask[r * nw + cw] = IoU(box r, box 64 * cw + c) > thresh, for tiles with cw >= r / 64 only
 // (a box is only ever suppressed by a better-scored one; the reference computes the lower triangle too and never reads it).
 // grid (col tile, row tile), 256 threads: warp w owns rows 8w..8w+7 of the tile, lane l the columns l and l + 32.
-__global__ void __launch_bounds__(256) k_nms_mask(const BevBox* __restrict__ P, int n, float thresh, int nw,
-                                                  unsigned long long* __restrict__ mask) {
+__global__ void __launch_bounds__(256) k_nms_mask(const BevBox* __restrict__ P, int n, const int32_t* __restrict__ ndev,
+                                                  float thresh, int nw, unsigned long long* __restrict__ mask) {
   const int ct = blockIdx.x, rt = blockIdx.y;
   if (ct < rt) return;
+  if (ndev) n = min(n, *ndev);
+  if (ct * 64 >= n) return;
   __shared__ BevBox cols[64];
   const int c0 = ct * 64, r0 = rt * 64;
   {
@@ -246,9 +251,12 @@ __device__ __forceinline__ float ev_iou_normal(const float4 a, const float4 b) {
 }
 
 __global__ void __launch_bounds__(256) k_nms_mask_normal(const float* __restrict__ boxes, int stride, const int32_t* __restrict__ order,
-                                                         int n, float thresh, int nw, unsigned long long* __restrict__ mask) {
+                                                         int n, const int32_t* __restrict__ ndev, float thresh, int nw,
+                                                         unsigned long long* __restrict__ mask) {
   const int ct = blockIdx.x, rt = blockIdx.y;
   if (ct < rt) return;
+  if (ndev) n = min(n, *ndev);
+  if (ct * 64 >= n) return;
   __shared__ float4 cols[64], rows[64];
   const int c0 = ct * 64, r0 = rt * 64;
   if (threadIdx.x < 128) {
@@ -274,17 +282,20 @@ __global__ void __launch_bounds__(256) k_nms_mask_normal(const float* __restrict
 // greedy pass of iou3d_nms.cpp:166-181 on the device, 64 boxes (one mask word) at a time: thread 0 resolves the chunk
 // against its diagonal words (a 64-step register chain, the shared loads issued up front), then thread t > chunk ORs the
 // rows of the chunk's survivors into its own removed-word with independent loads.  Stops once post_max boxes are kept.
-__global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* __restrict__ mask, int n, int nw, int post_max,
+__global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* __restrict__ mask, int n,
+                                                     const int32_t* __restrict__ ndev, int nw, int post_max,
                                                      const int32_t* __restrict__ order, int64_t* __restrict__ keep,
                                                      int32_t* __restrict__ nkeep) {
   __shared__ unsigned long long removed[1024];
   __shared__ unsigned long long diag[64];
   __shared__ unsigned long long survivors;
   const int t = threadIdx.x;
+  if (ndev) n = min(n, *ndev);
   removed[t] = 0ull;
   int cnt = 0;
   for (int c = 0; c < nw; c++) {
     const int base = c * 64;
+    if (base >= n) break;
     if (t < 64) diag[t] = (base + t < n) ? mask[(int64_t)(base + t) * nw + c] : ~0ull;
     __syncthreads();                                         // diag ready; removed[c] final (written in chunk c - 1's phase 2)
     if (t == 0) {
@@ -333,9 +344,9 @@ extern "C" int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes
   DFU_SLOT(ctx, A, BevBox*, EV_A, (size_t)na * sizeof(BevBox));
   DFU_SLOT(ctx, B, BevBox*, EV_B, (size_t)nb * sizeof(BevBox));
   DFU_PROF(ctx, st, PT_MISC);
-  k_bev_prepare<<<(na + 127) / 128, 128, 0, st>>>(boxes_a, stride_a, nullptr, na, A);
+  k_bev_prepare<<<(na + 127) / 128, 128, 0, st>>>(boxes_a, stride_a, nullptr, na, nullptr, A);
   DFU_LAUNCH_CHECK(ctx);
-  k_bev_prepare<<<(nb + 127) / 128, 128, 0, st>>>(boxes_b, stride_b, nullptr, nb, B);
+  k_bev_prepare<<<(nb + 127) / 128, 128, 0, st>>>(boxes_b, stride_b, nullptr, nb, nullptr, B);
   DFU_LAUNCH_CHECK(ctx);
   dim3 grid((nb + 127) / 128, paired ? 1 : na);
   k_bev_pairs<<<grid, 128, 0, st>>>(A, boxes_a, stride_a, na, B, boxes_b, stride_b, nb, mode, paired, out);
@@ -368,26 +379,32 @@ static int ev_nms(dfu_ctx* ctx, void* stream, const float* boxes, int stride, co
   ctx->launches += 3;
   int32_t* pin = (int32_t*)dfu_pinned(ctx, 2 * sizeof(int32_t));
   if (!pin) return DFU_ERR_CUDA;
-  DFU_CUDA(ctx, cudaMemcpyAsync(pin, cnt, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
-  int m = pin[0];
-  if (pre_maxsize > 0 && m > pre_maxsize) m = pre_maxsize;                 // model_nms_utils.py:15 / iou3d_nms_utils.py:129-130
-  if (m == 0) return DFU_OK;
+  // m = the candidates: score-passing rows, cut at pre_maxsize (model_nms_utils.py:15 / iou3d_nms_utils.py:129-130).  Its
+  // upper bound min(n, pre_maxsize) sizes the grids and the mask; the kernels clamp to the device-side count, so the count
+  // is read back only when the bound does not fit the single-block greedy pass
+  int m = (pre_maxsize > 0 && n > pre_maxsize) ? pre_maxsize : n;
+  const int32_t* mdev = cnt;
+  if (m > 65536) {
+    DFU_CUDA(ctx, cudaMemcpyAsync(pin, cnt, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    DFU_CUDA(ctx, cudaStreamSynchronize(st));
+    if (pin[0] < m) m = pin[0];
+    if (m == 0) return DFU_OK;
+  }
   const int nw = (m + 63) / 64;
   if (nw > 1024) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_nms_sync: %d candidates, at most 65536 (set pre_maxsize)", m);
   DFU_SLOT(ctx, mask, unsigned long long*, EV_MASK, (size_t)m * nw * sizeof(unsigned long long));
   if (normal) {
-    k_nms_mask_normal<<<dim3(nw, nw), 256, 0, st>>>(boxes, stride, sidx, m, iou_thresh, nw, mask);
+    k_nms_mask_normal<<<dim3(nw, nw), 256, 0, st>>>(boxes, stride, sidx, m, mdev, iou_thresh, nw, mask);
     DFU_LAUNCH_CHECK(ctx);
   } else {
     DFU_SLOT(ctx, P, BevBox*, EV_A, (size_t)m * sizeof(BevBox));
-    k_bev_prepare<<<(m + 127) / 128, 128, 0, st>>>(boxes, stride, sidx, m, P);
+    k_bev_prepare<<<(m + 127) / 128, 128, 0, st>>>(boxes, stride, sidx, m, mdev, P);
     DFU_LAUNCH_CHECK(ctx);
-    k_nms_mask<<<dim3(nw, nw), 256, 0, st>>>(P, m, iou_thresh, nw, mask);
+    k_nms_mask<<<dim3(nw, nw), 256, 0, st>>>(P, m, mdev, iou_thresh, nw, mask);
     DFU_LAUNCH_CHECK(ctx);
   }
   const int post = post_maxsize < 0 ? m : post_maxsize;
-  k_nms_reduce<<<1, 1024, 0, st>>>(mask, m, nw, post, sidx, keep_out, cnt + 1);
+  k_nms_reduce<<<1, 1024, 0, st>>>(mask, m, mdev, nw, post, sidx, keep_out, cnt + 1);
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cudaMemcpyAsync(pin + 1, cnt + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
