@@ -280,8 +280,8 @@ __global__ void __launch_bounds__(256) k_nms_mask_normal(const float* __restrict
 }
 
 // greedy pass of iou3d_nms.cpp:166-181 on the device, 64 boxes (one mask word) at a time: thread 0 resolves the chunk
-// against its diagonal words (a 64-step register chain, the shared loads issued up front), then thread t > chunk ORs the
-// rows of the chunk's survivors into its own removed-word with independent loads.  Stops once post_max boxes are kept.
+// against its diagonal words (a 64-step register chain, the shared loads issued up front), then the rows of the
+// chunk's survivors are ORed into the later removed-words, one (word, box) pair per thread.  Stops once post_max boxes are kept.
 __global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* __restrict__ mask, int n,
                                                      const int32_t* __restrict__ ndev, int nw, int post_max,
                                                      const int32_t* __restrict__ order, int64_t* __restrict__ keep,
@@ -317,14 +317,14 @@ __global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* _
     }
     cnt += __popcll(kb);
     if (cnt >= post_max) break;                              // uniform: the remaining boxes cannot enter keep[:post_max]
-    if (t > c && t < nw) {
-      unsigned long long acc = removed[t], bits = kb;
-      while (bits) {
-        const int b = __ffsll((long long)bits) - 1;
-        bits &= bits - 1ull;
-        acc |= mask[(int64_t)(base + b) * nw + t];
-      }
-      removed[t] = acc;
+    // one (later word, box of the chunk) pair per thread: every load is independent; the 64 boxes of a word are two warps,
+    // OR-reduced by the warp and merged with one shared atomic each
+    const int npairs = ((n + 63) / 64 - c - 1) * 64;
+    for (int p = t; p < npairs; p += 1024) {                 // npairs is a multiple of 64: warps enter and leave whole
+      const int w = c + 1 + (p >> 6), b = p & 63;
+      const unsigned long long v = ((kb >> b) & 1ull) ? mask[(int64_t)(base + b) * nw + w] : 0ull;
+      const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v), hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
+      if ((t & 31) == 0 && (lo | hi)) atomicOr(&removed[w], ((unsigned long long)hi << 32) | lo);
     }
   }
   if (t == 0) *nkeep = min(cnt, post_max);
