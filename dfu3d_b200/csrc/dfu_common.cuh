@@ -166,3 +166,34 @@ __device__ __forceinline__ void dfu_backproject_r(const dfu_view& vw, double rfu
 }
 
 __device__ __forceinline__ int dfu_warp_excl(unsigned ballot, int lane) { return __popc(ballot & ((1u << lane) - 1u)); }
+
+// ---------------------------------------------------------------- TMA 1-D bulk copies (global -> shared) + mbarrier
+// cp.async.bulk needs 16-byte aligned source, destination and size; completion is signalled on an mbarrier through
+// its transaction count (SASS: UBLKCP.S.G + SYNCS.ARRIVE.TRANS64).  Used to stage contiguous ranges of the sorted
+// point arrays (grid cells / BVH leaves) in shared memory.
+__device__ __forceinline__ uint32_t dfu_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void dfu_mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dfu_smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void dfu_mbar_arrive_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dfu_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void dfu_bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dfu_smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(dfu_smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void dfu_mbar_wait(unsigned long long* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(dfu_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}

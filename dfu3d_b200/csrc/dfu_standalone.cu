@@ -44,7 +44,8 @@ static int check_grid_err(dfu_ctx* ctx, cudaStream_t st, int sb, const char* wha
 }
 
 extern "C" int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
-                                 const double* radius_host, const int32_t* nb_host, uint8_t* out_keep, int32_t* out_count) {
+                                 const double* radius_host, const int32_t* nb_host, const int32_t* every_k_host,
+                                 uint8_t* out_keep, int32_t* out_count) {
   if (!ctx || nseg <= 0 || !seg_off_host || !radius_host || !nb_host || !out_keep)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_radius_filter: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
@@ -59,7 +60,7 @@ extern "C" int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, 
   DFU_SLOT(ctx, seg_off, int64_t*, SA_SEGOFF, (size_t)(nseg + 1) * 8);
   DFU_SLOT(ctx, prm, SegPrm*, SA_PRM, (size_t)nseg * sizeof(SegPrm));
   std::vector<SegPrm> ph(nseg);
-  for (int s = 0; s < nseg; s++) ph[s] = SegPrm{radius_host[s], nb_host[s], 1, 1, 0};
+  for (int s = 0; s < nseg; s++) ph[s] = SegPrm{radius_host[s], nb_host[s], every_k_host ? every_k_host[s] : 1, 1, 0};
   DFU_CUDA(ctx, cudaMemcpyAsync(seg_off, seg_off_host, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(prm, ph.data(), (size_t)nseg * sizeof(SegPrm), cudaMemcpyHostToDevice, st));
   k_rows_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(xyz, 3, n, seg_off, nseg, x, y, z, seg);

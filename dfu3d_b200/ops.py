@@ -36,10 +36,12 @@ def _out(t, as_numpy, dtype=None):
     return t.to(dtype=torch.bool) if dtype is bool else t
 
 
-def radius_filter(points, nb_points, radius, seg_off=None, ctx=None, return_counts=False):
+def radius_filter(points, nb_points, radius, seg_off=None, ctx=None, return_counts=False, every_k=None):
     """Open3D ``remove_radius_outlier(nb_points, radius)`` keep mask (call sites
     tools/PENet/dataloaders/my_loader.py:569-599): keep iff #{q : |p - q|^2 < r^2} > nb_points, self included.
-    ``nb_points`` / ``radius`` are scalars or one value per segment."""
+    ``nb_points`` / ``radius`` / ``every_k`` are scalars or one value per segment.  ``every_k``:
+    ``uniform_down_sample(every_k)`` first (my_loader.py:571): rows 0, k, 2k, ... of the segment take part, the others
+    get keep = False."""
     ctx = ctx or _lib.default_context(0)
     xyz, as_np = _dev_f64(ctx, points, 3)
     n = xyz.shape[0]
@@ -47,11 +49,12 @@ def radius_filter(points, nb_points, radius, seg_off=None, ctx=None, return_coun
     nseg = so.shape[0] - 1
     rad = np.ascontiguousarray(np.broadcast_to(np.asarray(radius, np.float64), (nseg,)))
     nbs = np.ascontiguousarray(np.broadcast_to(np.asarray(nb_points, np.int32), (nseg,)))
+    evk = None if every_k is None else np.ascontiguousarray(np.broadcast_to(np.asarray(every_k, np.int32), (nseg,)))
     keep = torch.zeros(n, dtype=torch.uint8, device=ctx.device)
     cnt = torch.zeros(nseg, dtype=torch.int32, device=ctx.device)
     ctx.check(ctx.lib.dfu_radius_filter(ctx.h, ctx.stream, _lib.dptr(xyz) if n else None, nseg, _lib.hptr(so),
-                                        _lib.hptr(rad), _lib.hptr(nbs), _lib.dptr(keep) if n else _lib.dptr(cnt),
-                                        _lib.dptr(cnt)))
+                                        _lib.hptr(rad), _lib.hptr(nbs), _lib.hptr(evk),
+                                        _lib.dptr(keep) if n else _lib.dptr(cnt), _lib.dptr(cnt)))
     k = _out(keep, as_np, bool)
     return (k, _out(cnt, as_np)) if return_counts else k
 

@@ -147,9 +147,11 @@ def make_calib(shape, cam=0):
 
 
 def make_view(shape, boxes, seed, cam=0, crop=None, scale=1.0, device='cpu', max_inst=32, min_pixels=24,
-              thing_classes=None):
+              thing_classes=None, backdrop=None):
     """One camera view.  ``scale`` < 1 shrinks the image (and intrinsics) for fast CPU tests.
-    ``crop=(H, W)``: the depth map covers image[:H, :W] (reference: vis_utils.py:147,161)."""
+    ``crop=(H, W)``: the depth map covers image[:H, :W] (reference: vis_utils.py:147,161).
+    ``backdrop`` (metres): rays that hit nothing within 100 m land on a sphere of that radius around the camera
+    instead of getting depth 0 ("sky-free" view: every pixel back-projects, BASELINE.json configs[2] ~8.6 M points)."""
     cfg = SHAPES[shape]
     P2, R0, V2C = make_calib(shape, cam)
     Hm, Wm = cfg['img']
@@ -172,7 +174,8 @@ def make_view(shape, boxes, seed, cam=0, crop=None, scale=1.0, device='cpu', max
     o_l = (o_c - torch.as_tensor(tt, device=device)) @ RtT.T
     d_l = d_c @ RtT.T
     t, bid = _raycast(o_l, d_l, boxes, -cfg['h'], device)
-    depth = torch.where(torch.isfinite(t) & (t < 100.0), t, torch.zeros_like(t))
+    far = torch.zeros_like(t) if backdrop is None else float(backdrop) / d_c.norm(dim=1)
+    depth = torch.where(torch.isfinite(t) & (t < 100.0), t, far)
     n = depth.shape[0]
     depth = depth * (1.0 + 0.02 * torch.randn(n, generator=g, dtype=torch.float64).to(device))
     salt = torch.rand(n, generator=g, dtype=torch.float64).to(device) < 0.01
@@ -207,7 +210,7 @@ def make_view(shape, boxes, seed, cam=0, crop=None, scale=1.0, device='cpu', max
 
 
 def make_frame(seed, shape='nuscenes', n_cams=1, sweeps=1, scale=1.0, crop=None, device='cpu', n_obj=None, max_inst=32,
-               only_cam=None):
+               only_cam=None, backdrop=None):
     """``dict(lidar [N,4] f32, views [n_cams], boxes_gt)``; seeded by ``seed`` alone.  ``only_cam`` keeps a
     single camera of the ``n_cams``-camera frame (same scene, same sweep)."""
     rng = np.random.default_rng(int(seed))
@@ -216,7 +219,8 @@ def make_frame(seed, shape='nuscenes', n_cams=1, sweeps=1, scale=1.0, crop=None,
     boxes = make_scene(rng, n_obj=n_obj, h=cfg['h'], yaw_centers=yaws)
     lidar = make_lidar(shape, boxes, seed, sweeps=sweeps, device=device)
     cams = range(n_cams) if only_cam is None else [only_cam]
-    views = [make_view(shape, boxes, seed, cam=c, crop=crop, scale=scale, device=device, max_inst=max_inst) for c in cams]
+    views = [make_view(shape, boxes, seed, cam=c, crop=crop, scale=scale, device=device, max_inst=max_inst,
+                       backdrop=backdrop) for c in cams]
     return {'lidar': lidar, 'views': views, 'boxes_gt': boxes, 'shape': shape}
 
 

@@ -197,9 +197,13 @@ int dfu_backproject_sync(dfu_ctx* ctx, void* stream, int V, const dfu_view* view
                          const float* depth, int height_gate, double* out_xyz, int32_t* out_pix, int64_t capacity,
                          int64_t* counts_host);
 
-/* Open3D remove_radius_outlier semantics (oracle/fakes.py): keep iff #{q: |p-q|^2 < r^2} > nb. */
+/* Open3D remove_radius_outlier semantics (oracle/fakes.py): keep iff #{q: |p-q|^2 < r^2} > nb.
+ * every_k_host (nullable, [nseg]): uniform_down_sample(every_k) applied to the segment first (call sites
+ * my_loader.py:571, my_loader_KittiPandasetWaymo.py:792-821): only rows 0, k, 2k, ... of the segment take part
+ * (as queries and as neighbours); all other rows get keep = 0. */
 int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
-                      const double* radius_host, const int32_t* nb_host, uint8_t* out_keep, int32_t* out_count /*nullable*/);
+                      const double* radius_host, const int32_t* nb_host, const int32_t* every_k_host,
+                      uint8_t* out_keep, int32_t* out_count /*nullable*/);
 
 /* Open3D remove_statistical_outlier semantics: mean distance to the k nearest (self included),
  * mu / Bessel sigma over the segment, keep iff 0 < mean < mu + ratio*sigma.

@@ -89,7 +89,7 @@ def test_radius_filter_matches_oracle(n, r, nb):
     rad = np.array([r, 2 * r], np.float64)
     nbs = np.array([nb, nb + 1], np.int32)
     ctx.check(ctx.lib.dfu_radius_filter(ctx.h, ctx.stream, _lib.dptr(d), 2, _lib.hptr(off), _lib.hptr(rad), _lib.hptr(nbs),
-                                        _lib.dptr(keep), _lib.dptr(cnt)))
+                                        None, _lib.dptr(keep), _lib.dptr(cnt)))
     torch.cuda.synchronize()
     want = np.concatenate([fakes.radius_outlier_mask(segs[0], nb, r), fakes.radius_outlier_mask(segs[1], nb + 1, 2 * r)])
     got = keep.cpu().numpy().astype(bool)
