@@ -44,6 +44,7 @@ struct dfu_ctx {
   int total_inst;
   void* table_clean_ptr;      // angular voxel table known to be all-ones (pass C resets what pass A touched)
   size_t table_clean_bytes;
+  int64_t sor_deferred, sor_points, sor_cause[3];   // last dfu_sor_filter call with out_stats_host: queries handled one by one
   // ---- per-kernel device timing (dfu_profile_*) ----
   int prof_on;
   int prof_used;

@@ -8,27 +8,67 @@
 //   mu      = sum over mean_i > 0 of mean_i / n,   sigma = sqrt(sum over mean_i > 0 of (mean_i - mu)^2 / (n - 1))
 //   keep_i  = 0 < mean_i < mu + ratio * sigma
 //
-// Exact k-NN on a MULTI-RESOLUTION grid obtained from ONE radix sort: points are sorted by a 48-bit Morton code of
-// their 16-bit cell coordinates (finest cell = bounding-box extent / 65536), so every cell of every coarser level
-// (edge 2^M finest cells) is one contiguous range of the sorted array.  Per query (one thread per SORTED point, so
-// that neighbouring threads walk the same ranges):
-//   1. the k nearest among the 2k Morton neighbours give an upper bound r_ub of the k-th neighbour distance;
-//   2. the smallest level M whose 2x2x2 block of cells around the query's nearest cell corner contains the ball of
-//      radius r_ub is scanned exhaustively (8 ranges, two binary searches each).  Dense regions (4 mm point spacing
-//      next to the sensor) and sparse ones (salt outliers metres from anything) therefore cost the same few hundred
-//      candidates, which a single-resolution grid cannot offer.
+// Exact k-NN, cell-centric, shared-memory staged (round 2 rebuild; the round-1 kernel walked an implicit octree with one
+// thread per point and kept its top-k list in local memory: 7 of 32 lanes active, 25 ms per 4 M points):
+//   * ONE radix sort by a 48-bit Hilbert key per segment puts spatial neighbours next to each other; every segment is
+//     padded to a multiple of 32 points.  Leaves ("groups") are 8 consecutive sorted points with an exact float
+//     bounding box rounded outwards; an 8-ary pyramid of boxes over the group array is the search structure.
+//   * k_sor_tile: one WARP per tile of 32 consecutive sorted queries.
+//       1. upper bound of the k-th neighbour distance from the +-k curve neighbours (float insertion network in
+//          registers, rounded up), staged with one TMA bulk copy per coordinate array;
+//       2. the tile's search box (union of the lanes' balls) is intersected with the pyramid level by level, 32 nodes
+//          per step; the surviving groups arrive in ascending order, so they form a few contiguous RUNS of the sorted
+//          arrays;
+//       3. the runs are staged in shared memory 64 groups at a time with cp.async.bulk + mbarrier (expect-tx), each
+//          lane tests the 64 staged boxes against its OWN ball (a 64-bit mask) and walks only its own groups;
+//       4. pass A counts the lane's neighbours in 16 shells of d^2 (lane-private shared-memory counters), which yields
+//          the shell that holds the k-th neighbour; pass B collects the <= k + few candidates below that shell into a
+//          lane-private shared-memory column; the k smallest are extracted in ascending order and their square roots
+//          added sequentially (bit-identical to std::accumulate over the sorted distances).
+//     No top-k list in local memory, no per-thread tree walk; all distance arithmetic is the exact float64 expression.
+//   * Queries whose bound is far larger than their tile's (salt outliers: their curve neighbours are far away), tiles
+//     whose search box meets too many nodes, and lanes whose k-th shell holds too many ties are DEFERRED to
+//     k_sor_single: one warp per query, nearest-first descent of the same pyramid with pruning against the current
+//     k-th distance, the k best kept sorted across the lanes of the warp (registers + shuffles).  k > 32 runs entirely
+//     on that kernel.
 // The reductions for mu and sigma are two-stage and order-fixed (chunk partials, then one block per segment), so the
 // result does not depend on scheduling.
 #include <cub/device/device_radix_sort.cuh>
-#include <vector>
+#include <stdlib.h>
 #include "dfu_ops.cuh"
 
-#define SOR_THREADS 128
 #define SOR_KMAX 64
-#define SOR_CHUNK 4096
-enum { SO_X = 170, SO_Y, SO_Z, SO_SEG, SO_SEGOFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_SX, SO_SY, SO_SZ, SO_TMP,
-       SO_MEAN, SO_CHSEG, SO_CHSTART, SO_PART, SO_SEGSTAT, SO_SEGCH };
+#define SOR_KFAST 32        /* k_sor_tile handles k <= 32 */
+#define SOR_CHUNK 4096      /* points per partial sum of the mu / sigma reductions */
+#define SOR_WARPS 2         /* warps (tiles in flight) per CTA of k_sor_tile */
+#define SOR_CG 32           /* groups staged per chunk (one bit of the lane's mask each) */
+#define SOR_NBIN 16
+#define SOR_FRONT 384       /* level-1 frontier capacity per tile */
+#define SOR_MAXLEV 10
+#define SOR_DEFER 9.0f      /* lanes whose squared bound exceeds 9 x the tile median go to k_sor_single */
+enum { SO_SEGOFF = 170, SO_POFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_REC, SO_TMP, SO_SPI,
+       SO_MEAN, SO_PART, SO_SEGSTAT, SO_SEGCH, SO_PYR, SO_TODO, SO_SCAL };
 
+struct SorBox { float4 lo, hi; };   // 32 bytes
+// 8 consecutive points of the sorted, padded array + their bounding box: ONE contiguous 224-byte record, so that a run
+// of consecutive groups is one bulk copy
+struct __align__(16) SorGroup {
+  double x[8], y[8], z[8];          // pads: +inf
+  SorBox box;
+};
+static_assert(sizeof(SorGroup) == 224, "SorGroup must be 224 bytes");
+
+struct SorTree {
+  const SorGroup* rec;               // [NP / 8]
+  const int32_t* spi;                // [NP] original index, -1 for pads
+  const int64_t* seg_off;            // [nseg+1]
+  const int64_t* poff;               // [nseg+1] padded offsets (multiples of 32)
+  const SorBox* lv[SOR_MAXLEV];      // lv[0]: compact copy of the group boxes; lv[L]: boxes of 8^L groups
+  int nlv[SOR_MAXLEV];
+  int nlev, nseg, ntiles, k;
+};
+
+// ---------------------------------------------------------------- keys
 __device__ __forceinline__ unsigned long long sor_spread3(unsigned v) {
   unsigned long long x = v & 0xffffu;
   x = (x | (x << 32)) & 0x001f00000000ffffull;
@@ -38,31 +78,52 @@ __device__ __forceinline__ unsigned long long sor_spread3(unsigned v) {
   x = (x | (x << 2)) & 0x1249249249249249ull;
   return x;
 }
-__device__ __forceinline__ unsigned long long sor_morton(unsigned cx, unsigned cy, unsigned cz) {
-  return (sor_spread3(cx) << 2) | (sor_spread3(cy) << 1) | sor_spread3(cz);
+// 48-bit Hilbert index of a 16-bit cell (Skilling's transpose algorithm).  Only the ORDER matters (locality of the
+// groups), never the result: any key gives the same neighbours.
+__device__ __forceinline__ unsigned long long sor_hilbert(unsigned x, unsigned y, unsigned z) {
+  unsigned X0 = x, X1 = y, X2 = z;
+  for (unsigned Q = 1u << 15; Q > 1; Q >>= 1) {
+    const unsigned P = Q - 1;
+    if (X0 & Q) X0 ^= P;
+    if (X1 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X1) & P; X0 ^= t; X1 ^= t; }
+    if (X2 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X2) & P; X0 ^= t; X2 ^= t; }
+  }
+  X1 ^= X0; X2 ^= X1;
+  unsigned t = 0;
+  for (unsigned Q = 1u << 15; Q > 1; Q >>= 1)
+    if (X2 & Q) t ^= Q - 1;
+  X0 ^= t; X1 ^= t; X2 ^= t;
+  return (sor_spread3(X0) << 2) | (sor_spread3(X1) << 1) | sor_spread3(X2);
 }
 
-// rows [n][3] -> SoA + segment id + per-segment bounding box (ordered-bit atomics; box[s] = min xyz, max xyz)
-__global__ void __launch_bounds__(256) k_sor_prepare(const double* __restrict__ rows, int64_t n, const int64_t* __restrict__ seg_off,
-                                                     int nseg, double* __restrict__ x, double* __restrict__ y, double* __restrict__ z,
-                                                     int32_t* __restrict__ seg, unsigned long long* __restrict__ box) {
+__device__ __forceinline__ int sor_seg_of(const int64_t* __restrict__ off, int nseg, int64_t i) {
+  int lo = 0, hi = nseg;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (off[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// per-segment bounding box (ordered-bit atomics; box[s] = min xyz, max xyz)
+__global__ void __launch_bounds__(256) k_sor_bbox(const double* __restrict__ rows, int64_t n, const int64_t* __restrict__ seg_off,
+                                                  int nseg, unsigned long long* __restrict__ box, int32_t* __restrict__ errflag) {
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   int s = -1;
   unsigned long long b[3] = {0, 0, 0};
   if (i < n) {
-    int lo = 0, hi = nseg;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (seg_off[mid] <= i) lo = mid; else hi = mid;
-    }
-    s = lo;
+    s = sor_seg_of(seg_off, nseg, i);
     const double px = rows[3 * i], py = rows[3 * i + 1], pz = rows[3 * i + 2];
-    x[i] = px; y[i] = py; z[i] = pz; seg[i] = s;
+    if (!(px == px && py == py && pz == pz) || isinf(px) || isinf(py) || isinf(pz)) atomicOr(errflag, 1);
     b[0] = dfu_order_f64(px); b[1] = dfu_order_f64(py); b[2] = dfu_order_f64(pz);
   }
+  // warp reduction when the warp sits in one segment, then ONE atomic per block and axis when the block does too
+  // (a single segment of millions of points would otherwise send 6 atomics per warp to the same 6 words)
+  __shared__ unsigned long long sh[8][6];
+  __shared__ int shs[8];
   const int s0 = __shfl_sync(0xffffffffu, s, 0);
-  const bool uniform = __all_sync(0xffffffffu, s == s0);
-  if (uniform && s0 >= 0) {
+  const bool uniform = __all_sync(0xffffffffu, s == s0) && s0 >= 0;
+  if (uniform) {
 #pragma unroll
     for (int a = 0; a < 3; a++) {
       unsigned long long mn = b[a], mx = b[a];
@@ -71,10 +132,7 @@ __global__ void __launch_bounds__(256) k_sor_prepare(const double* __restrict__ 
         const unsigned long long on = __shfl_xor_sync(0xffffffffu, mn, o), ox = __shfl_xor_sync(0xffffffffu, mx, o);
         mn = on < mn ? on : mn; mx = ox > mx ? ox : mx;
       }
-      if ((threadIdx.x & 31) == 0) {
-        atomicMin(box + 6 * s0 + a, mn);
-        atomicMax(box + 6 * s0 + 3 + a, mx);
-      }
+      if ((threadIdx.x & 31) == 0) { sh[threadIdx.x >> 5][a] = mn; sh[threadIdx.x >> 5][3 + a] = mx; }
     }
   } else if (s >= 0) {
 #pragma unroll
@@ -83,81 +141,104 @@ __global__ void __launch_bounds__(256) k_sor_prepare(const double* __restrict__ 
       atomicMax(box + 6 * s + 3 + a, b[a]);
     }
   }
-}
-
-struct SorSeg { double mn[3]; double c0; };   // finest cell edge and origin of a segment
-
-__device__ __forceinline__ SorSeg sor_seg(const unsigned long long* __restrict__ box, int s) {
-  SorSeg g;
-  double ext = 0.0;
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-    g.mn[a] = dfu_unorder_f64(box[6 * s + a]);
-    const double e = dfu_unorder_f64(box[6 * s + 3 + a]) - g.mn[a];
-    ext = e > ext ? e : ext;
+  if ((threadIdx.x & 31) == 0) shs[threadIdx.x >> 5] = uniform ? s0 : -1;
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    const int a = threadIdx.x;
+    bool same = true;
+    for (int w = 0; w < 8; w++) same = same && shs[w] == shs[0];
+    if (same && shs[0] >= 0) {
+      unsigned long long v = sh[0][a];
+      for (int w = 1; w < 8; w++) v = a < 3 ? (sh[w][a] < v ? sh[w][a] : v) : (sh[w][a] > v ? sh[w][a] : v);
+      if (a < 3) atomicMin(box + 6 * shs[0] + a, v); else atomicMax(box + 6 * shs[0] + a, v);
+    } else {
+      for (int w = 0; w < 8; w++)
+        if (shs[w] >= 0) {
+          if (a < 3) atomicMin(box + 6 * shs[w] + a, sh[w][a]); else atomicMax(box + 6 * shs[w] + a, sh[w][a]);
+        }
+    }
   }
-  g.c0 = ext > 0.0 ? ext * (1.0 / 65536.0) * (1.0 + 1e-6) : 1.0;
-  return g;
-}
-__device__ __forceinline__ unsigned sor_coord(double v, double mn, double c0) {
-  const double c = floor((v - mn) / c0);
-  return c < 0.0 ? 0u : (c > 65535.0 ? 65535u : (unsigned)c);
 }
 
-__global__ void __launch_bounds__(256) k_sor_keys(const double* __restrict__ x, const double* __restrict__ y,
-                                                  const double* __restrict__ z, const int32_t* __restrict__ seg, int64_t n,
-                                                  const unsigned long long* __restrict__ box, unsigned long long* __restrict__ key,
-                                                  int32_t* __restrict__ idx, int32_t* __restrict__ errflag) {
+__global__ void __launch_bounds__(256) k_sor_keys(const double* __restrict__ rows, int64_t n, const int64_t* __restrict__ seg_off,
+                                                  int nseg, const unsigned long long* __restrict__ box,
+                                                  unsigned long long* __restrict__ key, int32_t* __restrict__ idx) {
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
-  const int s = seg[i];
-  const SorSeg g = sor_seg(box, s);
-  const double px = x[i], py = y[i], pz = z[i];
-  if (!(px == px && py == py && pz == pz) || isinf(px) || isinf(py) || isinf(pz)) atomicOr(errflag, 1);
-  key[i] = ((unsigned long long)(unsigned)s << 48) |
-           sor_morton(sor_coord(px, g.mn[0], g.c0), sor_coord(py, g.mn[1], g.c0), sor_coord(pz, g.mn[2], g.c0));
+  const int s = sor_seg_of(seg_off, nseg, i);
+  double mn[3], ext = 0.0;
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    mn[a] = dfu_unorder_f64(box[6 * s + a]);
+    const double e = dfu_unorder_f64(box[6 * s + 3 + a]) - mn[a];
+    ext = e > ext ? e : ext;
+  }
+  const double c0 = ext > 0.0 ? ext * (1.0 / 65536.0) * (1.0 + 1e-6) : 1.0;
+  unsigned c[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const double v = floor((rows[3 * i + a] - mn[a]) / c0);
+    c[a] = v < 0.0 ? 0u : (v > 65535.0 ? 65535u : (unsigned)v);      // NaN -> 0 (the call fails with DFU_ERR_DATA anyway)
+  }
+  key[i] = ((unsigned long long)(unsigned)s << 48) | sor_hilbert(c[0], c[1], c[2]);
   idx[i] = (int32_t)i;
 }
 
-__global__ void __launch_bounds__(256) k_sor_gather(const int32_t* __restrict__ sidx, const double* __restrict__ x,
-                                                    const double* __restrict__ y, const double* __restrict__ z, int64_t n,
-                                                    double* __restrict__ sx, double* __restrict__ sy, double* __restrict__ sz) {
-  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (t >= n) return;
-  const int i = sidx[t];
-  sx[t] = x[i]; sy[t] = y[i]; sz[t] = z[i];
+// one warp per tile of the PADDED sorted domain: group records in sorted order (+inf pads), original index (-1 pads),
+// and the bounding box of every group of 8 points, rounded outwards to float (in the record and in lv[0])
+__global__ void __launch_bounds__(256) k_sor_gather(const int32_t* __restrict__ sidx, const double* __restrict__ rows,
+                                                    const int64_t* __restrict__ seg_off, const int64_t* __restrict__ poff, int nseg,
+                                                    int ntiles, SorGroup* __restrict__ rec, int32_t* __restrict__ spi,
+                                                    SorBox* __restrict__ gbox) {
+  const int tile = (int)(((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5);
+  if (tile >= ntiles) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t t = (int64_t)tile * 32 + lane;
+  const int s = sor_seg_of(poff, nseg, (int64_t)tile * 32);
+  const int64_t r = t - poff[s];
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  double px = inf, py = inf, pz = inf;
+  int i = -1;
+  if (r < seg_off[s + 1] - seg_off[s]) {
+    i = sidx[seg_off[s] + r];
+    px = rows[3 * (int64_t)i]; py = rows[3 * (int64_t)i + 1]; pz = rows[3 * (int64_t)i + 2];
+  }
+  SorGroup& G = rec[t >> 3];
+  G.x[lane & 7] = px; G.y[lane & 7] = py; G.z[lane & 7] = pz;
+  spi[t] = i;
+  float lx = i >= 0 ? __double2float_rd(px) : INFINITY, ly = i >= 0 ? __double2float_rd(py) : INFINITY,
+        lz = i >= 0 ? __double2float_rd(pz) : INFINITY;
+  float hx = i >= 0 ? __double2float_ru(px) : -INFINITY, hy = i >= 0 ? __double2float_ru(py) : -INFINITY,
+        hz = i >= 0 ? __double2float_ru(pz) : -INFINITY;
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) {
+    lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, o)); ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, o));
+    lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, o));
+    hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, o));
+  }
+  if ((lane & 7) == 0) {
+    SorBox b;
+    b.lo = make_float4(lx, ly, lz, 0.f);
+    b.hi = make_float4(hx, hy, hz, 0.f);
+    G.box = b;
+    gbox[t >> 3] = b;
+  }
 }
 
-__device__ __forceinline__ int sor_lower_bound(const unsigned long long* __restrict__ a, int lo, int hi, unsigned long long v) {
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (__ldg(a + mid) < v) lo = mid + 1; else hi = mid;
+// next pyramid level: union of 8 children (empty boxes have lo = +inf, hi = -inf and never intersect anything)
+__global__ void __launch_bounds__(256) k_sor_pyr(const SorBox* __restrict__ child, int nchild, SorBox* __restrict__ parent, int nparent) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= nparent) return;
+  float4 lo = make_float4(INFINITY, INFINITY, INFINITY, 0.f), hi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+  for (int c = 8 * j; c < 8 * j + 8 && c < nchild; c++) {
+    const SorBox b = child[c];
+    lo.x = fminf(lo.x, b.lo.x); lo.y = fminf(lo.y, b.lo.y); lo.z = fminf(lo.z, b.lo.z);
+    hi.x = fmaxf(hi.x, b.hi.x); hi.y = fmaxf(hi.y, b.hi.y); hi.z = fmaxf(hi.z, b.hi.z);
   }
-  return lo;
+  SorBox o;
+  o.lo = lo; o.hi = hi;
+  parent[j] = o;
 }
-
-// bounded list of the k smallest squared distances seen so far
-struct SorTopK {
-  double v[SOR_KMAX];
-  int k, cnt, imax;
-  double lim;   // candidates with d2 >= lim cannot enter once the list is full
-  __device__ __forceinline__ void init(int kk) { k = kk; cnt = 0; imax = 0; lim = 1.7976931348623157e308; }
-  __device__ __forceinline__ void push(double d2) {
-    if (cnt < k) {
-      v[cnt] = d2;
-      if (cnt == 0 || d2 > v[imax]) imax = cnt;
-      cnt++;
-      if (cnt == k) lim = v[imax];
-    } else if (d2 < lim) {
-      v[imax] = d2;
-      int im = 0;
-      double m = v[0];
-      for (int j = 1; j < k; j++)
-        if (v[j] > m) { m = v[j]; im = j; }
-      imax = im; lim = m;
-    }
-  }
-};
 
 __device__ __forceinline__ double sor_d2(double ax, double ay, double az, double px, double py, double pz) {
   // ((a - b) ** 2).sum(-1): separately rounded products, (dx^2 + dy^2) + dz^2
@@ -165,145 +246,563 @@ __device__ __forceinline__ double sor_d2(double ax, double ay, double az, double
   return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
-// squared distance from q to the level-M cell with level-M coordinates e[], enlarged by `slack` (conservative)
-__device__ __forceinline__ double sor_cell_d2(const SorSeg& g, const double* q, int ex, int ey, int ez, int M, double slack) {
-  const int e[3] = {ex, ey, ez};
-  double acc = 0.0;
-#pragma unroll
-  for (int a = 0; a < 3; a++) {
-    const double blo = g.mn[a] + ldexp((double)e[a], M) * g.c0 - slack, bhi = g.mn[a] + ldexp((double)(e[a] + 1), M) * g.c0 + slack;
-    const double d = q[a] < blo ? blo - q[a] : (q[a] > bhi ? q[a] - bhi : 0.0);
-    acc += d * d;
+// ---------------------------------------------------------------- the tile kernel
+#ifdef SOR_STATS
+__device__ unsigned long long g_sor_stats[8];   // consumes, pairs, passes, groups staged, frontier nodes, walking lanes
+#endif
+template <int LCAP>
+struct __align__(128) SorWarpSmem {
+  SorGroup stage[SOR_CG];                                   // staged groups (also the curve window of step 1)
+  double list[LCAP][32];                                    // squared distances of a lane's neighbours, one column per lane
+  unsigned cnt[SOR_NBIN + 1][32];                           // lanes with more than LCAP neighbours: per shell, [NBIN] = below slo
+  double opx[32], opy[32], opz[32];                         // the lanes' queries, readable by every lane of the warp
+  double oshi[32], oslo[32], ow[32], oinvw[32];             // neighbours: d2 <= shi; shells: 16 equal parts of (slo, shi]
+  int nl[32];                                               // neighbours found per lane in the current pass (may exceed LCAP)
+  int front[2][SOR_FRONT];                                  // pyramid frontiers (ping-pong)
+  int grp[SOR_CG];                                          // group ids of the chunk, ascending
+  unsigned short pair[SOR_CG * 32];                         // (owner lane << 8 | staged group): the chunk's work list
+  unsigned long long mbar;
+};
+
+struct SorLane {
+  double px, py, pz;      // the query
+  double shi, slo;        // current squared bound of the k-th neighbour distance / lower edge of the shells
+  float fx, fy, fz;       // float copy of the query
+  float flim;             // float-side squared test radius (conservative, see sor_lane_flim); < 0: the lane does not walk
+  bool active, walk;
+};
+
+// float-side test radius for the box tests of a lane: a group may only be skipped if no point of it can lie within
+// sqrt(lim2).  The float copy of the query is off by at most half an ulp per axis; boxes are rounded outwards.
+__device__ __forceinline__ float sor_lane_flim(double lim2, float fx, float fy, float fz) {
+  const float r = __double2float_ru(__dsqrt_ru(lim2));
+  const float e = 2.4e-7f * (fabsf(fx) + fabsf(fy) + fabsf(fz)) + 1e-30f;
+  const float rr = __fadd_ru(r, e);
+  return __fmul_ru(__fmul_ru(rr, rr), 1.000004f);
+}
+
+__device__ __forceinline__ float sor_box_d2f(const float4 lo, const float4 hi, float fx, float fy, float fz) {
+  const float dx = fmaxf(fmaxf(lo.x - fx, fx - hi.x), 0.f), dy = fmaxf(fmaxf(lo.y - fy, fy - hi.y), 0.f),
+              dz = fmaxf(fmaxf(lo.z - fz, fz - hi.z), 0.f);
+  return dx * dx + dy * dy + dz * dz;
+}
+
+__device__ __forceinline__ bool sor_box_hits(const SorBox& b, const float4 qlo, const float4 qhi) {
+  return b.lo.x <= qhi.x && b.hi.x >= qlo.x && b.lo.y <= qhi.y && b.hi.y >= qlo.y && b.lo.z <= qhi.z && b.hi.z >= qlo.z;
+}
+
+// Shell of a neighbour with slo < d2 <= shi.  The shells are bounded by the EXACT doubles e_b = fl(slo + (b + 1) * w),
+// b < 15, and e_15 = shi, so that "all neighbours up to shell b" is the plain comparison d2 <= e_b of the next pass.
+__device__ __forceinline__ double sor_edge(int b, double slo, double w, double shi) {
+  return b >= SOR_NBIN - 1 ? shi : __fma_rn((double)(b + 1), w, slo);
+}
+__device__ __forceinline__ int sor_shell(double d2, double slo, double w, double invw, double shi) {
+  int b = __double2int_rz(__dmul_rn(__dsub_rn(d2, slo), invw));
+  b = b < 0 ? 0 : (b > SOR_NBIN - 1 ? SOR_NBIN - 1 : b);
+  if (b < SOR_NBIN - 1 && d2 > sor_edge(b, slo, w, shi)) b++;
+  else if (b > 0 && d2 <= sor_edge(b - 1, slo, w, shi)) b--;
+  return b;
+}
+
+// search box of the walking lanes: union of their balls, rounded outwards
+__device__ __forceinline__ void sor_search_box(const SorLane& L, float4& qlo, float4& qhi) {
+  const unsigned full = 0xffffffffu;
+  qlo = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  qhi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+  if (L.walk) {
+    const double r = __dsqrt_ru(L.shi) * (1.0 + 1e-12);
+    qlo = make_float4(__double2float_rd(L.px - r), __double2float_rd(L.py - r), __double2float_rd(L.pz - r), 0.f);
+    qhi = make_float4(__double2float_ru(L.px + r), __double2float_ru(L.py + r), __double2float_ru(L.pz + r), 0.f);
   }
-  return acc * (1.0 - 1e-12);
-}
-__device__ __forceinline__ unsigned sor_compact3(unsigned long long x) {
-  x &= 0x1249249249249249ull;
-  x = (x | (x >> 2)) & 0x10c30c30c30c30c3ull;
-  x = (x | (x >> 4)) & 0x100f00f00f00f00full;
-  x = (x | (x >> 8)) & 0x001f0000ff0000ffull;
-  x = (x | (x >> 16)) & 0x001f00000000ffffull;
-  x = (x | (x >> 32)) & 0xffffull;
-  return (unsigned)x;
-}
-
-#define SOR_LEAF 96   /* measured on the config-3 cloud: 4: 50.6 ms, 16: 35.7, 32: 30.0, 64: 27.0, 128: 26.7, 256: 28.1, 2048: 48.6 */
-#define SOR_STACK 136
-
-__global__ void __launch_bounds__(SOR_THREADS) k_sor_knn(const unsigned long long* __restrict__ skey, const int32_t* __restrict__ sidx,
-                                                         const double* __restrict__ sx, const double* __restrict__ sy,
-                                                         const double* __restrict__ sz, int64_t n,
-                                                         const int64_t* __restrict__ seg_off,
-                                                         const unsigned long long* __restrict__ box, int k,
-                                                         double* __restrict__ mean_out) {
-  const int64_t t64 = (int64_t)blockIdx.x * SOR_THREADS + threadIdx.x;
-  if (t64 >= n) return;
-  const int t = (int)t64;
-  const unsigned long long key = skey[t];
-  const int s = (int)(key >> 48);
-  const int lo = (int)seg_off[s], hi = (int)seg_off[s + 1];     // the segment's range is the same in sorted order
-  const int kk = (hi - lo) < k ? (hi - lo) : k;
-  const double px = sx[t], py = sy[t], pz = sz[t];
-  SorTopK top;
-  top.init(kk);
-  // 1. Morton window
-  const int w0 = t - k < lo ? lo : t - k, w1 = t + k + 1 > hi ? hi : t + k + 1;
-  for (int j = w0; j < w1; j++) top.push(sor_d2(__ldg(sx + j), __ldg(sy + j), __ldg(sz + j), px, py, pz));
-  if (w1 - w0 < hi - lo) {
-    const SorSeg g = sor_seg(box, s);
-    const double rub = __dsqrt_ru(top.lim);
-    const double slack = g.c0 * 1e-3;
-    const unsigned cq[3] = {sor_coord(px, g.mn[0], g.c0), sor_coord(py, g.mn[1], g.c0), sor_coord(pz, g.mn[2], g.c0)};
-    const double q[3] = {px, py, pz};
-    const unsigned long long segbits = (unsigned long long)(unsigned)s << 48;
-    // node stack: sorted range [r0, r1) that is (part of) one level-M cell
-    int st_r0[SOR_STACK], st_r1[SOR_STACK];
-    signed char st_M[SOR_STACK];
-    int sp = 0;
-    // 2. smallest level whose 2x2x2 block around the nearest cell corner contains the ball (q, rub), domain faces
-    //    excepted (nothing lies beyond the bounding box)
-    int M = 1;
-    while (M < 16 && ldexp(g.c0, M) < 2.0 * rub) M++;
-    int b0[3] = {0, 0, 0};
-    for (; M < 16; M++) {
-      bool ok = true;
-      const int top_cell = (int)(65535u >> M);
 #pragma unroll
-      for (int a = 0; a < 3; a++) {
-        const int c = (int)(cq[a] >> M), half = (int)((cq[a] >> (M - 1)) & 1u);
-        b0[a] = c - 1 + half;
-        const double blo = g.mn[a] + ldexp((double)b0[a], M) * g.c0, bhi = g.mn[a] + ldexp((double)(b0[a] + 2), M) * g.c0;
-        if (b0[a] > 0 && !(q[a] - rub >= blo + slack)) ok = false;
-        if (b0[a] + 1 < top_cell && !(q[a] + rub <= bhi - slack)) ok = false;
-      }
-      if (ok) break;
+  for (int o = 16; o > 0; o >>= 1) {
+    qlo.x = fminf(qlo.x, __shfl_xor_sync(full, qlo.x, o)); qlo.y = fminf(qlo.y, __shfl_xor_sync(full, qlo.y, o));
+    qlo.z = fminf(qlo.z, __shfl_xor_sync(full, qlo.z, o)); qhi.x = fmaxf(qhi.x, __shfl_xor_sync(full, qhi.x, o));
+    qhi.y = fmaxf(qhi.y, __shfl_xor_sync(full, qhi.y, o)); qhi.z = fmaxf(qhi.z, __shfl_xor_sync(full, qhi.z, o));
+  }
+}
+
+// Stage the chunk's groups (ids ascending in w.grp[0..ng)) with ONE bulk copy per run of consecutive ids, wait for the
+// bytes, let every lane mark the staged groups whose box can hold a point within its bound, flatten the (lane, group)
+// marks of the whole warp into one work list and spread it evenly over the lanes: each lane evaluates the 8 exact
+// squared distances of its (owner, group) items against the OWNER's query and appends the neighbours (d2 <= shi) to
+// the owner's column; beyond LCAP entries only the shell counts are kept.
+template <int LCAP>
+__device__ __forceinline__ void sor_consume(const SorTree& T, SorWarpSmem<LCAP>& w, int ng, unsigned& phase, const SorLane& L, int lane) {
+  const unsigned full = 0xffffffffu;
+  // ---- runs of consecutive groups -> bulk copies
+  const int g = lane < ng ? w.grp[lane] : -2;
+  const bool st = lane < ng && (lane == 0 || w.grp[lane - 1] + 1 != g);
+  const unsigned starts = __ballot_sync(full, st);
+  if (lane == 0) dfu_mbar_arrive_expect_tx(&w.mbar, (uint32_t)ng * (uint32_t)sizeof(SorGroup));
+  __syncwarp();
+  if (st) {
+    const unsigned later = lane < 31 ? (starts >> (lane + 1)) : 0u;
+    const int len = later ? __ffs((int)later) : ng - lane;
+    dfu_bulk_g2s(w.stage + lane, T.rec + g, (uint32_t)len * (uint32_t)sizeof(SorGroup), &w.mbar);
+  }
+  dfu_mbar_wait(&w.mbar, phase);
+  phase ^= 1u;
+  // ---- the lane's own groups
+  unsigned m = 0u;
+  if (L.flim >= 0.f) {
+    for (int gi = 0; gi < ng; gi++) {
+      const SorBox b = w.stage[gi].box;                  // broadcast
+      if (sor_box_d2f(b.lo, b.hi, L.fx, L.fy, L.fz) <= L.flim) m |= 1u << gi;
     }
-    if (M >= 16) {
-      st_r0[0] = lo; st_r1[0] = hi; st_M[0] = 16; sp = 1;
-    } else {
-      const int top_cell = (int)(65535u >> M);
-      for (int o = 0; o < 8; o++) {
-        const int ex = b0[0] + (o >> 2), ey = b0[1] + ((o >> 1) & 1), ez = b0[2] + (o & 1);
-        if (ex < 0 || ey < 0 || ez < 0 || ex > top_cell || ey > top_cell || ez > top_cell) continue;
-        if (sor_cell_d2(g, q, ex, ey, ez, M, slack) >= top.lim) continue;
-        const unsigned long long klo = segbits | (sor_morton((unsigned)ex, (unsigned)ey, (unsigned)ez) << (3 * M));
-        const unsigned long long khi = klo + (1ull << (3 * M));
-        const int r0 = sor_lower_bound(skey, lo, hi, klo);
-        if (r0 >= hi || __ldg(skey + r0) >= khi) continue;
-        const int r1 = sor_lower_bound(skey, r0, hi, khi);
-        st_r0[sp] = r0; st_r1[sp] = r1; st_M[sp] = (signed char)M; sp++;
-      }
+  }
+  // ---- work list of the warp
+  int off = __popc(m);
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(full, off, o);
+    if (lane >= o) off += v;
+  }
+  const int P = __shfl_sync(full, off, 31);
+  off -= __popc(m);
+#ifdef SOR_STATS
+  if (lane == 0) { atomicAdd(&g_sor_stats[0], 1ull); atomicAdd(&g_sor_stats[1], (unsigned long long)P); atomicAdd(&g_sor_stats[3], (unsigned long long)ng); }
+#endif
+  while (m) {
+    const int gi = __ffs((int)m) - 1;
+    m &= m - 1;
+    w.pair[off++] = (unsigned short)((lane << 8) | gi);
+  }
+  __syncwarp();
+  // uniform trip count + a barrier per iteration: without it the lanes that leave the neighbour loop early run ahead
+  // into the next item on their own and the warp splinters (measured: 6 of 32 lanes per instruction)
+  for (int e0 = 0; e0 < P; e0 += 32, __syncwarp()) {
+    const int e = e0 + lane;
+    if (e >= P) continue;
+    const int pr = w.pair[e], o = pr >> 8;
+    const SorGroup& G = w.stage[pr & 255];
+    const double qx = w.opx[o], qy = w.opy[o], qz = w.opz[o], shi = w.oshi[o];
+    double d2v[8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      const int j = (q + lane) & 7;                      // rotated: the lanes spread over the banks
+      d2v[q] = sor_d2(G.x[j], G.y[j], G.z[j], qx, qy, qz);
     }
-    // 3. depth-first descent with pruning against the current k-th distance; children are pushed far-to-near
-    while (sp > 0) {
-      sp--;
-      const int r0 = st_r0[sp], r1 = st_r1[sp], Mn = st_M[sp];
-      if (Mn < 16) {
-        const unsigned long long pre = (__ldg(skey + r0) & 0xffffffffffffull) >> (3 * Mn);
-        if (sor_cell_d2(g, q, (int)sor_compact3(pre >> 2), (int)sor_compact3(pre >> 1), (int)sor_compact3(pre), Mn, slack) >= top.lim)
-          continue;
-      }
-      if (r1 - r0 <= SOR_LEAF || Mn == 0) {
-        for (int j = r0; j < r1; j++) {
-          if (j >= w0 && j < w1) continue;
-          top.push(sor_d2(__ldg(sx + j), __ldg(sy + j), __ldg(sz + j), px, py, pz));
+    unsigned hm = 0u;
+#pragma unroll
+    for (int q = 0; q < 8; q++) hm |= (d2v[q] <= shi) ? (1u << q) : 0u;
+    if (hm) {
+      // the neighbours of the item take consecutive slots of the owner's column: one atomic per item
+      int slot = atomicAdd(&w.nl[o], __popc(hm));
+      while (hm) {
+        const int q = __ffs((int)hm) - 1;
+        hm &= hm - 1;
+        // d2v[q] through a select tree (a dynamic index would put the array in local memory)
+        const double a0 = (q & 1) ? d2v[1] : d2v[0], a1 = (q & 1) ? d2v[3] : d2v[2], a2 = (q & 1) ? d2v[5] : d2v[4],
+                     a3 = (q & 1) ? d2v[7] : d2v[6];
+        const double b0 = (q & 2) ? a1 : a0, b1 = (q & 2) ? a3 : a2;
+        const double d2 = (q & 4) ? b1 : b0;
+        if (slot < LCAP) {
+          w.list[slot][o] = d2;
+        } else {
+          const double slo = w.oslo[o];
+          const int b = d2 <= slo ? SOR_NBIN : sor_shell(d2, fmax(slo, 0.0), w.ow[o], w.oinvw[o], shi);
+          atomicAdd(&w.cnt[b][o], 1u);
         }
+        slot++;
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// One pass over the candidates of the tile: the level-1 frontier w.front[fsel][0..nf) is expanded 4 nodes (32 groups)
+// at a time against the search box of the walking lanes; every 32 surviving groups are consumed.
+template <int LCAP>
+__device__ __forceinline__ void sor_pass(const SorTree& T, SorWarpSmem<LCAP>& w, int fsel, int nf, int gfirst, int glast, unsigned& phase,
+                                         const SorLane& L, int lane) {
+  const unsigned full = 0xffffffffu;
+  float4 qlo, qhi;
+  sor_search_box(L, qlo, qhi);
+  int ng = 0;
+  for (int f0 = 0; f0 < nf || ng > 0; f0 += 4) {
+    const int fi = f0 + (lane >> 3);
+    bool hit = false;
+    int g = -1;
+    if (fi < nf) {
+      g = w.front[fsel][fi] * 8 + (lane & 7);
+      if (g >= gfirst && g <= glast) hit = sor_box_hits(T.lv[0][g], qlo, qhi);
+    }
+    const unsigned bm = __ballot_sync(full, hit);
+    // fill the chunk up to SOR_CG groups; the rest of this batch opens the next chunk
+    const int room = SOR_CG - ng, nb = __popc(bm);
+    const int rank = __popc(bm & ((1u << lane) - 1u));
+    if (hit && rank < room) w.grp[ng + rank] = g;
+    __syncwarp();
+    const int filled = nb < room ? ng + nb : SOR_CG;
+    if (filled == SOR_CG || (f0 + 4 >= nf && filled > 0)) {
+      sor_consume<LCAP>(T, w, filled, phase, L, lane);
+      if (hit && rank >= room) w.grp[rank - room] = g;
+      ng = nb > room ? nb - room : 0;
+      __syncwarp();
+    } else {
+      ng = filled;
+    }
+  }
+}
+
+// cause: 0 far bound, 1 search box meets too many nodes, 2 ties in the k-th shell
+__device__ __forceinline__ void sor_defer(bool want, int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int cause, int lane) {
+  const unsigned m = __ballot_sync(0xffffffffu, want);
+  if (!m) return;
+  int base = 0;
+  if (lane == 0) {
+    base = atomicAdd(ntodo, __popc(m));
+    atomicAdd(ntodo + 3 + cause, __popc(m));
+  }
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (want) todo[base + __popc(m & ((1u << lane) - 1u))] = (int32_t)t;
+}
+
+template <int KCAP, int LCAP>
+__global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* __restrict__ mean_out, int32_t* __restrict__ todo,
+                                                             int32_t* __restrict__ ntodo, int32_t* __restrict__ tile_ctr) {
+  extern __shared__ __align__(128) unsigned char sor_smem_raw[];
+  SorWarpSmem<LCAP>& w = reinterpret_cast<SorWarpSmem<LCAP>*>(sor_smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const unsigned full = 0xffffffffu;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  if (lane == 0) dfu_mbar_init(&w.mbar, 1);
+  __syncwarp();
+  unsigned phase = 0;
+  const int W = T.k > 32 ? T.k : 32;                       // curve window of step 1 (staged: +-32 positions)
+  for (;;) {
+    int tile = 0;
+    if (lane == 0) tile = atomicAdd(tile_ctr, 1);
+    tile = __shfl_sync(full, tile, 0);
+    if (tile >= T.ntiles) break;
+    const int64_t t0 = (int64_t)tile * 32, t = t0 + lane;
+    const int s = sor_seg_of(T.poff, T.nseg, t0);
+    const int64_t ps = T.poff[s], pe = T.poff[s + 1];
+    const int ns = (int)(T.seg_off[s + 1] - T.seg_off[s]);
+    const int kk = ns < T.k ? ns : T.k;
+    SorLane L;
+    const int orig = T.spi[t];
+    L.active = orig >= 0;
+    // ---- 1. bound from the curve neighbours: positions t-32 .. t+32 of the segment, staged from [t0-32, t0+64)
+    {
+      const int64_t a = t0 - 32 > ps ? t0 - 32 : ps, b = t0 + 64 < pe ? t0 + 64 : pe;
+      const int off = (int)(a - (t0 - 32));              // 0 or 32
+      if (lane == 0) {
+        const uint32_t bytes = (uint32_t)((b - a) >> 3) * (uint32_t)sizeof(SorGroup);
+        dfu_mbar_arrive_expect_tx(&w.mbar, bytes);
+        dfu_bulk_g2s(w.stage + (off >> 3), T.rec + (a >> 3), bytes, &w.mbar);
+      }
+      dfu_mbar_wait(&w.mbar, phase);
+      phase ^= 1u;
+      {
+        const int p = 32 + lane;
+        L.px = w.stage[p >> 3].x[p & 7]; L.py = w.stage[p >> 3].y[p & 7]; L.pz = w.stage[p >> 3].z[p & 7];
+      }
+      float best[KCAP];
+#pragma unroll
+      for (int i = 0; i < KCAP; i++) best[i] = INFINITY;
+      const int last = (int)(b - (t0 - 32)) - 1;          // last staged position
+      const int jlo = off - (32 + lane) > -W ? off - (32 + lane) : -W;
+      const int jhi = last - (32 + lane) < W ? last - (32 + lane) : W;
+      for (int j = jlo; j <= jhi; j++) {
+        const int p = 32 + lane + j;
+        const SorGroup& G = w.stage[p >> 3];
+        float v = __double2float_ru(sor_d2(G.x[p & 7], G.y[p & 7], G.z[p & 7], L.px, L.py, L.pz));   // pads: +inf
+#pragma unroll
+        for (int i = 0; i < KCAP; i++) {
+          const float lo = fminf(best[i], v);
+          v = fmaxf(best[i], v);
+          best[i] = lo;
+        }
+      }
+      // best[] ascends: the kk-th smallest is the largest of the first kk (a select chain keeps best[] in registers)
+      float kth = 0.f;
+#pragma unroll
+      for (int i = 0; i < KCAP; i++) kth = fmaxf(kth, i < kk ? best[i] : 0.f);
+      L.shi = (double)kth;
+      L.slo = -1.0;
+      __syncwarp();
+    }
+    // ---- 1b. lanes whose bound is far above the tile's median are handled one by one
+    {
+      float v = L.active ? (float)L.shi : INFINITY;
+#pragma unroll
+      for (int k2 = 2; k2 <= 32; k2 <<= 1)
+#pragma unroll
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+          const float o = __shfl_xor_sync(full, v, j);
+          const bool up = (lane & k2) == 0 || k2 == 32, lower = (lane & j) == 0;
+          v = (lower == up) ? fminf(v, o) : fmaxf(v, o);
+        }
+      const int nv = __popc(__ballot_sync(full, L.active));
+      const float med = __shfl_sync(full, v, nv > 0 ? nv >> 1 : 0);
+      const bool far = L.active && (!(L.shi < (double)INFINITY) || (float)L.shi > SOR_DEFER * med);
+      sor_defer(far, t, todo, ntodo, 0, lane);
+      if (far) L.active = false;
+    }
+    if (!__any_sync(full, L.active)) continue;
+    L.walk = L.active;
+    L.fx = (float)L.px; L.fy = (float)L.py; L.fz = (float)L.pz;
+    L.flim = L.walk ? sor_lane_flim(L.shi, L.fx, L.fy, L.fz) : -1.f;
+    w.opx[lane] = L.px; w.opy[lane] = L.py; w.opz[lane] = L.pz;
+    // ---- 2. pyramid descent to the level-1 nodes that meet the tile's search box
+    const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
+    int fsel = 0, nf = 0;
+    {
+      float4 qlo, qhi;
+      sor_search_box(L, qlo, qhi);
+      int lev = 1;
+      while (lev < T.nlev - 1 && ((glast >> (3 * lev)) - (gfirst >> (3 * lev)) + 1) > 32) lev++;
+      const int nfirst = gfirst >> (3 * lev), nlast = glast >> (3 * lev);
+      bool overflow = false;
+      for (int b0 = nfirst; b0 <= nlast; b0 += 32) {       // more than 32 nodes only at the top level
+        const int node = b0 + lane;
+        const bool hit = node <= nlast && sor_box_hits(T.lv[lev][node], qlo, qhi);
+        const unsigned bm = __ballot_sync(full, hit);
+        if (nf + __popc(bm) > SOR_FRONT) { overflow = true; break; }
+        if (hit) w.front[0][nf + __popc(bm & ((1u << lane) - 1u))] = node;
+        nf += __popc(bm);
+      }
+      __syncwarp();
+      while (!overflow && lev > 1) {
+        const int cl = lev - 1, cfirst = gfirst >> (3 * cl), clast = glast >> (3 * cl);
+        int nn = 0;
+        for (int f0 = 0; f0 < nf; f0 += 4) {
+          const int fi = f0 + (lane >> 3);
+          bool hit = false;
+          int c = -1;
+          if (fi < nf) {
+            c = w.front[fsel][fi] * 8 + (lane & 7);
+            if (c >= cfirst && c <= clast) hit = sor_box_hits(T.lv[cl][c], qlo, qhi);
+          }
+          const unsigned bm = __ballot_sync(full, hit);
+          if (nn + __popc(bm) > SOR_FRONT) { overflow = true; break; }
+          if (hit) w.front[fsel ^ 1][nn + __popc(bm & ((1u << lane) - 1u))] = c;
+          nn += __popc(bm);
+        }
+        __syncwarp();
+        fsel ^= 1; nf = nn; lev = cl;
+      }
+      if (overflow) {          // a search box that meets too many nodes (curve jump inside the tile): one by one
+        sor_defer(L.active, t, todo, ntodo, 1, lane);
         continue;
       }
-      // split into the (up to 8) children at level Mn - 1
-      const int Mc = Mn - 1;
-      const unsigned long long pre = (Mn < 16) ? ((__ldg(skey + r0) & 0xffffffffffffull) >> (3 * Mn)) : 0ull;
-      int cr[9];
-      cr[0] = r0; cr[8] = r1;
-      for (int c = 1; c < 8; c++)
-        cr[c] = sor_lower_bound(skey, cr[c - 1], r1, segbits | (((pre << 3) | (unsigned long long)c) << (3 * Mc)));
-      double cd[8];
-      int ord[8], nc = 0;
-      for (int c = 0; c < 8; c++) {
-        if (cr[c + 1] <= cr[c]) continue;
-        const unsigned long long cp = (pre << 3) | (unsigned long long)c;
-        const double d = sor_cell_d2(g, q, (int)sor_compact3(cp >> 2), (int)sor_compact3(cp >> 1), (int)sor_compact3(cp), Mc, slack);
-        if (d >= top.lim) continue;
-        int b = nc++;
-        while (b > 0 && cd[ord[b - 1]] < d) { ord[b] = ord[b - 1]; b--; }   // descending distance
-        ord[b] = c; cd[c] = d;
+    }
+    // ---- 3. passes: every neighbour with d2 <= shi goes to the lane's column; a lane that finds more than LCAP
+    //         narrows (slo, shi] to the shell that holds its k-th neighbour and walks again
+    int nl = 0;
+    for (int pass = 0; pass < 40; pass++) {
+      if (L.walk) {
+        const double wd = (L.shi - fmax(L.slo, 0.0)) * (1.0 / SOR_NBIN);
+        w.oshi[lane] = L.shi; w.oslo[lane] = L.slo; w.ow[lane] = wd; w.oinvw[lane] = wd > 0.0 ? 1.0 / wd : 0.0;
+#pragma unroll
+        for (int b = 0; b <= SOR_NBIN; b++) w.cnt[b][lane] = 0u;
       }
-      for (int a = 0; a < nc && sp < SOR_STACK; a++) {
-        const int c = ord[a];
-        st_r0[sp] = cr[c]; st_r1[sp] = cr[c + 1]; st_M[sp] = (signed char)Mc; sp++;
+      w.nl[lane] = 0;
+      __syncwarp();
+      sor_pass<LCAP>(T, w, fsel, nf, gfirst, glast, phase, L, lane);
+#ifdef SOR_STATS
+      if (lane == 0) { atomicAdd(&g_sor_stats[2], 1ull); atomicAdd(&g_sor_stats[4], (unsigned long long)nf); }
+      atomicAdd(&g_sor_stats[5], (unsigned long long)(L.walk ? 1 : 0));
+#endif
+      bool ties = false;
+      if (L.walk) {
+        nl = w.nl[lane];
+        L.walk = false;
+        L.flim = -1.f;
+        if (nl > LCAP) {
+          // the shell counts so far miss the LCAP neighbours that went into the column
+          const double slo = fmax(L.slo, 0.0), wd = w.ow[lane], invw = w.oinvw[lane];
+          for (int j = 0; j < LCAP; j++) {
+            const double d2 = w.list[j][lane];
+            w.cnt[d2 <= L.slo ? SOR_NBIN : sor_shell(d2, slo, wd, invw, L.shi)][lane] += 1u;
+          }
+          int cum = (int)w.cnt[SOR_NBIN][lane], bs = -1;
+#pragma unroll
+          for (int b = 0; b < SOR_NBIN; b++) {
+            if (bs < 0) {
+              cum += (int)w.cnt[b][lane];
+              if (cum >= kk) bs = b;
+            }
+          }
+          // neighbours up to shell bs: d2 <= e_bs, at least kk of them; those below e_(bs-1) are fewer than kk
+          const double nhi = bs < 0 ? L.shi : sor_edge(bs, slo, wd, L.shi);
+          const double nlo = bs <= 0 ? L.slo : sor_edge(bs - 1, slo, wd, L.shi);
+          ties = bs < 0 || !(nhi - fmax(nlo, 0.0) < L.shi - slo);       // no progress: equal distances
+          if (!ties) {
+            L.shi = nhi; L.slo = nlo;
+            L.walk = true;
+            L.flim = sor_lane_flim(L.shi, L.fx, L.fy, L.fz);
+          }
+        }
+      }
+      __syncwarp();
+      sor_defer(ties, t, todo, ntodo, 2, lane);
+      if (ties) L.active = false;
+      if (!__any_sync(full, L.walk)) break;
+    }
+    // ---- 4. the k' smallest in ascending order; sequential sum of square roots
+    {
+      const bool fin = L.active && !L.walk;
+      const int nlf = fin ? nl : 0;
+      double acc = 0.0;
+      for (int r = 0; r < kk; r++) {
+        double bv = inf;
+        int bi = 0;
+        for (int j = 0; j < nlf; j++) {
+          const double x = w.list[j][lane];
+          if (x < bv) { bv = x; bi = j; }
+        }
+        acc = __dadd_rn(acc, __dsqrt_rn(bv));
+        if (fin) w.list[bi][lane] = inf;
+        __syncwarp();                       // keep the warp together (the lanes' columns differ in length)
+      }
+      if (fin) mean_out[orig] = __ddiv_rn(acc, (double)kk);
+    }
+    sor_defer(L.active && L.walk, t, todo, ntodo, 2, lane);      // still narrowing after 40 passes: cannot happen
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- one warp per query (deferred queries, k > 32)
+#define SOR_STACK 128
+struct SorSingleSmem {
+  double sd[SOR_STACK];
+  int snode[SOR_STACK];
+  signed char slev[SOR_STACK];
+};
+
+__device__ __forceinline__ double sor_box_d2(const SorBox& b, double px, double py, double pz) {
+  const double dx = fmax(fmax((double)b.lo.x - px, px - (double)b.hi.x), 0.0), dy = fmax(fmax((double)b.lo.y - py, py - (double)b.hi.y), 0.0),
+               dz = fmax(fmax((double)b.lo.z - pz, pz - (double)b.hi.z), 0.0);
+  return (dx * dx + dy * dy + dz * dz) * (1.0 - 1e-12);      // lower bound of the distance to any point of the box
+}
+
+// insert v into the ascending list held one element per lane in b0 (ranks 0..31) and b1 (ranks 32..63)
+__device__ __forceinline__ void sor_insert(double v, double& b0, double& b1, bool two, int lane) {
+  const unsigned full = 0xffffffffu;
+  const int p0 = __popc(__ballot_sync(full, b0 <= v));
+  const double up0 = __shfl_up_sync(full, b0, 1);
+  const double carry = __shfl_sync(full, b0, 31);
+  if (p0 < 32) {
+    b0 = lane < p0 ? b0 : (lane == p0 ? v : up0);
+    if (two) {
+      const double up1 = __shfl_up_sync(full, b1, 1);
+      b1 = lane == 0 ? carry : up1;
+    }
+  } else if (two) {
+    const int p1 = __popc(__ballot_sync(full, b1 <= v));
+    const double up1 = __shfl_up_sync(full, b1, 1);
+    b1 = lane < p1 ? b1 : (lane == p1 ? v : up1);
+  }
+}
+
+__global__ void __launch_bounds__(128) k_sor_single(SorTree T, const int32_t* __restrict__ todo, const int32_t* __restrict__ ntodo,
+                                                    int all, double* __restrict__ mean_out) {
+  __shared__ SorSingleSmem sm[4];
+  SorSingleSmem& S = sm[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const unsigned full = 0xffffffffu;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  const int64_t nq = all ? (int64_t)T.ntiles * 32 : (int64_t)*ntodo;
+  const int64_t nw = (int64_t)gridDim.x * 4;
+  for (int64_t e = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5); e < nq; e += nw) {
+    const int64_t t = all ? e : (int64_t)todo[e];
+    const int orig = T.spi[t];
+    if (orig < 0) continue;
+    const int s = sor_seg_of(T.poff, T.nseg, t);
+    const int64_t ps = T.poff[s], pe = T.poff[s + 1];
+    const int ns = (int)(T.seg_off[s + 1] - T.seg_off[s]);
+    const int kk = ns < T.k ? ns : T.k;
+    const bool two = kk > 32;
+    const double px = T.rec[t >> 3].x[t & 7], py = T.rec[t >> 3].y[t & 7], pz = T.rec[t >> 3].z[t & 7];
+    const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
+    double b0 = inf, b1 = inf, kth = inf;
+    int sp = 0;
+    // start level: at most 32 nodes of the segment (or the top level); push them far-to-near
+    int lev = 1;
+    while (lev < T.nlev - 1 && ((glast >> (3 * lev)) - (gfirst >> (3 * lev)) + 1) > 32) lev++;
+    {
+      const int nfirst = gfirst >> (3 * lev), nlast = glast >> (3 * lev);
+      for (int b0i = nfirst; b0i <= nlast; b0i += 32) {
+        const int node = b0i + lane;
+        double d = inf;
+        if (node <= nlast) d = sor_box_d2(T.lv[lev][node], px, py, pz);
+        // rank by descending distance among the lanes of this batch (ties by lane)
+        int rank = 0;
+        for (int o = 0; o < 32; o++) {
+          const double od = __shfl_sync(full, d, o);
+          rank += (od > d || (od == d && o < lane)) ? 1 : 0;
+        }
+        const int nvalid = __popc(__ballot_sync(full, d < inf));
+        // lanes with d = inf rank first (they are the largest); valid lanes get ranks (32 - nvalid) .. 31
+        if (d < inf && sp + nvalid <= SOR_STACK) {
+          const int slot = sp + rank - (32 - nvalid);
+          S.sd[slot] = d; S.snode[slot] = node; S.slev[slot] = (signed char)lev;
+        }
+        sp += nvalid <= SOR_STACK - sp ? nvalid : 0;
+        __syncwarp();
       }
     }
+    while (sp > 0) {
+      sp--;
+      const double nd = S.sd[sp];
+      const int node = S.snode[sp], nl = S.slev[sp];
+      __syncwarp();
+      if (!(nd < kth)) continue;
+      if (nl == 1) {
+        // leaf: 64 consecutive sorted points (pads are +inf; positions outside the segment are skipped)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int64_t j = (int64_t)node * 64 + h * 32 + lane;
+          double c = inf;
+          if (j >= ps && j < pe) {
+            const SorGroup& G = T.rec[j >> 3];
+            c = sor_d2(G.x[j & 7], G.y[j & 7], G.z[j & 7], px, py, pz);
+          }
+          unsigned m = __ballot_sync(full, c < kth);
+          while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const double v = __shfl_sync(full, c, src);
+            if (v < kth) {
+              sor_insert(v, b0, b1, two, lane);
+              kth = kk <= 32 ? __shfl_sync(full, b0, kk - 1) : __shfl_sync(full, b1, kk - 33);
+            }
+          }
+        }
+      } else {
+        // inner node: its 8 children, nearest pushed last
+        const int cl = nl - 1, cfirst = gfirst >> (3 * cl), clast = glast >> (3 * cl);
+        const int c = node * 8 + (lane & 7);
+        double d = inf;
+        if (lane < 8 && c >= cfirst && c <= clast) {
+          d = sor_box_d2(T.lv[cl][c], px, py, pz);
+          if (!(d < kth)) d = inf;
+        }
+        int rank = 0;
+#pragma unroll
+        for (int o = 0; o < 8; o++) {
+          const double od = __shfl_sync(full, d, o);
+          rank += (od > d || (od == d && o < lane)) ? 1 : 0;
+        }
+        const int nvalid = __popc(__ballot_sync(full, d < inf));
+        if (d < inf && sp + nvalid <= SOR_STACK) {
+          const int slot = sp + rank - (8 - nvalid);
+          S.sd[slot] = d; S.snode[slot] = c; S.slev[slot] = (signed char)cl;
+        }
+        // the stack holds at most 7 siblings per level above the current path: SOR_STACK = 96 > 7 * SOR_MAXLEV + 32
+        sp += nvalid;
+        __syncwarp();
+      }
+    }
+    // ascending sum of square roots
+    const double q0 = __dsqrt_rn(b0), q1 = __dsqrt_rn(b1);
+    double acc = 0.0;
+    for (int r = 0; r < kk; r++) acc = __dadd_rn(acc, r < 32 ? __shfl_sync(full, q0, r) : __shfl_sync(full, q1, r - 32));
+    if (lane == 0) mean_out[orig] = __ddiv_rn(acc, (double)kk);
   }
-  // 4. ascending order, sequential sum of square roots (std::accumulate over the sorted k-NN distances)
-  for (int a = 1; a < kk; a++) {
-    const double v = top.v[a];
-    int b = a - 1;
-    while (b >= 0 && top.v[b] > v) { top.v[b + 1] = top.v[b]; b--; }
-    top.v[b + 1] = v;
-  }
-  double acc = 0.0;
-  for (int a = 0; a < kk; a++) acc = __dadd_rn(acc, __dsqrt_rn(top.v[a]));
-  mean_out[sidx[t]] = __ddiv_rn(acc, (double)kk);
 }
 
 // ---- order-fixed two-stage reductions ------------------------------------------------------------------
@@ -320,14 +819,22 @@ __device__ __forceinline__ double sor_block_sum(double v) {
   return r;   // valid in thread 0
 }
 
+// chunk c of segment s = points [seg_off[s] + (c - seg_ch[s]) * SOR_CHUNK, ...): chunks never straddle segments
 // PASS 0: sum of mean_i > 0;  PASS 1: sum of (mean_i - mu)^2 over mean_i > 0
 template <int PASS>
-__global__ void __launch_bounds__(256) k_sor_chunk_sum(const double* __restrict__ mean, const int32_t* __restrict__ ch_seg,
-                                                       const int64_t* __restrict__ ch_start, const int64_t* __restrict__ seg_off,
-                                                       const double* __restrict__ segstat, double* __restrict__ part) {
+__global__ void __launch_bounds__(256) k_sor_chunk_sum(const double* __restrict__ mean, const int32_t* __restrict__ seg_ch, int nseg,
+                                                       const int64_t* __restrict__ seg_off, const double* __restrict__ segstat,
+                                                       double* __restrict__ part) {
   const int c = blockIdx.x;
-  const int s = ch_seg[c];
-  const int64_t a = ch_start[c];
+  int lo = 0, hi = nseg;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (seg_ch[mid] <= c) lo = mid; else hi = mid;
+  }
+  // empty segments own no chunk: step over them
+  int s = lo;
+  while (s + 1 < nseg && seg_ch[s + 1] <= c) s++;
+  const int64_t a = seg_off[s] + (int64_t)(c - seg_ch[s]) * SOR_CHUNK;
   int64_t b = a + SOR_CHUNK;
   if (b > seg_off[s + 1]) b = seg_off[s + 1];
   const double mu = PASS ? segstat[4 * s] : 0.0;
@@ -361,12 +868,12 @@ __global__ void __launch_bounds__(256) k_sor_seg_fin(const double* __restrict__ 
   }
 }
 
-__global__ void __launch_bounds__(256) k_sor_mask(const double* __restrict__ mean, const int32_t* __restrict__ seg, int64_t n,
-                                                  const double* __restrict__ segstat, uint8_t* __restrict__ keep) {
+__global__ void __launch_bounds__(256) k_sor_mask(const double* __restrict__ mean, const int64_t* __restrict__ seg_off, int nseg,
+                                                  int64_t n, const double* __restrict__ segstat, uint8_t* __restrict__ keep) {
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
   const double m = mean[i];
-  keep[i] = (m > 0.0 && m < segstat[4 * seg[i] + 2]) ? 1 : 0;
+  keep[i] = (m > 0.0 && m < segstat[4 * sor_seg_of(seg_off, nseg, i) + 2]) ? 1 : 0;
 }
 
 extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host, int k,
@@ -376,94 +883,165 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
   if (nseg > 65535) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: %d segments (max 65535)", nseg);
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t n = seg_off_host[nseg];
-  if (n >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: too many points");
   for (int s = 0; s < nseg; s++)
     if (seg_off_host[s + 1] < seg_off_host[s]) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_sor_filter: seg_off must ascend");
   if (out_stats_host) memset(out_stats_host, 0, (size_t)nseg * 16);
   if (n == 0) return DFU_OK;
   if (!xyz) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_sor_filter: xyz is NULL");
-  // chunk table (host): chunks never straddle segments
-  std::vector<int32_t> ch_seg, seg_ch(nseg + 1);
-  std::vector<int64_t> ch_start;
+  // per-segment tables (host, O(nseg)): padded offsets (multiples of 32) and first chunk of the reductions.  They are
+  // uploaded from pageable memory: cudaMemcpyAsync returns once the bytes are staged, so no stream sync is needed.
+  int64_t* tab = (int64_t*)malloc((size_t)(nseg + 1) * 12);
+  if (!tab) return dfu_set_err(ctx, DFU_ERR_CUDA, "dfu_sor_filter: out of host memory");
+  int64_t* poff_h = tab;
+  int32_t* segch_h = (int32_t*)(tab + nseg + 1);
+  int64_t np = 0, nch64 = 0;
   for (int s = 0; s < nseg; s++) {
-    seg_ch[s] = (int32_t)ch_seg.size();
-    for (int64_t a = seg_off_host[s]; a < seg_off_host[s + 1]; a += SOR_CHUNK) { ch_seg.push_back(s); ch_start.push_back(a); }
+    const int64_t c = seg_off_host[s + 1] - seg_off_host[s];
+    poff_h[s] = np; segch_h[s] = (int32_t)nch64;
+    np += (c + 31) / 32 * 32;
+    nch64 += (c + SOR_CHUNK - 1) / SOR_CHUNK;
   }
-  seg_ch[nseg] = (int32_t)ch_seg.size();
-  const int nch = (int)ch_seg.size();
-  DFU_SLOT(ctx, x, double*, SO_X, n * 8);
-  DFU_SLOT(ctx, y, double*, SO_Y, n * 8);
-  DFU_SLOT(ctx, z, double*, SO_Z, n * 8);
-  DFU_SLOT(ctx, seg, int32_t*, SO_SEG, n * 4);
-  DFU_SLOT(ctx, seg_off, int64_t*, SO_SEGOFF, (size_t)(nseg + 1) * 8);
-  DFU_SLOT(ctx, box, unsigned long long*, SO_BOX, (size_t)nseg * 48 + 64);
-  DFU_SLOT(ctx, key, unsigned long long*, SO_KEY, n * 8);
-  DFU_SLOT(ctx, idx, int32_t*, SO_IDX, n * 4);
-  DFU_SLOT(ctx, skey, unsigned long long*, SO_SKEY, n * 8);
-  DFU_SLOT(ctx, sidx, int32_t*, SO_SIDX, n * 4);
-  DFU_SLOT(ctx, sx, double*, SO_SX, n * 8);
-  DFU_SLOT(ctx, sy, double*, SO_SY, n * 8);
-  DFU_SLOT(ctx, sz, double*, SO_SZ, n * 8);
-  DFU_SLOT(ctx, chs, int32_t*, SO_CHSEG, (size_t)nch * 4);
-  DFU_SLOT(ctx, cha, int64_t*, SO_CHSTART, (size_t)nch * 8);
-  DFU_SLOT(ctx, part, double*, SO_PART, (size_t)nch * 8);
-  DFU_SLOT(ctx, segstat, double*, SO_SEGSTAT, (size_t)nseg * 32);
-  DFU_SLOT(ctx, segch, int32_t*, SO_SEGCH, (size_t)(nseg + 1) * 4);
+  poff_h[nseg] = np; segch_h[nseg] = (int32_t)nch64;
+  if (np >= 0x7fffffffLL) { free(tab); return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: too many points"); }
+  const int nch = (int)nch64, ntiles = (int)(np / 32);
+  // pyramid geometry
+  SorTree T;
+  memset(&T, 0, sizeof(T));
+  int64_t nodes = 0;
+  {
+    int c = (int)(np / 8), L = 0;
+    while (true) {
+      T.nlv[L] = c; nodes += c; L++;
+      if (c <= 8 || L == SOR_MAXLEV) break;
+      c = (c + 7) / 8;
+    }
+    T.nlev = L;
+    if (T.nlev < 2) { T.nlv[1] = 1; nodes += 1; T.nlev = 2; }
+  }
+#define SOR_SLOT(var, type, id, bytes)                      \
+  type var = (type)dfu_slot(ctx, id, bytes);                \
+  if (!var) { free(tab); return DFU_ERR_CUDA; }
+  SOR_SLOT(seg_off, int64_t*, SO_SEGOFF, (size_t)(nseg + 1) * 8);
+  SOR_SLOT(poff, int64_t*, SO_POFF, (size_t)(nseg + 1) * 8);
+  SOR_SLOT(segch, int32_t*, SO_SEGCH, (size_t)(nseg + 1) * 4);
+  SOR_SLOT(box, unsigned long long*, SO_BOX, (size_t)nseg * 48);
+  SOR_SLOT(key, unsigned long long*, SO_KEY, n * 8);
+  SOR_SLOT(idx, int32_t*, SO_IDX, n * 4);
+  SOR_SLOT(skey, unsigned long long*, SO_SKEY, n * 8);
+  SOR_SLOT(sidx, int32_t*, SO_SIDX, n * 4);
+  SOR_SLOT(rec, SorGroup*, SO_REC, (size_t)(np / 8) * sizeof(SorGroup));
+  SOR_SLOT(spi, int32_t*, SO_SPI, np * 4);
+  SOR_SLOT(pyr, SorBox*, SO_PYR, (size_t)nodes * sizeof(SorBox));
+  SOR_SLOT(todo, int32_t*, SO_TODO, np * 4);
+  SOR_SLOT(scal, int32_t*, SO_SCAL, 64);          // [0] error flag, [1] deferred count, [2] tile counter
+  SOR_SLOT(part, double*, SO_PART, (size_t)(nch > 0 ? nch : 1) * 8);
+  SOR_SLOT(segstat, double*, SO_SEGSTAT, (size_t)nseg * 32);
   double* mean = out_mean;
   if (!mean) {
     mean = (double*)dfu_slot(ctx, SO_MEAN, n * 8);
-    if (!mean) return DFU_ERR_CUDA;
+    if (!mean) { free(tab); return DFU_ERR_CUDA; }
   }
-  int32_t* errflag = (int32_t*)(box + (size_t)nseg * 6);
-  DFU_CUDA(ctx, cudaMemcpyAsync(seg_off, seg_off_host, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(chs, ch_seg.data(), (size_t)nch * 4, cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(cha, ch_start.data(), (size_t)nch * 8, cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(segch, seg_ch.data(), (size_t)(nseg + 1) * 4, cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));   // the host vectors above go out of scope
+  cudaError_t ce = cudaMemcpyAsync(seg_off, seg_off_host, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st);
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(poff, poff_h, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st);
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(segch, segch_h, (size_t)(nseg + 1) * 4, cudaMemcpyHostToDevice, st);
+  free(tab);
+  if (ce != cudaSuccess) return dfu_set_err(ctx, DFU_ERR_CUDA, "dfu_sor_filter: upload: %s", cudaGetErrorString(ce));
+  {
+    SorBox* p = pyr;
+    for (int L = 0; L < T.nlev; L++) { T.lv[L] = p; p += T.nlv[L]; }
+  }
+  T.rec = rec; T.spi = spi; T.seg_off = seg_off; T.poff = poff; T.nseg = nseg; T.ntiles = ntiles; T.k = k;
   const unsigned nb = (unsigned)((n + 255) / 256);
   {
     DFU_PROF(ctx, st, PT_GRID_BUILD);
-    // box minima start at all-ones, maxima (and the error flag behind them) at zero
-    DFU_CUDA(ctx, cudaMemsetAsync(box, 0, (size_t)nseg * 48 + 64, st));
+    // box minima start at all-ones, maxima at zero; scalars at zero
+    DFU_CUDA(ctx, cudaMemsetAsync(box, 0, (size_t)nseg * 48, st));
     DFU_CUDA(ctx, cudaMemset2DAsync(box, 48, 0xFF, 24, (size_t)nseg, st));
-    k_sor_prepare<<<nb, 256, 0, st>>>(xyz, n, seg_off, nseg, x, y, z, seg, box);
+    DFU_CUDA(ctx, cudaMemsetAsync(scal, 0, 64, st));
+    k_sor_bbox<<<nb, 256, 0, st>>>(xyz, n, seg_off, nseg, box, scal);
     DFU_LAUNCH_CHECK(ctx);
-    k_sor_keys<<<nb, 256, 0, st>>>(x, y, z, seg, n, box, key, idx, errflag);
+    k_sor_keys<<<nb, 256, 0, st>>>(xyz, n, seg_off, nseg, box, key, idx);
     DFU_LAUNCH_CHECK(ctx);
+    int segbits = 0;
+    while ((1 << segbits) < nseg) segbits++;
     size_t tb = 0;
-    DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, key, skey, idx, sidx, (int)n, 0, 64, st));
+    DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, key, skey, idx, sidx, (int)n, 0, 48 + segbits, st));
     DFU_SLOT(ctx, tmp, void*, SO_TMP, tb);
-    DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, key, skey, idx, sidx, (int)n, 0, 64, st));
-    ctx->launches += 8;
-    k_sor_gather<<<nb, 256, 0, st>>>(sidx, x, y, z, n, sx, sy, sz);
+    DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, key, skey, idx, sidx, (int)n, 0, 48 + segbits, st));
+    ctx->launches += 7;
+    k_sor_gather<<<(unsigned)(((int64_t)ntiles * 32 + 255) / 256), 256, 0, st>>>(sidx, xyz, seg_off, poff, nseg, ntiles, rec, spi,
+                                                                                  (SorBox*)T.lv[0]);
     DFU_LAUNCH_CHECK(ctx);
+    for (int L = 1; L < T.nlev; L++) {
+      k_sor_pyr<<<(T.nlv[L] + 255) / 256, 256, 0, st>>>(T.lv[L - 1], T.nlv[L - 1], (SorBox*)T.lv[L], T.nlv[L]);
+      DFU_LAUNCH_CHECK(ctx);
+    }
   }
   {
     DFU_PROF(ctx, st, PT_SOR_KNN);
-    k_sor_knn<<<(unsigned)((n + SOR_THREADS - 1) / SOR_THREADS), SOR_THREADS, 0, st>>>(skey, sidx, sx, sy, sz, n, seg_off, box, k, mean);
-    DFU_LAUNCH_CHECK(ctx);
+    const int grid_single = 148 * 8;
+    if (k <= SOR_KFAST) {
+      int grid = 148 * 8;
+      if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
+      if (k <= 20) {
+        const size_t smem = sizeof(SorWarpSmem<40>) * SOR_WARPS;
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<20, 40>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_sor_tile<20, 40><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
+      } else {
+        const size_t smem = sizeof(SorWarpSmem<64>) * SOR_WARPS;
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_sor_tile<32, 64><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
+      }
+      DFU_LAUNCH_CHECK(ctx);
+      k_sor_single<<<grid_single, 128, 0, st>>>(T, todo, scal + 1, 0, mean);
+      DFU_LAUNCH_CHECK(ctx);
+    } else {
+      k_sor_single<<<grid_single, 128, 0, st>>>(T, todo, scal + 1, 1, mean);
+      DFU_LAUNCH_CHECK(ctx);
+    }
   }
   {
     DFU_PROF(ctx, st, PT_SOR_MASK);
-    k_sor_chunk_sum<0><<<nch, 256, 0, st>>>(mean, chs, cha, seg_off, segstat, part);
+    k_sor_chunk_sum<0><<<nch, 256, 0, st>>>(mean, segch, nseg, seg_off, segstat, part);
     DFU_LAUNCH_CHECK(ctx);
     k_sor_seg_fin<0><<<nseg, 256, 0, st>>>(part, segch, seg_off, std_ratio, segstat);
     DFU_LAUNCH_CHECK(ctx);
-    k_sor_chunk_sum<1><<<nch, 256, 0, st>>>(mean, chs, cha, seg_off, segstat, part);
+    k_sor_chunk_sum<1><<<nch, 256, 0, st>>>(mean, segch, nseg, seg_off, segstat, part);
     DFU_LAUNCH_CHECK(ctx);
     k_sor_seg_fin<1><<<nseg, 256, 0, st>>>(part, segch, seg_off, std_ratio, segstat);
     DFU_LAUNCH_CHECK(ctx);
-    k_sor_mask<<<nb, 256, 0, st>>>(mean, seg, n, segstat, out_keep);
+    k_sor_mask<<<nb, 256, 0, st>>>(mean, seg_off, nseg, n, segstat, out_keep);
     DFU_LAUNCH_CHECK(ctx);
   }
   if (out_stats_host) {
-    std::vector<double> hs((size_t)nseg * 4);
-    int32_t e = 0;
-    DFU_CUDA(ctx, cudaMemcpyAsync(hs.data(), segstat, (size_t)nseg * 32, cudaMemcpyDeviceToHost, st));
-    DFU_CUDA(ctx, cudaMemcpyAsync(&e, errflag, 4, cudaMemcpyDeviceToHost, st));
-    DFU_CUDA(ctx, cudaStreamSynchronize(st));
-    if (e) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: a coordinate is NaN or infinite");
-    for (int s = 0; s < nseg; s++) { out_stats_host[2 * s] = hs[4 * s]; out_stats_host[2 * s + 1] = hs[4 * s + 1]; }
+    double* hs = (double*)malloc((size_t)nseg * 32 + 64);
+    if (!hs) return dfu_set_err(ctx, DFU_ERR_CUDA, "dfu_sor_filter: out of host memory");
+    int32_t e[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const int32_t* e4 = e + 4;
+    cudaError_t c2 = cudaMemcpyAsync(hs, segstat, (size_t)nseg * 32, cudaMemcpyDeviceToHost, st);
+    if (c2 == cudaSuccess) c2 = cudaMemcpyAsync(e, scal, 32, cudaMemcpyDeviceToHost, st);
+    if (c2 == cudaSuccess) c2 = cudaStreamSynchronize(st);
+    if (c2 == cudaSuccess)
+      for (int s = 0; s < nseg; s++) { out_stats_host[2 * s] = hs[4 * s]; out_stats_host[2 * s + 1] = hs[4 * s + 1]; }
+    free(hs);
+    if (c2 != cudaSuccess) return dfu_set_err(ctx, DFU_ERR_CUDA, "dfu_sor_filter: read-back: %s", cudaGetErrorString(c2));
+    if (e[0]) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: a coordinate is NaN or infinite");
+    ctx->sor_deferred = e[1];
+    for (int c = 0; c < 3; c++) ctx->sor_cause[c] = e4[c];
+    ctx->sor_points = n;
   }
   return DFU_OK;
+}
+
+extern "C" int64_t dfu_sor_counter(const dfu_ctx* ctx, int which) {
+  if (!ctx) return -1;
+#ifdef SOR_STATS
+  if (which >= 10 && which < 18) {
+    unsigned long long h[8];
+    cudaMemcpyFromSymbol(h, g_sor_stats, sizeof(h));
+    return (int64_t)h[which - 10];
+  }
+#endif
+  if (which >= 2 && which <= 4) return ctx->sor_cause[which - 2];
+  return which == 0 ? ctx->sor_deferred : ctx->sor_points;
 }

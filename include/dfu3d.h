@@ -211,6 +211,11 @@ int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, c
 int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
                    int k, double std_ratio, uint8_t* out_keep, double* out_mean, double* out_stats_host);
 
+/* Diagnostics of the last dfu_sor_filter call that returned statistics (out_stats_host != NULL):
+ * which = 0: queries that were handled one by one (k_sor_single) instead of by the tile kernel; 1: points of that call;
+ * 2..4: of those queries, deferred for a far bound / a search box meeting too many nodes / ties at the k-th distance. */
+int64_t dfu_sor_counter(const dfu_ctx* ctx, int which);
+
 /* BallQuery gate: keep[i] = min_j |query_i - ref_j| < max_dist. */
 int dfu_nn_gate(dfu_ctx* ctx, void* stream, const double* query_xyz, int64_t nq, const double* ref_xyz, int64_t nr,
                 double max_dist, uint8_t* out_keep);
