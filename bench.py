@@ -163,7 +163,8 @@ def run_reference(a):
             jobs = [(910000 + (k * per_step + i) // a.cams, a.cams, a.sweeps, (k * per_step + i) % a.cams, a.max_inst)
                     for i in range(per_step)]
             res = pool.map(_cpu_view_worker, jobs, chunksize=1)
-            # wall time of the parallel step = the busiest worker's share: total compute seconds / workers
+            # step time = MEAN worker: summed compute seconds / workers (a lower bound of the wall time of the parallel
+            # step, i.e. it favours the CPU arm)
             return sum(r[0] for r in res) / float(procs)
         for w in range(1):                  # ONE warm-up step whatever --warmup says: a CPU step costs ~20 s
             step(1000 + w)                  # imports + first-touch in every worker
@@ -172,7 +173,7 @@ def run_reference(a):
     tot = sum(times)
     value = (per_step * a.steps / float(a.cams)) / tot
     sample = ('%d views per step (%d worker processes x %d), %d-cam %d-sweep nuScenes-shaped frames, one whole view per '
-              'worker, inputs generated outside the timed part; step time = summed compute seconds / workers' % (per_step, procs, max(1, a.cpu_sample_views), a.cams, a.sweeps))
+              'worker, inputs generated outside the timed part; step time = summed compute seconds / workers (the mean worker, not the busiest)' % (per_step, procs, max(1, a.cpu_sample_views), a.cams, a.sweeps))
     line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup,
             'ms_per_step': 1000.0 * tot / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic', 'impl': 'reference', 'config': workload_config(a),
@@ -286,7 +287,10 @@ def main():
     numa = bind_to_gpu_numa(local) if world > 1 else None
     dev = torch.device('cuda', local)
     if world > 1:
-        os.environ['NCCL_DEBUG'] = os.environ.get('DFU_NCCL_DEBUG', 'NONE')    # WARN still prints the version banner on stdout: keep stdout to the ONE JSON line
+        # an externally set NCCL_DEBUG is honoured (the driver counts ranks from the INFO lines); NCCL writes to fd 1,
+        # which is pointed at stderr while the communicator is created so that stdout stays the ONE JSON line
+        if 'DFU_NCCL_DEBUG' in os.environ:
+            os.environ['NCCL_DEBUG'] = os.environ['DFU_NCCL_DEBUG']
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         # NCCL writes its banner to fd 1 when the communicator is created (first collective): keep it off stdout
         sys.stdout.flush()
@@ -311,12 +315,25 @@ def main():
     del frames
     host = pipeline.HostBatch.from_device(vb)          # pinned host copies of every input tensor
 
+    from dfu3d_b200 import shard
+    # global frame id / camera ordinal of every local view: rank r owns frames {i : i mod world == r}
+    frame_of_view = [(rank + world * (v // a.cams), v % a.cams) for v in range(a.frames * a.cams)]
+    gathered = {'boxes': 0}
+
+    def finish(res):
+        # the step delivers what depth2pointsrgbpm delivers: the label text of every box (formatted on the host) and, at
+        # N > 1, the host-side gather of the pseudo-box lists (north star; dfu3d_b200/shard.py) -- both inside the timed region
+        if world > 1:
+            allb = shard.gather_boxes(shard.globalise(res.boxes, frame_of_view), device=dev)
+            gathered['boxes'] = int(allb.shape[0])
+        return res
+
     def step_resident():
         vb.labelmap = None
-        return pipe.run(vb, cloud_dtype=torch.float16, instances=True, want_lines=False)
+        return finish(pipe.run(vb, cloud_dtype=torch.float16, instances=True, want_lines=True))
 
     def step_e2e():
-        return pipe.run_host(host, cloud_dtype=torch.float16, want_lines=False)
+        return finish(pipe.run_host(host, cloud_dtype=torch.float16, want_lines=True))
 
     def barrier():
         if world > 1:

@@ -35,21 +35,48 @@ __global__ void __launch_bounds__(256) k_cluster_aux(DfuGrid g, const double* __
                                                      double* __restrict__ sR, CellAux* __restrict__ aux,
                                                      int32_t* __restrict__ parent, int32_t* __restrict__ rootmin) {
   const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (t >= g.n) return;
-  const int s = (int)(g.skey[t] >> 48);
-  const double x = g.sx[t], y = g.sy[t];
-  // R = R0 + Rd * np.linalg.norm([x, y])   (rectangle_fitting.py:167)
-  const double R = __dadd_rn(R0[s], __dmul_rn(Rd[s], __dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)))));
-  sR[t] = R;
-  const int c = g.pcell[t];
-  atomicMin(&aux[c].minx, dfu_order_f64(x));
-  atomicMax(&aux[c].maxx, dfu_order_f64(x));
-  atomicMin(&aux[c].miny, dfu_order_f64(y));
-  atomicMax(&aux[c].maxy, dfu_order_f64(y));
-  atomicMax(&aux[c].maxR, dfu_order_f64(R));
-  if (t == g.ustart[c]) {
-    parent[c] = c;
-    rootmin[c] = 0x7fffffff;
+  const bool ok = t < g.n;
+  int c = -1;
+  unsigned long long bx = 0, by = 0, bR = 0;
+  if (ok) {
+    const int s = (int)(g.skey[t] >> 48);
+    const double x = g.sx[t], y = g.sy[t];
+    // R = R0 + Rd * np.linalg.norm([x, y])   (rectangle_fitting.py:167)
+    const double R = __dadd_rn(R0[s], __dmul_rn(Rd[s], __dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)))));
+    sR[t] = R;
+    // The pair test visits the 5x5 cell neighbourhood (cell edge R0 / sqrt(2)): exact only while R <= 2 cells.  A
+    // caller-supplied R0 <= 0, Rd < 0 or an R beyond that is an error (sticky flag, bit 1), never silently wrong clusters.
+    if (!(R0[s] > 0.0) || Rd[s] < 0.0 || !(R <= 2.0 * g.cell[s])) atomicOr(g.errflag, 2);
+    c = g.pcell[t];
+    bx = dfu_order_f64(x); by = dfu_order_f64(y); bR = dfu_order_f64(R);
+    if (t == g.ustart[c]) {
+      parent[c] = c;
+      rootmin[c] = 0x7fffffff;
+    }
+  }
+  const int c0 = __shfl_sync(0xffffffffu, c, 0);
+  if (__all_sync(0xffffffffu, c == c0)) {
+    if (c0 < 0) return;
+    // the whole warp sits in one cell (cells hold hundreds of points): shuffle reduction, 5 atomics per warp
+    unsigned long long mnx = bx, mxx = bx, mny = by, mxy = by, mxR = bR;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long a0 = __shfl_xor_sync(0xffffffffu, mnx, o), a1 = __shfl_xor_sync(0xffffffffu, mxx, o),
+                               a2 = __shfl_xor_sync(0xffffffffu, mny, o), a3 = __shfl_xor_sync(0xffffffffu, mxy, o),
+                               a4 = __shfl_xor_sync(0xffffffffu, mxR, o);
+      mnx = a0 < mnx ? a0 : mnx; mxx = a1 > mxx ? a1 : mxx; mny = a2 < mny ? a2 : mny; mxy = a3 > mxy ? a3 : mxy;
+      mxR = a4 > mxR ? a4 : mxR;
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(&aux[c0].minx, mnx); atomicMax(&aux[c0].maxx, mxx); atomicMin(&aux[c0].miny, mny); atomicMax(&aux[c0].maxy, mxy);
+      atomicMax(&aux[c0].maxR, mxR);
+    }
+  } else if (ok) {
+    atomicMin(&aux[c].minx, bx);
+    atomicMax(&aux[c].maxx, bx);
+    atomicMin(&aux[c].miny, by);
+    atomicMax(&aux[c].maxy, by);
+    atomicMax(&aux[c].maxR, bR);
   }
 }
 
@@ -96,9 +123,11 @@ __global__ void __launch_bounds__(C_THREADS) k_cluster_pairs(DfuGrid g, const do
       if (k != ~0ull) {
         const int cx = (int)((k >> 32) & 0xffff) + c_off[o][0], cy = (int)((k >> 16) & 0xffff) + c_off[o][1];
         if (cx >= 1 && cy >= 1 && cx < 65535 && cy < 65535) {
-          const unsigned long long k2 = dfu_grid_key((int)(k >> 48), cx, cy, 1);
-          const int c2 = dfu_lower_bound_u64(g.ukey, ncell, k2);
-          if (c2 < ncell && g.ukey[c2] == k2 && uf_find(parent, c) != uf_find(parent, c2)) s_c2 = c2;
+          const int sg = (int)(k >> 48);
+          const unsigned long long k2 = dfu_grid_key(sg, cx, cy, 1);
+          const int sc0 = g.segcell[sg], sc1 = g.segcell[sg + 1];
+          const int c2 = sc0 + dfu_lower_bound_u64(g.ukey + sc0, sc1 - sc0, k2);
+          if (c2 < sc1 && g.ukey[c2] == k2 && uf_find(parent, c) != uf_find(parent, c2)) s_c2 = c2;
         }
       }
     }
@@ -252,98 +281,137 @@ __device__ __forceinline__ void fit_project(double x, double y, double cs, doubl
   c2 = __dadd_rn(__dmul_rn(x, -sn), __dmul_rn(y, cs));     // X @ [-sin, cos]   (:125)
 }
 
-// Reductions over a GROUP of G threads (G = 32: one warp, shuffles only; G = 256: one block, shuffles + shared memory).
-// Clusters of a few hundred points get a warp per (cluster, angle); the few clusters with more than FIT_BIG points
-// get a block, so that the kernel's duration is not the serial walk of one warp through the largest cluster.
-#define FIT_BIG 2048
-template <int G, int OP> __device__ __forceinline__ double group_reduce(double v) {
+// One CTA per cluster.  The cluster's points (contiguous in the gathered arrays) are staged ONCE in shared memory with two
+// TMA bulk copies (x and y; cp.async.bulk + mbarrier) and the 89 angles loop over the staged copy: round 1 re-read the
+// points from global memory 89 x 3 times per cluster.  Clusters of up to FIT_WARP_MAX points give every warp its own angles
+// (shuffle reductions only); larger ones work on one angle at a time with all 256 threads.  Clusters that do not fit
+// the staging buffer (> FIT_STAGE points) read global memory as before.
+#define FIT_STAGE 3072      /* points staged per cluster (48 KB) */
+#define FIT_WARP_MAX 512
+
+__device__ __forceinline__ double fit_block_reduce(double v, int op, double* sh) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const double w = __shfl_xor_sync(0xffffffffu, v, o);
-    v = OP == 0 ? fmin(v, w) : (OP == 1 ? fmax(v, w) : v + w);
+    v = op == 0 ? fmin(v, w) : (op == 1 ? fmax(v, w) : v + w);
   }
-  if (G == 32) return v;
-  __shared__ double sh[8];
   __syncthreads();                       // previous use of sh is over
   if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
   __syncthreads();
   double r = sh[0];
 #pragma unroll
-  for (int i = 1; i < 8; i++) r = OP == 0 ? fmin(r, sh[i]) : (OP == 1 ? fmax(r, sh[i]) : r + sh[i]);
+  for (int i = 1; i < 8; i++) r = op == 0 ? fmin(r, sh[i]) : (op == 1 ? fmax(r, sh[i]) : r + sh[i]);
   return r;
 }
+__device__ __forceinline__ double fit_warp_reduce(double v, int op) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double w = __shfl_xor_sync(0xffffffffu, v, o);
+    v = op == 0 ? fmin(v, w) : (op == 1 ? fmax(v, w) : v + w);
+  }
+  return v;
+}
 
-// one group per (cluster, angle): variance criterion (rectangle_fitting.py:83-111), np.var = mean((d - mean(d))^2)
-template <int G>
-__global__ void __launch_bounds__(256) k_fit_cost(const double* __restrict__ cx, const double* __restrict__ cy,
-                                                  const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
-                                                  int na, double* __restrict__ cost, const int32_t* __restrict__ big) {
-  const int lane = threadIdx.x % G;
-  const long long nunits = G == 32 ? (long long)K * na : (long long)big[0] * na;
-  // G = 32: one warp per (cluster, angle), large clusters skipped; G = 256: persistent blocks over the listed ones
-  for (long long w = G == 32 ? ((long long)blockIdx.x * 256 + threadIdx.x) / 32 : blockIdx.x; w < nunits;
-       w += G == 32 ? nunits : gridDim.x) {
-  const int k = G == 32 ? (int)(w / na) : big[1 + w / na], a = (int)(w % na);
-  const int p0 = coff[k], p1 = coff[k + 1];
-  if (G == 32 && p1 - p0 > FIT_BIG) return;
-  const double cs = angles[2 * a], sn = angles[2 * a + 1];
+// variance criterion of one angle over points px/py [n], lanes lane, lane + G, ...  (rectangle_fitting.py:83-111;
+// np.var = mean((d - mean(d))^2)).  BLOCK: reductions over the 256 threads, else over the warp.
+template <bool BLOCK>
+__device__ __forceinline__ double fit_angle_cost(const double* __restrict__ px, const double* __restrict__ py, int n, double cs, double sn,
+                                                 int lane, double* sh, double* ext) {
+  const int G = BLOCK ? 256 : 32;
   double mn1 = INFINITY, mx1 = -INFINITY, mn2 = INFINITY, mx2 = -INFINITY;
-  for (int p = p0 + lane; p < p1; p += G) {
+  for (int p = lane; p < n; p += G) {
     double c1, c2;
-    fit_project(cx[p], cy[p], cs, sn, c1, c2);
+    fit_project(px[p], py[p], cs, sn, c1, c2);
     mn1 = fmin(mn1, c1); mx1 = fmax(mx1, c1); mn2 = fmin(mn2, c2); mx2 = fmax(mx2, c2);
   }
-  mn1 = group_reduce<G, 0>(mn1); mx1 = group_reduce<G, 1>(mx1); mn2 = group_reduce<G, 0>(mn2); mx2 = group_reduce<G, 1>(mx2);
+  if (BLOCK) {
+    mn1 = fit_block_reduce(mn1, 0, sh); mx1 = fit_block_reduce(mx1, 1, sh); mn2 = fit_block_reduce(mn2, 0, sh); mx2 = fit_block_reduce(mx2, 1, sh);
+  } else {
+    mn1 = fit_warp_reduce(mn1, 0); mx1 = fit_warp_reduce(mx1, 1); mn2 = fit_warp_reduce(mn2, 0); mx2 = fit_warp_reduce(mx2, 1);
+  }
+  if (ext) { ext[0] = mn1; ext[1] = mn2; ext[2] = mx1; ext[3] = mx2; }
   double s1 = 0, s2 = 0, n1 = 0, n2 = 0;
-  for (int p = p0 + lane; p < p1; p += G) {
+  for (int p = lane; p < n; p += G) {
     double c1, c2;
-    fit_project(cx[p], cy[p], cs, sn, c1, c2);
+    fit_project(px[p], py[p], cs, sn, c1, c2);
     const double D1 = fmin(fabs(mx1 - c1), fabs(c1 - mn1)), D2 = fmin(fabs(mx2 - c2), fabs(c2 - mn2));
     if (D1 < D2) { s1 += D1; n1 += 1; } else { s2 += D2; n2 += 1; }
   }
-  s1 = group_reduce<G, 2>(s1); s2 = group_reduce<G, 2>(s2); n1 = group_reduce<G, 2>(n1); n2 = group_reduce<G, 2>(n2);
+  if (BLOCK) {
+    s1 = fit_block_reduce(s1, 2, sh); s2 = fit_block_reduce(s2, 2, sh); n1 = fit_block_reduce(n1, 2, sh); n2 = fit_block_reduce(n2, 2, sh);
+  } else {
+    s1 = fit_warp_reduce(s1, 2); s2 = fit_warp_reduce(s2, 2); n1 = fit_warp_reduce(n1, 2); n2 = fit_warp_reduce(n2, 2);
+  }
   const double m1 = n1 > 0 ? s1 / n1 : 0.0, m2 = n2 > 0 ? s2 / n2 : 0.0;
   double q1 = 0, q2 = 0;
-  for (int p = p0 + lane; p < p1; p += G) {
+  for (int p = lane; p < n; p += G) {
     double c1, c2;
-    fit_project(cx[p], cy[p], cs, sn, c1, c2);
+    fit_project(px[p], py[p], cs, sn, c1, c2);
     const double D1 = fmin(fabs(mx1 - c1), fabs(c1 - mn1)), D2 = fmin(fabs(mx2 - c2), fabs(c2 - mn2));
     if (D1 < D2) { const double e = D1 - m1; q1 += e * e; } else { const double e = D2 - m2; q2 += e * e; }
   }
-  q1 = group_reduce<G, 2>(q1); q2 = group_reduce<G, 2>(q2);
-  if (lane == 0) {
-    const double V1 = n1 > 0 ? -(q1 / n1) : 0.0, V2 = n2 > 0 ? -(q2 / n2) : 0.0;
-    cost[(long long)k * na + a] = V1 + V2;
+  if (BLOCK) { q1 = fit_block_reduce(q1, 2, sh); q2 = fit_block_reduce(q2, 2, sh); }
+  else { q1 = fit_warp_reduce(q1, 2); q2 = fit_warp_reduce(q2, 2); }
+  const double V1 = n1 > 0 ? -(q1 / n1) : 0.0, V2 = n2 > 0 ? -(q2 / n2) : 0.0;
+  return V1 + V2;
+}
+
+#define FIT_SLICES 8        /* CTAs per cluster: each takes every 8th angle */
+__global__ void __launch_bounds__(256) k_fit_cost2(const double* __restrict__ cx, const double* __restrict__ cy,
+                                                   const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
+                                                   int na, double* __restrict__ cost) {
+  extern __shared__ __align__(128) unsigned char fit_smem[];
+  double* sx = reinterpret_cast<double*>(fit_smem);                    // [FIT_STAGE]
+  double* sy = sx + FIT_STAGE;                                         // [FIT_STAGE]
+  double* sh = sy + FIT_STAGE;                                         // [8]
+  unsigned long long* mbar = reinterpret_cast<unsigned long long*>(sh + 8);
+  const int k = blockIdx.x, sl = blockIdx.y;
+  const int p0 = coff[k], n = coff[k + 1] - p0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double *px = cx + p0, *py = cy + p0;
+  if (n <= FIT_STAGE - 2 && n > 64) {
+    // the bulk copy needs 16-byte alignment: start at the even element at or below p0
+    const int a0 = p0 & ~1, skew = p0 - a0;
+    const uint32_t bytes = (uint32_t)(((n + skew + 1) & ~1) * 8);
+    if (threadIdx.x == 0) {
+      dfu_mbar_init(mbar, 1);
+      dfu_mbar_arrive_expect_tx(mbar, 2u * bytes);
+      dfu_bulk_g2s(sx, cx + a0, bytes, mbar);
+      dfu_bulk_g2s(sy, cy + a0, bytes, mbar);
+    }
+    __syncthreads();
+    dfu_mbar_wait(mbar, 0);
+    px = sx + skew; py = sy + skew;
   }
+  if (n <= FIT_WARP_MAX) {
+    for (int a = sl + FIT_SLICES * warp; a < na; a += FIT_SLICES * 8) {
+      const double c = fit_angle_cost<false>(px, py, n, angles[2 * a], angles[2 * a + 1], lane, nullptr, nullptr);
+      if (lane == 0) cost[(long long)k * na + a] = c;
+    }
+  } else {
+    for (int a = sl; a < na; a += FIT_SLICES) {
+      const double c = fit_angle_cost<true>(px, py, n, angles[2 * a], angles[2 * a + 1], threadIdx.x, sh, nullptr);
+      if (threadIdx.x == 0) cost[(long long)k * na + a] = c;
+    }
   }
 }
 
-// big[0] = number of clusters with more than FIT_BIG points, big[1..] = their ids (any order)
-__global__ void __launch_bounds__(256) k_fit_big_list(const int32_t* __restrict__ coff, int K, int32_t* __restrict__ big) {
-  const int k = blockIdx.x * 256 + threadIdx.x;
-  if (k < K && coff[k + 1] - coff[k] > FIT_BIG) big[1 + atomicAdd(big, 1)] = k;
-}
-
-// one group per cluster: first maximum (rectangle_fitting.py:135-136), runner-up, rectangle at the best angle (:138-157)
-template <int G>
-__global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ cx, const double* __restrict__ cy,
-                                                    const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
-                                                    int na, const double* __restrict__ cost, double* __restrict__ rect,
-                                                    const int32_t* __restrict__ big) {
-  const int lane = threadIdx.x % G;
-  const int nunits = G == 32 ? K : big[0];
-  for (int w = G == 32 ? (int)(((long long)blockIdx.x * 256 + threadIdx.x) / 32) : blockIdx.x; w < nunits;
-       w += G == 32 ? nunits : gridDim.x) {
-  const int k = G == 32 ? w : big[1 + w];
-  const int p0 = coff[k], p1 = coff[k + 1];
-  if (G == 32 && p1 - p0 > FIT_BIG) return;
-  // every warp of the group scans the (<= 96) costs redundantly: identical result in each, no cross-warp exchange
-  const int wl = threadIdx.x & 31;
+// one CTA per cluster: first maximum (rectangle_fitting.py:135-136), runner-up, rectangle at the best angle (:138-157);
+// every warp scans the costs redundantly (identical result in each)
+__global__ void __launch_bounds__(256) k_fit_finish2(const double* __restrict__ cx, const double* __restrict__ cy,
+                                                     const int32_t* __restrict__ coff, int K, const double* __restrict__ angles,
+                                                     int na, const double* __restrict__ cost, double* __restrict__ rect) {
+  __shared__ double sh[8];
+  const int k = blockIdx.x;
+  const int p0 = coff[k], n = coff[k + 1] - p0;
+  const int lane = threadIdx.x & 31;
+  const double *px = cx + p0, *py = cy + p0;
+  const double* scost = cost + (long long)k * na;
   double best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int a = wl; a < na; a += 32) {
-    const double c = cost[(long long)k * na + a];
-    if (c > best) { best = c; bi = a; }      // ascending a per lane: keeps the first maximum of the lane
+  for (int a = lane; a < na; a += 32) {
+    const double c = scost[a];
+    if (c > best) { best = c; bi = a; }        // ascending a per lane: keeps the first maximum of the lane
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -352,25 +420,24 @@ __global__ void __launch_bounds__(256) k_fit_finish(const double* __restrict__ c
     if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
   }
   double run = -INFINITY;
-  for (int a = wl; a < na; a += 32)
-    if (a != bi) run = fmax(run, cost[(long long)k * na + a]);
+  for (int a = lane; a < na; a += 32)
+    if (a != bi) run = fmax(run, scost[a]);
   run = warp_max(run);
   if (bi == 0x7fffffff) bi = 0;               // all costs NaN: the reference keeps theta = None; flagged by best = -inf
   const double cs = angles[2 * bi], sn = angles[2 * bi + 1];
   double mn1 = INFINITY, mx1 = -INFINITY, mn2 = INFINITY, mx2 = -INFINITY;
-  for (int p = p0 + lane; p < p1; p += G) {
+  for (int p = threadIdx.x; p < n; p += 256) {
     double c1, c2;
-    fit_project(cx[p], cy[p], cs, sn, c1, c2);
+    fit_project(px[p], py[p], cs, sn, c1, c2);
     mn1 = fmin(mn1, c1); mx1 = fmax(mx1, c1); mn2 = fmin(mn2, c2); mx2 = fmax(mx2, c2);
   }
-  mn1 = group_reduce<G, 0>(mn1); mx1 = group_reduce<G, 1>(mx1); mn2 = group_reduce<G, 0>(mn2); mx2 = group_reduce<G, 1>(mx2);
-  if (lane == 0) {
+  mn1 = fit_block_reduce(mn1, 0, sh); mx1 = fit_block_reduce(mx1, 1, sh); mn2 = fit_block_reduce(mn2, 0, sh); mx2 = fit_block_reduce(mx2, 1, sh);
+  if (threadIdx.x == 0) {
     double* r = rect + (long long)k * 16;
     r[0] = cs; r[1] = -sn; r[2] = cs; r[3] = -sn;
     r[4] = sn; r[5] = cs; r[6] = sn; r[7] = cs;
     r[8] = mn1; r[9] = mn2; r[10] = mx1; r[11] = mx2;
-    r[12] = atan2(sn, cs); r[13] = best; r[14] = run; r[15] = (double)(p1 - p0);
-  }
+    r[12] = atan2(sn, cs); r[13] = best; r[14] = run; r[15] = (double)n;
   }
 }
 
@@ -385,7 +452,6 @@ int dfu_fit_clusters(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, con
   DFU_SLOT(ctx, cx, double*, sb + 3, n * 8);
   DFU_SLOT(ctx, cy, double*, sb + 4, n * 8);
   DFU_SLOT(ctx, coff, int32_t*, sb + 5, ((size_t)K + 1) * 4);
-  DFU_SLOT(ctx, cost, double*, sb + 6, (size_t)K * na * 8);
   const unsigned nb = (unsigned)((n + 255) / 256);
   k_fit_iota<<<nb, 256, 0, st>>>(idx, n);
   DFU_LAUNCH_CHECK(ctx);
@@ -398,18 +464,12 @@ int dfu_fit_clusters(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, con
   ctx->launches += 4;
   k_fit_gather<<<nb, 256, 0, st>>>(scop, order, x, y, n, K, cx, cy, coff);
   DFU_LAUNCH_CHECK(ctx);
-  const long long nw = (long long)K * na;
-  DFU_SLOT(ctx, big, int32_t*, sb + 7, ((size_t)K + 1) * 4);
-  DFU_CUDA(ctx, cudaMemsetAsync(big, 0, 4, st));
-  k_fit_big_list<<<(K + 255) / 256, 256, 0, st>>>(coff, K, big);
+  DFU_SLOT(ctx, cost, double*, sb + 6, (size_t)K * na * 8);
+  const size_t smem = (size_t)(2 * FIT_STAGE + 8) * 8 + 16;
+  DFU_CUDA(ctx, cudaFuncSetAttribute(k_fit_cost2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_fit_cost2<<<dim3((unsigned)K, FIT_SLICES), 256, smem, st>>>(cx, cy, coff, K, angles_dev, na, cost);
   DFU_LAUNCH_CHECK(ctx);
-  k_fit_cost<32><<<(unsigned)((nw * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, big);
-  DFU_LAUNCH_CHECK(ctx);
-  k_fit_cost<256><<<148 * 4, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, big);       // persistent over the big clusters
-  DFU_LAUNCH_CHECK(ctx);
-  k_fit_finish<32><<<(unsigned)(((long long)K * 32 + 255) / 256), 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev, big);
-  DFU_LAUNCH_CHECK(ctx);
-  k_fit_finish<256><<<148, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev, big);
+  k_fit_finish2<<<K, 256, 0, st>>>(cx, cy, coff, K, angles_dev, na, cost, rect_dev);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }

@@ -6,7 +6,7 @@
 #include <string.h>
 #include "../../include/dfu3d.h"
 
-#define DFU_NSLOTS 224
+#define DFU_NSLOTS 256
 #define DFU_PROF_POOL 8192
 #ifndef DFU_PROF_NTAGS
 #define DFU_PROF_NTAGS 24
@@ -82,6 +82,13 @@ enum {
   SL_OP0, SL_OP1, SL_OP2, SL_OP3, SL_OP4, SL_OP5, SL_OP6, SL_OP7, SL_OP8, SL_OP9, SL_OP10, SL_OP11, SL_VOXCELL, SL_WARPSTAT, SL_AMBQ
 };
 static_assert(SL_AMBQ < 44, "SL_* ids must stay below the operator slot ranges");
+// Scratch slot ranges of the files (one table, so that no two users share an id):
+//   0..43   SL_* (this header)                      44..93  OPS_A / OPS_B / OPS_C (dfu_ops.cuh: grid, clustering, fit)
+//   100..131 IS_* (dfu_instances.cu)                140..152 SA_* (dfu_standalone.cu)     160..166 GA_* (dfu_instances.cu)
+//   170..189 SO_* (dfu_sor.cu)                      200..208 CV_*, 214..216 CS_* (dfu_consumer.cu)   210..212 GT_* (dfu_gtdb.cu)
+//   224..233 EV_* (dfu_evolve.cu)
+#define DFU_SLOTS_OPS_FIRST 44
+#define DFU_SLOTS_OPS_END 100
 
 int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...);
 void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes);      // NULL on failure (error recorded)

@@ -16,8 +16,8 @@
 #include <cub/cub.cuh>
 #include "dfu_common.cuh"
 
-enum { EV_A = 60, EV_B, EV_KEY, EV_IDX, EV_SKEY, EV_SIDX, EV_TMP, EV_CNT, EV_MASK, EV_KEEP };
-static_assert(EV_KEEP < 100, "slot ids");
+enum { EV_A = 224, EV_B, EV_KEY, EV_IDX, EV_SKEY, EV_SIDX, EV_TMP, EV_CNT, EV_MASK, EV_KEEP };
+static_assert(EV_A >= 224 && EV_KEEP < DFU_NSLOTS, "EV_* ids: own range 224..233 (see dfu_common.cuh)");
 
 #define EV_EPS 1e-8f                   // iou3d_cpu.cpp:38
 #define EV_MAXPTS 24                   // the reference reserves 16 (iou3d_cpu.cpp:170) and can overrun it; 16 edge pairs + 8 corners

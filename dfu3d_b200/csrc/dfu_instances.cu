@@ -15,7 +15,7 @@
 #define OPS_A 44                         // grid operators: GRID_SLOTS + 1 slots
 #define OPS_B (OPS_A + GRID_SLOTS + 1)   // clustering: CLUSTER_SLOTS slots
 #define OPS_C (OPS_B + CLUSTER_SLOTS)    // fit: FIT_SLOTS slots
-static_assert(OPS_C + FIT_SLOTS <= DFU_NSLOTS, "scratch slot table too small");
+static_assert(OPS_A == DFU_SLOTS_OPS_FIRST && OPS_C + FIT_SLOTS <= DFU_SLOTS_OPS_END, "operator slot ranges must stay inside 44..99");
 
 struct InstTables {
   const dfu_view* views;
@@ -321,6 +321,7 @@ extern "C" int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[0], co.ncluster, 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[1], dfu_grid_err_ptr(ctx, GA_CLUSTER), 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  if (hk[1] & 2) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "dfu_generate_anns_sync: R0 <= 0, Rd < 0 or R0 + Rd*|p| > sqrt(2)*R0 for some point (the cell neighbourhood of the clustering would miss pairs)");
   if (hk[1]) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_generate_anns_sync: a coordinate is NaN or the set spans more than 65533 cells");
   const int K = hk[0];
   *n_boxes_host = K;
@@ -512,6 +513,7 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   DFU_CUDA(ctx, cudaMemcpyAsync(rb + 1, dfu_grid_err_ptr(ctx, OPS_B), 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
   const int K = *(int32_t*)rb;
+  if (*(int32_t*)(rb + 1) & 2) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "cluster: R0 <= 0, Rd < 0 or R0 + Rd*|p| > sqrt(2)*R0 for some point (the cell neighbourhood of the clustering would miss pairs)");
   if (*(int32_t*)(rb + 1) != 0) return dfu_set_err(ctx, DFU_ERR_DATA, "cluster grid: a coordinate is NaN or spans more than 65533 cells");
   *n_boxes_host = K;
   if (K == 0) return DFU_OK;

@@ -25,11 +25,12 @@ struct DfuGrid {
   int32_t* pcell;                // [n] cell ordinal of the sorted point
   unsigned long long* ukey;      // [ncell] unique keys
   int32_t* ustart;               // [ncell+1] first sorted position of each cell
+  int32_t* segcell;              // [nseg+1] first cell of each segment (cells of a segment are contiguous)
   int32_t* ncell;                // device scalar
   int32_t* errflag;              // device scalar: != 0 if a coordinate overflowed 16 bits
 };
 
-#define GRID_SLOTS 14   /* + 1 (cell edges) used by the operators: reserve GRID_SLOTS + 1 */
+#define GRID_SLOTS 15   /* + 1 (cell edges) used by the operators: reserve GRID_SLOTS + 1 */
 // slot_base .. slot_base+GRID_SLOTS-1 are used.  z may be NULL (2-D grid).  active may be NULL (all active).
 int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* x, const double* y, const double* z,
                    const int32_t* seg, const uint8_t* active, int64_t n, int nseg, const double* cell_dev, DfuGrid* g);

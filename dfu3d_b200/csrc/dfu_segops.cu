@@ -88,7 +88,8 @@ __global__ void __launch_bounds__(G_THREADS) k_grid_heads(const unsigned long lo
 // pcell (inclusive scan of head) -> cell ordinal; scatter the cell table
 __global__ void __launch_bounds__(G_THREADS) k_grid_cells(const unsigned long long* __restrict__ skey, int64_t n,
                                                           int32_t* __restrict__ pcell, unsigned long long* __restrict__ ukey,
-                                                          int32_t* __restrict__ ustart, int32_t* __restrict__ ncell) {
+                                                          int32_t* __restrict__ ustart, int32_t* __restrict__ ncell,
+                                                          int32_t* __restrict__ segcell, int nseg) {
   const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (t >= n) return;
   const int c = pcell[t] - 1;
@@ -96,10 +97,18 @@ __global__ void __launch_bounds__(G_THREADS) k_grid_cells(const unsigned long lo
   if (t == 0 || skey[t] != skey[t - 1]) {
     ukey[c] = skey[t];
     ustart[c] = (int32_t)t;
+    // first cell of every segment that starts here (inactive points carry segment 0xffff and sort last)
+    int s1 = (int)(skey[t] >> 48);
+    if (s1 > nseg) s1 = nseg;
+    const int s0 = t == 0 ? -1 : (int)(skey[t - 1] >> 48);
+    for (int s = s0 + 1; s <= s1; s++) segcell[s] = c;
   }
   if (t == n - 1) {
     ustart[c + 1] = (int32_t)n;
     *ncell = c + 1;
+    int s1 = (int)(skey[t] >> 48);
+    if (s1 > nseg) s1 = nseg;
+    for (int s = s1 + 1; s <= nseg; s++) segcell[s] = c + 1;
   }
 }
 
@@ -120,11 +129,14 @@ int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const
   DFU_SLOT(ctx, ukey, unsigned long long*, sb + 9, m * 8);
   DFU_SLOT(ctx, ustart, int32_t*, sb + 10, (m + 1) * 4);
   DFU_SLOT(ctx, scal, int32_t*, sb + 11, 64);
+  DFU_SLOT(ctx, segcell, int32_t*, sb + 13, (size_t)(nseg + 2) * 4);
+  g->segcell = segcell;
   g->n = n; g->nseg = nseg; g->cell = cell_dev; g->segmin = segmin; g->skey = skey; g->sidx = sidx;
   g->sx = sx; g->sy = sy; g->sz = sz; g->pcell = pcell; g->ukey = ukey; g->ustart = ustart;
   g->ncell = scal; g->errflag = scal + 1;
   DFU_CUDA(ctx, cudaMemsetAsync(scal, 0, 4, st));   // ncell only; errflag (scal[1]) is reset by dfu_grid_err_reset
   DFU_CUDA(ctx, cudaMemsetAsync(ustart, 0, 8, st));
+  DFU_CUDA(ctx, cudaMemsetAsync(segcell, 0, (size_t)(nseg + 2) * 4, st));
   if (n == 0) return DFU_OK;
   DFU_CUDA(ctx, cudaMemsetAsync(segmin, 0xFF, (size_t)nseg * 3 * 8, st));
   const unsigned nb = (unsigned)((n + G_THREADS - 1) / G_THREADS);
@@ -143,7 +155,7 @@ int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tb, pcell, pcell, (int)n, st));
   ctx->launches += 2;
-  k_grid_cells<<<nb, G_THREADS, 0, st>>>(skey, n, pcell, ukey, ustart, g->ncell);
+  k_grid_cells<<<nb, G_THREADS, 0, st>>>(skey, n, pcell, ukey, ustart, g->ncell, segcell, nseg);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }
@@ -173,8 +185,11 @@ __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, do
   int count = 0;
   // all 27 cells lie in the three x-rows cx-1 .. cx+1 = ONE range of the cell table: two searches over the whole
   // table, then every column search runs inside that (much shorter) range
-  const int xr0 = grid_lb(g.ukey, 0, ncell, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
-  const int xr1 = grid_lb(g.ukey, xr0, ncell, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));   // cell coordinates never exceed 65534
+  // the cells of a segment are one range of the table: the row searches run inside it
+  const int sc0 = __ldg(g.segcell + s), sc1 = __ldg(g.segcell + s + 1);
+  (void)ncell;
+  const int xr0 = grid_lb(g.ukey, sc0, sc1, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
+  const int xr1 = grid_lb(g.ukey, xr0, sc1, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));   // cell coordinates never exceed 65534
   if (xr1 <= xr0) return false;
   // the query's own (x, y) column first: with a small nb the walk usually ends there
   for (int o = 0; o < 9; o++) {
@@ -257,8 +272,9 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_walk(DfuGrid g, const SegP
     const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
     bool kp = false;
     if (cx >= 0 && cy >= 0 && cz >= 0) {
-      const int xr0 = grid_lb(g.ukey, 0, ncell, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
-      const int xr1 = grid_lb(g.ukey, xr0, ncell, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));
+      const int sc0 = __ldg(g.segcell + s), sc1 = __ldg(g.segcell + s + 1);
+      const int xr0 = grid_lb(g.ukey, sc0, sc1, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
+      const int xr1 = grid_lb(g.ukey, xr0, sc1, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));
       int count = 0;
       for (int o = 0; o < 9 && !kp; o++) {
         const int ex = cx + o / 3 - 1, ey = cy + o % 3 - 1;

@@ -505,7 +505,8 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* 
       const int last = (int)(b - (t0 - 32)) - 1;          // last staged position
       const int jlo = off - (32 + lane) > -W ? off - (32 + lane) : -W;
       const int jhi = last - (32 + lane) < W ? last - (32 + lane) : W;
-      for (int j = jlo; j <= jhi; j++) {
+#pragma unroll 4
+      for (int j = jlo; j <= jhi; j++) {                   // unrolled: the insertions of consecutive points pipeline
         const int p = 32 + lane + j;
         const SorGroup& G = w.stage[p >> 3];
         float v = __double2float_ru(sor_d2(G.x[p & 7], G.y[p & 7], G.z[p & 7], L.px, L.py, L.pz));   // pads: +inf
@@ -648,14 +649,25 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* 
       const int nlf = fin ? nl : 0;
       double acc = 0.0;
       for (int r = 0; r < kk; r++) {
-        double bv = inf;
-        int bi = 0;
-        for (int j = 0; j < nlf; j++) {
-          const double x = w.list[j][lane];
-          if (x < bv) { bv = x; bi = j; }
+        // four independent running minima over interleaved quarters of the column (a single compare-select chain of
+        // nlf links is pure latency); ties resolve to the same VALUE whichever slot wins
+        double b0 = inf, b1 = inf, b2 = inf, b3 = inf;
+        int i0 = 0, i1 = 0, i2 = 0, i3 = 0;
+        for (int j = 0; j < nlf; j += 4) {
+          const double x0 = w.list[j][lane];
+          const double x1 = j + 1 < nlf ? w.list[j + 1][lane] : inf;
+          const double x2 = j + 2 < nlf ? w.list[j + 2][lane] : inf;
+          const double x3 = j + 3 < nlf ? w.list[j + 3][lane] : inf;
+          if (x0 < b0) { b0 = x0; i0 = j; }
+          if (x1 < b1) { b1 = x1; i1 = j + 1; }
+          if (x2 < b2) { b2 = x2; i2 = j + 2; }
+          if (x3 < b3) { b3 = x3; i3 = j + 3; }
         }
-        acc = __dadd_rn(acc, __dsqrt_rn(bv));
-        if (fin) w.list[bi][lane] = inf;
+        if (b1 < b0) { b0 = b1; i0 = i1; }
+        if (b3 < b2) { b2 = b3; i2 = i3; }
+        if (b2 < b0) { b0 = b2; i0 = i2; }
+        acc = __dadd_rn(acc, __dsqrt_rn(b0));
+        if (fin) w.list[i0][lane] = inf;
         __syncwarp();                       // keep the warp together (the lanes' columns differ in length)
       }
       if (fin) mean_out[orig] = __ddiv_rn(acc, (double)kk);

@@ -133,6 +133,7 @@ extern "C" int dfu_lshape_fit_sync(dfu_ctx* ctx, void* stream, const double* xy,
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[0], co.ncluster, 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[1], dfu_grid_err_ptr(ctx, OPS_B), 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  if (hk[1] & 2) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "dfu_lshape_fit_sync: R0 <= 0, Rd < 0 or R0 + Rd*|p| > sqrt(2)*R0 for some point (the cell neighbourhood of the clustering would miss pairs)");
   if (hk[1]) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_lshape_fit_sync: a coordinate is NaN or the set spans more than 65533 cells");
   const int K = hk[0];
   *n_clusters_host = K;

@@ -297,12 +297,54 @@ class FusionPipeline(object):
             vb._boxes2d_flat = b2
         res.box2d = b2[res.boxes[:, 1].astype(np.int64)] if res.boxes.shape[0] else np.zeros((0, 4), np.float32)
         if want_lines:
-            res.label_lines = [[] for _ in range(V)]
-            for rec, bb in zip(res.boxes, res.box2d):
-                if rec[20] != 0:       # skipped by the Car aspect rule (my_loader.py:651)
-                    continue
-                res.label_lines[int(rec[0])].append(format_label_line(self.cfg.label_names[int(rec[3])], rec, bb))
+            res.label_lines = format_label_lines(self.cfg.label_names, res.boxes, vb, b2, V)
         return res
+
+
+def _string_table(strings):
+    """NUL-separated byte table + int32 offsets (the layout dfu_format_label_lines reads)."""
+    enc = [x.encode() for x in strings]
+    off = np.zeros(max(len(enc), 1), np.int32)
+    pos = 0
+    for i, e in enumerate(enc):
+        off[i] = pos
+        pos += len(e) + 1
+    return np.frombuffer(b'\0'.join(enc) + b'\0', np.uint8).copy(), off
+
+
+def format_label_lines(names, boxes, vb, b2_flat, V):
+    """All label lines of a batch (my_loader.py:680), per view: the text of format_label_line for every record that
+    the Car aspect rule did not skip, produced by the library's host routine dfu_format_label_lines (Python spends
+    ~1 us per repr(float); a 64-frame batch has ~32 k of them).  The float32 2-D box tokens are formatted once per
+    instance and cached on the ViewBatch."""
+    lines = [[] for _ in range(V)]
+    n = int(boxes.shape[0])
+    if n == 0:
+        return lines
+    lib = _lib.load()
+    tabs = getattr(vb, '_label_tabs', None)
+    if tabs is None or tabs[4] != b2_flat.shape[0] or tabs[5] != tuple(names):
+        b2s = [' '.join(str(np.float32(x)) for x in row) for row in b2_flat]
+        nt, no = _string_table(names)
+        bt, bo = _string_table(b2s if b2s else [''])
+        tabs = (nt, no, bt, bo, b2_flat.shape[0], tuple(names))
+        vb._label_tabs = tabs
+    nt, no, bt, bo = tabs[:4]
+    boxes = np.ascontiguousarray(boxes, np.float64)
+    out = np.empty(n * 512, np.uint8)
+    per_view = np.zeros(V, np.int64)
+    nb = lib.dfu_format_label_lines(_lib.hptr(boxes), n, V, _lib.hptr(nt), _lib.hptr(no), len(names), _lib.hptr(bt),
+                                    _lib.hptr(bo), int(b2_flat.shape[0]), _lib.hptr(out), out.shape[0], _lib.hptr(per_view))
+    if nb < 0:
+        raise RuntimeError('dfu_format_label_lines failed (%d)' % nb)
+    flat = out[:nb].tobytes().decode().splitlines(True)
+    # records are sorted by view, so each view's lines are one slice
+    pos = 0
+    for v in range(V):
+        c = int(per_view[v])
+        lines[v] = flat[pos:pos + c]
+        pos += c
+    return lines
 
 
 def format_label_line(name, rec, box2d):

@@ -235,6 +235,16 @@ int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host
                            int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int n_angles,
                            double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host);
 
+/* ---- label text (host only; my_loader.py:680) --------------------------------------------------------------
+ * dfu_repr_f64: Python's str() / repr() of float64 values (shortest round-trip digits, fixed notation for
+ * 1e-4 <= |v| < 1e16), one per line.  dfu_format_label_lines: every KITTI label line of a batch of box records
+ * ("cls 0 0 alpha xmin ymin xmax ymax h w l x y z ry"), names / b2txt are NUL-separated string tables addressed by
+ * name_off [n_names] / b2_off [n_inst].  Both return the bytes written, or -(bytes needed) if cap is too small. */
+int64_t dfu_repr_f64(const double* vals_host, int64_t n, char* out_host, int64_t cap);
+int64_t dfu_format_label_lines(const double* boxes_host, int64_t n, int V, const char* names, const int32_t* name_off,
+                               int n_names, const char* b2txt, const int32_t* b2_off, int64_t n_inst, char* out_host,
+                               int64_t cap, int64_t* lines_per_view_host);
+
 /* ---- GT-database tooling (the consumer of the pseudo-boxes) ---------------------------------------------
  * points-in-rotated-boxes with the arithmetic of the reference's CPU routine
  * (pcdet/ops/roiaware_pool3d/src/roiaware_pool3d.cpp:121-168, called by

@@ -53,3 +53,35 @@ def test_product_never_imports_oracle():
             if f.endswith('.py'):
                 src = open(os.path.join(dp, f)).read()
                 assert not re.search(r'^\s*(from|import)\s+oracle', src, flags=re.M), f
+
+
+def test_host_label_text_equals_python_str_of_floats():
+    """dfu_repr_f64 / dfu_format_label_lines (host-only routines of the library): the reference writes label fields with
+    Python's str() (my_loader.py:680); str(np.float64(v)) == repr(float(v)) == the library's text, on 1e5 random values
+    over 28 decades plus the special cases, and whole lines equal pipeline.format_label_line."""
+    import numpy as np
+    from dfu3d_b200 import _lib, pipeline
+    lib = _lib.load()
+    r = np.random.default_rng(1)
+    x = np.concatenate([r.normal(size=100000) * 10.0 ** r.integers(-9, 19, 100000),
+                        [0.0, -0.0, 1e16, 1e-5, 1e-4, 123456.0, 1e15, 9999999999999998.0, np.inf, -np.inf, np.nan, 5e-324,
+                         1.7976931348623157e308, 1e22, 100.0, 0.5]])
+    out = np.empty(x.size * 48, np.uint8)
+    nb = lib.dfu_repr_f64(_lib.hptr(x), x.size, _lib.hptr(out), out.size)
+    got = out[:nb].tobytes().decode().split('\n')[:-1]
+    assert got == [repr(float(v)) for v in x]
+    assert all(str(np.float64(v)) == repr(float(v)) for v in x[:20000])
+    K = 500
+    boxes = r.normal(size=(K, 24)) * 10.0 ** r.integers(-6, 6, (K, 1))
+    boxes[:, 0] = np.sort(r.integers(0, 4, K)); boxes[:, 1] = r.integers(0, 50, K); boxes[:, 3] = r.integers(0, 10, K)
+    boxes[:, 20] = (r.random(K) < 0.1)
+    b2 = r.uniform(0, 1600, (50, 4)).astype(np.float32)
+
+    class VB(object):
+        pass
+    got = pipeline.format_label_lines(pipeline.NUSC_NAMES, boxes, VB(), b2, 4)
+    want = [[] for _ in range(4)]
+    for rec in boxes:
+        if rec[20] == 0:
+            want[int(rec[0])].append(pipeline.format_label_line(pipeline.NUSC_NAMES[int(rec[3])], rec, b2[int(rec[1])]))
+    assert got == want

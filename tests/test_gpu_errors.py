@@ -116,3 +116,25 @@ def test_widened_rows_report_bad_arguments():
     row_off = np.zeros(2, np.int64)
     rc = ctx.lib.dfu_fuse_emit_cloud(pipe.ctx.h, buf.data_ptr() + 2, 2, res.cloud.shape[0], _lib.hptr(row_off))
     assert rc != 0 and b'aligned' in ctx.lib.dfu_last_error(pipe.ctx.h)
+
+
+def test_cluster_radius_beyond_the_cell_neighbourhood_is_an_error():
+    """the cell union-find visits the 5x5 neighbourhood of cells of edge R0 / sqrt(2), exact only while
+    R0 + Rd * |p| <= sqrt(2) * R0.  A caller-supplied R0 / Rd outside that (or R0 <= 0, Rd < 0) must fail loudly instead of
+    splitting components the reference's _adoptive_range_segmentation (rectangle_fitting.py:161-191) would merge."""
+    rng = np.random.default_rng(0)
+    ox = 60.0 + rng.uniform(-2, 2, 300)
+    oy = rng.uniform(-1, 1, 300)
+    cl, rect = ops.lshape_fit(ox, oy, R0=0.2, Rd=0.001)           # 0.2 + 0.06 <= 0.283: fine
+    assert cl.shape == (300,)
+    with pytest.raises(RuntimeError, match='R0'):
+        ops.lshape_fit(ox, oy, R0=0.2, Rd=0.01)                    # 0.2 + 0.6 > 0.283
+    with pytest.raises(RuntimeError, match='R0'):
+        ops.lshape_fit(ox, oy, R0=-1.0, Rd=0.001)
+    with pytest.raises(RuntimeError, match='R0'):
+        ops.lshape_fit(ox, oy, R0=3.0, Rd=-0.5)
+    # the reference's own parameters pass at any realistic range
+    cl, rect = ops.lshape_fit(ox, oy, R0=3.0, Rd=0.001)
+    from oracle import restate
+    want = restate.cluster_adaptive(ox, oy, 3.0, 0.001)
+    assert np.array_equal(cl, np.asarray(want[0] if isinstance(want, tuple) else want).astype(cl.dtype))
