@@ -32,11 +32,14 @@ assert FUSION_DTYPE.itemsize == 104, FUSION_DTYPE.itemsize
 
 INST_DTYPE = np.dtype([
     ('cls', np.int32), ('lidar_enabled', np.int32), ('lidar_nb', np.int32), ('lidar_every_k', np.int32),
-    ('pseudo_nb', np.int32), ('pseudo_every_k', np.int32), ('car_aspect_rule', np.int32), ('pad', np.int32),
+    ('pseudo_nb', np.int32), ('pseudo_every_k', np.int32), ('car_aspect_rule', np.int32), ('anns_mode', np.int32),
     ('lidar_r', np.float64), ('pseudo_r', np.float64), ('gate_dist', np.float64),
     ('cluster_R0', np.float64), ('cluster_Rd', np.float64),
+    ('lidar_r_small', np.float64), ('lidar_n0', np.int32),
+    ('pseudo_n_hi', np.int32), ('pseudo_k_hi', np.int32), ('pseudo_n_mid', np.int32), ('pseudo_k_mid', np.int32),
+    ('pad', np.int32),
 ], align=True)
-assert INST_DTYPE.itemsize == 72, INST_DTYPE.itemsize
+assert INST_DTYPE.itemsize == 104, INST_DTYPE.itemsize
 
 PROF_NTAGS = 24
 PROF_TAGS = ['pack_masks', 'project', 'lists', 'densify_a', 'densify_b', 'densify_c', 'vox_gather', 'emit_cloud',

@@ -286,7 +286,7 @@ __device__ __forceinline__ void fit_project(double x, double y, double cs, doubl
 // points from global memory 89 x 3 times per cluster.  Clusters of up to FIT_WARP_MAX points give every warp its own angles
 // (shuffle reductions only); larger ones work on one angle at a time with all 256 threads.  Clusters that do not fit
 // the staging buffer (> FIT_STAGE points) read global memory as before.
-#define FIT_STAGE 3072      /* points staged per cluster (48 KB) */
+#define FIT_STAGE 1024      /* points staged per cluster (16 KB: 13 CTAs per SM) */
 #define FIT_WARP_MAX 512
 
 __device__ __forceinline__ double fit_block_reduce(double v, int op, double* sh) {

@@ -91,6 +91,18 @@ static_assert(SL_AMBQ < 44, "SL_* ids must stay below the operator slot ranges")
 #define DFU_SLOTS_OPS_END 100
 
 int dfu_set_err(dfu_ctx* ctx, int code, const char* fmt, ...);
+
+// Every entry point runs on the context's device whatever the calling thread's current device is (one context per
+// device in one process: torch's current device may differ), and restores the caller's device on return.
+struct dfu_dev_guard {
+  int prev;
+  bool sw;
+  explicit dfu_dev_guard(const dfu_ctx* c) : prev(-1), sw(false) {
+    if (c && cudaGetDevice(&prev) == cudaSuccess && prev != c->device) sw = cudaSetDevice(c->device) == cudaSuccess;
+  }
+  ~dfu_dev_guard() { if (sw) cudaSetDevice(prev); }
+};
+#define DFU_ON_DEVICE(ctx) dfu_dev_guard dev_guard__(ctx)
 void* dfu_slot(dfu_ctx* ctx, int id, size_t bytes);      // NULL on failure (error recorded)
 void* dfu_pinned(dfu_ctx* ctx, size_t bytes);
 

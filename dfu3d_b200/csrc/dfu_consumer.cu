@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_split_scatter(const float* __res
 
 extern "C" int dfu_split_cloud_sync(dfu_ctx* ctx, void* stream, const float* cloud, int C, int64_t n, const float* range_host,
                                     float* out_lidar, float* out_pseudo, int64_t* counts_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || C < 3 || n < 0 || !counts_host || (n > 0 && (!cloud || !out_lidar || !out_pseudo)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_split_cloud_sync: bad argument");
   counts_host[0] = counts_host[1] = 0;
@@ -164,6 +165,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_vox_scatter(const float* __restr
 extern "C" int dfu_voxelize_sync(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n,
                                  const float* voxel_size_host, const float* range_host, int max_points, int max_voxels,
                                  float* voxels, int32_t* coords, int32_t* num_points, int64_t* nvox_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || C < 3 || n < 0 || !voxel_size_host || !range_host || max_points <= 0 || max_voxels <= 0 || !voxels || !coords ||
       !num_points || !nvox_host || (n > 0 && !points))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_voxelize_sync: bad argument");

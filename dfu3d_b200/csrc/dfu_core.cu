@@ -111,6 +111,7 @@ extern "C" int64_t dfu_launch_count(const dfu_ctx* ctx) { return ctx ? ctx->laun
 
 // ---------------------------------------------------------------- per-kernel device timing
 extern "C" int dfu_profile_enable(dfu_ctx* ctx, int on) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx) return DFU_ERR_ARG;
   if (on && !ctx->prof_ev) {
     ctx->prof_ev = (cudaEvent_t*)calloc(2 * DFU_PROF_POOL, sizeof(cudaEvent_t));
@@ -122,6 +123,7 @@ extern "C" int dfu_profile_enable(dfu_ctx* ctx, int on) {
 }
 
 extern "C" int dfu_profile_read(dfu_ctx* ctx, double* ms_out, int64_t* calls_out, int n, int reset) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx) return DFU_ERR_ARG;
   if (ctx->prof_used > 0) {
     DFU_CUDA(ctx, cudaDeviceSynchronize());

@@ -525,6 +525,7 @@ __global__ void __launch_bounds__(256) k_emit_cloud(const dfu_view* __restrict__
 
 // ---------------------------------------------------------------- C ABI
 extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int allow_overflow) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !(ctx->stage & 1)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_densify_sync: no batch bound");
   const int V = ctx->V;
   cudaStream_t st = ctx->stream;
@@ -667,6 +668,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
 }
 
 extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t capacity_rows, int64_t* row_off_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || (ctx->stage & 6) != 6)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_cloud: project and densify stages must have run");
   const int V = ctx->V;
@@ -719,6 +721,7 @@ __global__ void k_soa_to_rows(const double* __restrict__ soa, double* __restrict
 
 extern "C" int dfu_fuse_emit_voxels(dfu_ctx* ctx, int32_t* repz_pix, int32_t* repy_pix, double* repz_xyz,
                                     double* repy_xyz, int64_t capacity) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !(ctx->stage & 4)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_voxels: densify stage not run");
   const int64_t n = ctx->off_vox[ctx->V];
   if (capacity < n) return dfu_set_err(ctx, DFU_ERR_CAPACITY, "voxel outputs need %lld entries", (long long)n);
@@ -804,6 +807,7 @@ __global__ void __launch_bounds__(S2_THREADS) k_bp_scatter(const dfu_view* __res
 extern "C" int dfu_backproject_sync(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host,
                                     const dfu_fusion_params* prm_host, const float* depth, int height_gate,
                                     double* out_xyz, int32_t* out_pix, int64_t capacity, int64_t* counts_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || V <= 0 || !views_host || !prm_host || !depth || !counts_host)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_backproject_sync: bad argument");
   cudaStream_t st = (cudaStream_t)stream;

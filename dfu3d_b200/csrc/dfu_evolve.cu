@@ -333,6 +333,7 @@ __global__ void __launch_bounds__(1024) k_nms_reduce(const unsigned long long* _
 // ---------------------------------------------------------------- C ABI
 extern "C" int dfu_boxes_iou_sync(dfu_ctx* ctx, void* stream, const float* boxes_a, int stride_a, int na, const float* boxes_b,
                                   int stride_b, int nb, int mode, float* out) {
+  DFU_ON_DEVICE(ctx);
   const int paired = (mode & 4) != 0;
   mode &= ~4;
   if (!ctx || na < 0 || nb < 0 || stride_a < 7 || stride_b < 7 || mode < 0 || mode > 2 || (paired && na != nb) ||
@@ -415,6 +416,7 @@ static int ev_nms(dfu_ctx* ctx, void* stream, const float* boxes, int stride, co
 extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
                             int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize, int post_maxsize,
                             int64_t* keep_out, int64_t* n_keep_host) {
+  DFU_ON_DEVICE(ctx);
   return ev_nms(ctx, stream, boxes, stride, scores, n, use_score_thresh, score_thresh, iou_thresh, pre_maxsize, post_maxsize,
                 keep_out, n_keep_host, 0);
 }
@@ -422,6 +424,7 @@ extern "C" int dfu_nms_sync(dfu_ctx* ctx, void* stream, const float* boxes, int 
 extern "C" int dfu_nms_normal_sync(dfu_ctx* ctx, void* stream, const float* boxes, int stride, const float* scores, int n,
                                    int use_score_thresh, float score_thresh, float iou_thresh, int pre_maxsize,
                                    int post_maxsize, int64_t* keep_out, int64_t* n_keep_host) {
+  DFU_ON_DEVICE(ctx);
   return ev_nms(ctx, stream, boxes, stride, scores, n, use_score_thresh, score_thresh, iou_thresh, pre_maxsize, post_maxsize,
                 keep_out, n_keep_host, 1);
 }

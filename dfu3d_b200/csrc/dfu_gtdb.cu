@@ -127,6 +127,7 @@ __global__ void k_crop_box_offsets(const int64_t* __restrict__ blkoff, int M, in
 
 extern "C" int dfu_points_in_boxes(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* boxes,
                                    int M, int32_t* out_mask) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || C < 3 || n < 0 || M < 0 || (n > 0 && M > 0 && (!points || !boxes || !out_mask)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_points_in_boxes: bad argument");
   if (n == 0 || M == 0) return DFU_OK;
@@ -140,6 +141,7 @@ extern "C" int dfu_points_in_boxes(dfu_ctx* ctx, void* stream, const float* poin
 extern "C" int dfu_crop_boxes_sync(dfu_ctx* ctx, void* stream, const float* points, int C, int64_t n, const float* boxes,
                                    int M, const double* centres64, float* out_rows, int64_t capacity,
                                    int64_t* offsets_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || C < 3 || n < 0 || M < 0 || !offsets_host || (n > 0 && M > 0 && (!points || !boxes)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_crop_boxes_sync: bad argument");
   for (int b = 0; b <= M; b++) offsets_host[b] = 0;

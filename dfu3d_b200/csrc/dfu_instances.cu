@@ -197,7 +197,7 @@ __global__ void k_inst_offsets(const int64_t* __restrict__ seg_off, const int64_
 
 // ---------------------------------------------------------------- GenerateAnns arithmetic (my_loader.py:633-684)
 struct InstDev {
-  int32_t view, cls, car_rule, pad;
+  int32_t view, cls, car_rule, anns_mode;
 };
 
 __device__ __forceinline__ void cross_point(double a0, double a1, double b0, double b1, double c0, double c1, double& x,
@@ -209,7 +209,8 @@ __device__ __forceinline__ void cross_point(double a0, double a1, double b0, dou
 }
 
 // rect [K][16] -> box [K][DFU_BOX_DOUBLES] (layout: include/dfu3d.h)
-__device__ void anns_record(const double* __restrict__ r, double zmax, const float* M43 /*nullable*/, int car_rule,
+// mode 0: my_loader.py:633-684; mode 1: my_loader0.py:811-930 (center_type 'prior_linecorner')
+__device__ void anns_record(const double* __restrict__ r, double zmax, const float* M43 /*nullable*/, int car_rule, int mode,
                             double* __restrict__ o) {
   const double *a = r, *b = r + 4, *c = r + 8;
   double X[4], Y[4];
@@ -217,19 +218,33 @@ __device__ void anns_record(const double* __restrict__ r, double zmax, const flo
   cross_point(a[1], a[2], b[1], b[2], c[1], c[2], X[1], Y[1]);
   cross_point(a[2], a[3], b[2], b[3], c[2], c[3], X[2], Y[2]);
   cross_point(a[3], a[0], b[3], b[0], c[3], c[0], X[3], Y[3]);
-  const double cx = (X[0] + X[2]) / 2, cy = (Y[0] + Y[2]) / 2;
-  const double cz = zmax / 2 - 1.5, height = zmax;
+  double cx = (X[0] + X[2]) / 2, cy = (Y[0] + Y[2]) / 2;
+  double cz = zmax / 2 - 1.5, height = zmax;
+  if (mode == 1 && height < 1.0) height = 1.56;                            // my_loader0.py:832
   const double d3x = X[0] - X[3], d3y = Y[0] - Y[3], d1x = X[0] - X[1], d1y = Y[0] - Y[1];
   const double l1 = __dsqrt_rn(__dadd_rn(__dmul_rn(d3x, d3x), __dmul_rn(d3y, d3y)));
   const double l2 = __dsqrt_rn(__dadd_rn(__dmul_rn(d1x, d1x), __dmul_rn(d1y, d1y)));
-  const bool skip = car_rule && (l1 / l2 > 5 || l2 / l1 > 5);
+  bool skip = (car_rule || mode == 1) && (l1 / l2 > 5 || l2 / l1 > 5);     // my_loader.py:651 (Car only) / my_loader0.py:835 (all)
   double length, width, rot;
+  const double rot3 = atan((Y[3] - Y[0]) / (X[3] - X[0] + 1e-8)), rot1 = atan((Y[1] - Y[0]) / (X[1] - X[0] + 1e-8));
   if (l1 >= l2) {
     length = l1; width = l2;
-    rot = atan((Y[3] - Y[0]) / (X[3] - X[0] + 1e-8));
+    rot = rot3;
   } else {
     length = l2; width = l1;
-    rot = atan((Y[1] - Y[0]) / (X[1] - X[0] + 1e-8));
+    rot = rot1;
+  }
+  if (mode == 1) {
+    // 'prior_linecorner' (my_loader0.py:848-857, :889-898): a short rectangle is taken for one end of a 3.9 m car seen
+    // end-on: heading along the OTHER side, centre pushed along it; then every box becomes 3.9 x 1.6 (:876, :916) and
+    // boxes whose centre is closer than 10 m are dropped (:918)
+    if (width < 1.5 && length < 2.0) {
+      rot = l1 >= l2 ? rot1 : rot3;
+      cx = (3.9 - length) / 2 * cos(rot) + cx;
+      cy = (3.9 - length) / 2 * sin(rot) + cy;
+    }
+    length = 3.9; width = 1.6;
+    if (sqrt(cx * cx + cy * cy) < 10.0) skip = true;
   }
   rot = -rot - 3.141592653589793 / 2;
   const double theta = atan(-cx / (cy + 1e-8));
@@ -259,7 +274,7 @@ __global__ void __launch_bounds__(128) k_anns(const double* __restrict__ rect, i
   const InstDev d = idev[g];
   double* o = boxes + (int64_t)k * DFU_BOX_DOUBLES;
   o[0] = d.view; o[1] = g; o[2] = k - cop[inst_off[g]]; o[3] = d.cls;
-  anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(zmax[g]), views[d.view].M43, d.car_rule, o);
+  anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(zmax[g]), views[d.view].M43, d.car_rule, d.anns_mode, o);
 }
 
 // ---------------------------------------------------------------- stand-alone GenerateAnns (my_loader.py:633-684)
@@ -286,7 +301,7 @@ __global__ void __launch_bounds__(128) k_anns_single(const double* __restrict__ 
   if (k >= K) return;
   double* o = boxes + (int64_t)k * DFU_BOX_DOUBLES;
   o[0] = 0; o[1] = 0; o[2] = k; o[3] = 0;
-  anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(*zmax), vw.M43, car_rule, o);
+  anns_record(rect + (int64_t)k * 16, dfu_unorder_f64(*zmax), vw.M43, car_rule & 1, car_rule >> 1, o);
 }
 
 #define GA_CLUSTER OPS_B
@@ -296,6 +311,7 @@ enum { GA_X = 160, GA_Y, GA_SEG, GA_MISC, GA_ANG, GA_RECT, GA_BOX };
 extern "C" int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host, const double* points, int64_t n,
                                       int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int na,
                                       double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !view_host || n < 0 || !angles_cs_host || na <= 0 || na > DFU_N_ANGLES_MAX || !n_boxes_host)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_generate_anns_sync: bad argument");
   *n_boxes_host = 0;
@@ -350,6 +366,7 @@ enum {
 extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, int G, const double* angles_cs_host,
                                        int na, double* boxes_out_host, int64_t capacity_boxes, int64_t* n_boxes_host,
                                        int64_t* seg_counts_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || (ctx->stage & 6) != 6)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_instances_sync: project and densify stages must have run");
   if (G != ctx->total_inst || (G > 0 && !ip) || !angles_cs_host || na <= 0 || na > DFU_N_ANGLES_MAX || !n_boxes_host)
@@ -435,10 +452,13 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
     for (int v = 0; v < V; v++)
       for (int j = 0; j < ctx->views_host[v].n_inst; j++, g++) {
         const dfu_inst_params& q = ip[g];
-        sp_h[2 * g] = SegPrm{q.lidar_r, q.lidar_nb, q.lidar_every_k, q.lidar_enabled, 0};
-        sp_h[2 * g + 1] = SegPrm{q.pseudo_r, q.pseudo_nb, q.pseudo_every_k, 1, 0};
+        sp_h[2 * g] = dfu_seg_prm(q.lidar_r, q.lidar_nb, q.lidar_every_k, q.lidar_enabled);
+        sp_h[2 * g].n0 = q.lidar_n0; sp_h[2 * g].r_small = q.lidar_r_small;
+        sp_h[2 * g + 1] = dfu_seg_prm(q.pseudo_r, q.pseudo_nb, q.pseudo_every_k, 1);
+        sp_h[2 * g + 1].n_hi = q.pseudo_n_hi; sp_h[2 * g + 1].k_hi = q.pseudo_k_hi;
+        sp_h[2 * g + 1].n_mid = q.pseudo_n_mid; sp_h[2 * g + 1].k_mid = q.pseudo_k_mid;
         g_h[g] = q.gate_dist; g_h[G + g] = q.cluster_R0; g_h[2 * G + g] = q.cluster_Rd;
-        id_h[g] = InstDev{v, q.cls, q.car_aspect_rule, 0};
+        id_h[g] = InstDev{v, q.cls, q.car_aspect_rule, q.anns_mode};
       }
   }
   memcpy(ang_h, angles_cs_host, (size_t)na * 16);

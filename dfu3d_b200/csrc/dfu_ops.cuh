@@ -9,8 +9,18 @@ struct SegPrm {
   int32_t nb;        // keep iff count > nb
   int32_t every_k;   // uniform_down_sample stride applied before the filter (1 = none)
   int32_t enabled;   // 0: the segment is emptied (quirk Q5)
-  int32_t pad;
+  // count-dependent schedules of the KITTI loaders (my_loader0.py:739-766): resolved on the device from the
+  // segment's point count n by k_seg_resolve, BEFORE anything else reads r / every_k
+  int32_t n0;        // >= 0: r = (n > n0) ? r : r_small
+  double r_small;
+  int32_t n_hi, k_hi, n_mid, k_mid;   // n_hi >= 0: every_k = n > n_hi ? k_hi : (n > n_mid ? k_mid : every_k)
 };
+static inline SegPrm dfu_seg_prm(double r, int nb, int every_k, int enabled) {
+  SegPrm p;
+  p.r = r; p.nb = nb; p.every_k = every_k; p.enabled = enabled; p.n0 = -1; p.r_small = r; p.n_hi = -1; p.k_hi = 1; p.n_mid = -1;
+  p.k_mid = 1;
+  return p;
+}
 
 // Uniform grid over the ACTIVE points of all segments.  Cell coordinates are relative to the segment's bounding-box
 // minimum, 16 bits per axis, key = seg:16 | cx:16 | cy:16 | cz:16 (cx,cy,cz offset by +1 so that -1 is representable).
@@ -64,7 +74,7 @@ __device__ __forceinline__ int dfu_cell_coord(double v, double mn, double cell) 
 
 // radius filter (Open3D remove_radius_outlier semantics) over all segments; keep [n] u8 (0 for inactive points)
 int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* x, const double* y, const double* z,
-                    const int32_t* seg, const int64_t* seg_off_dev, int64_t n, int nseg, const SegPrm* prm_dev,
+                    const int32_t* seg, const int64_t* seg_off_dev, int64_t n, int nseg, SegPrm* prm_dev,
                     uint8_t* keep);
 
 // keep[i] = exists reference point j of the same segment with sqrt(|q_i - r_j|^2) < maxdist[seg]

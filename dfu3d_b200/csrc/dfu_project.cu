@@ -231,6 +231,7 @@ extern "C" int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_vi
                                  const dfu_fusion_params* prm, const void* lidar_xyzi, const uint32_t* labelmap,
                                  float* out_uv, float* out_depth, int32_t* out_pix, uint8_t* out_flags,
                                  uint32_t* out_label) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !views_dev || !prm || !lidar_xyzi || V <= 0 || max_lidar_cnt < 0)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_project_label: bad argument");
   if (max_lidar_cnt == 0) return DFU_OK;
@@ -245,6 +246,7 @@ extern "C" int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_vi
 
 extern "C" int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, const void* masks,
                               int is_f32, int Hm, int Wm, uint32_t* labelmap) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !views_dev || !labelmap || V <= 0 || Hm <= 0 || Wm <= 0)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_pack_masks: bad argument");
   const int HW = Hm * Wm;
@@ -262,6 +264,7 @@ extern "C" int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view*
 
 extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, int max_lidar_cnt,
                                 const dfu_fusion_params* prm, const void* lidar_xyzi, double* out_depth) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !views_dev || !prm || !out_depth || V <= 0)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_sparse_depth: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
@@ -291,6 +294,7 @@ extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_vie
 // op 4 rect_to_lidar f64 [n][3] -> f64 [n][3]            (:89-102)
 // op 5 lidar_to_img  f32 [n][3] -> f32 [n][2], f32 [n]   (:125-132)
 // op 6 get_fov_flag  f32 rect [n][3], in1 = int32 {H, W} -> u8 [n]   (vis_utils.py:108-123 == my_loader.py:85-100)
+// op 7 corners3d_to_img_boxes  f64 corners [n][3] -> f64 [n][2] image x, y   (:146-164; min / max over the 8 corners on the host)
 __global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const void* __restrict__ in0,
                                                      const void* __restrict__ in1, const void* __restrict__ in2, int64_t n,
                                                      void* __restrict__ out0, void* __restrict__ out1) {
@@ -336,12 +340,22 @@ __global__ void __launch_bounds__(256) k_calib_apply(dfu_view vw, int op, const 
     const double* a = (const double*)in0 + 3 * i;
     double* o = (double*)out0 + 3 * i;
     for (int j = 0; j < 3; j++) o[j] = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.inv44, j, 4);
+  } else if (op == 7) {
+    // corners3d_to_img_boxes (:146-164): float64 corner [x y z 1] . P2^T, then x / w, y / w (divides by the HOMOGENEOUS
+    // coordinate, unlike rect_to_img)
+    const double* a = (const double*)in0 + 3 * i;
+    double* o = (double*)out0 + 2 * i;
+    const double h0 = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.P2T, 0, 3), h1 = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.P2T, 1, 3),
+                 h2 = dfu_row4_f64(a[0], a[1], a[2], 1.0, vw.P2T, 2, 3);
+    o[0] = __ddiv_rn(h0, h2);
+    o[1] = __ddiv_rn(h1, h2);
   }
 }
 
 extern "C" int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0,
                                const void* in1, const void* in2, int64_t n, void* out0, void* out1) {
-  if (!ctx || !view_host || op < 0 || op > 6 || n < 0 || (n > 0 && (!in0 || !out0)))
+  DFU_ON_DEVICE(ctx);
+  if (!ctx || !view_host || op < 0 || op > 7 || n < 0 || (n > 0 && (!in0 || !out0)))
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: bad argument");
   if (n > 0 && (op == 2 || op == 5) && !out1) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op needs out1");
   if (n > 0 && op == 6 && !in1) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_calib_apply: op 6 needs the image shape");
@@ -357,6 +371,7 @@ extern "C" int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_
 extern "C" int dfu_fuse_begin(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_host,
                               const dfu_fusion_params* prm, const void* lidar_xyzi, const float* depth,
                               const void* image, const uint32_t* labelmap) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || V <= 0 || !views_host || !prm || !lidar_xyzi || !depth)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_begin: bad argument");
   if (prm->H <= 0 || prm->W <= 0 || prm->Hm < prm->H || prm->Wm < prm->W)
@@ -398,6 +413,7 @@ extern "C" int dfu_fuse_begin(dfu_ctx* ctx, void* stream, int V, const dfu_view*
 }
 
 extern "C" int dfu_fuse_project_sync(dfu_ctx* ctx, int64_t* counts_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !(ctx->stage & 1)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_project_sync: no batch bound");
   const int V = ctx->V;
   cudaStream_t st = ctx->stream;
@@ -446,6 +462,7 @@ extern "C" int dfu_fuse_project_sync(dfu_ctx* ctx, int64_t* counts_host) {
 }
 
 extern "C" int dfu_fuse_emit_project(dfu_ctx* ctx, int32_t* out_pix, uint8_t* out_flags, uint32_t* out_label) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || !(ctx->stage & 2)) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_fuse_emit_project: project stage not run");
   const int64_t ns = ctx->total_slots;
   cudaStream_t st = ctx->stream;

@@ -301,6 +301,17 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_walk(DfuGrid g, const SegP
   }
 }
 
+// count-dependent radius / stride (my_loader0.py:739-766): one thread per segment, in place
+__global__ void __launch_bounds__(G_THREADS) k_seg_resolve(SegPrm* __restrict__ prm, const int64_t* __restrict__ seg_off, int nseg) {
+  const int s = blockIdx.x * G_THREADS + threadIdx.x;
+  if (s >= nseg) return;
+  SegPrm p = prm[s];
+  const int64_t n = seg_off[s + 1] - seg_off[s];
+  if (p.n0 >= 0 && !(n > p.n0)) p.r = p.r_small;
+  if (p.n_hi >= 0) p.every_k = n > p.n_hi ? p.k_hi : (n > p.n_mid ? p.k_mid : p.every_k);
+  prm[s] = p;
+}
+
 __global__ void __launch_bounds__(G_THREADS) k_seg_active(const int32_t* __restrict__ seg, const int64_t* __restrict__ seg_off,
                                                           int64_t n, const SegPrm* __restrict__ prm, uint8_t* __restrict__ active,
                                                           double* __restrict__ cell, int nseg) {
@@ -314,9 +325,11 @@ __global__ void __launch_bounds__(G_THREADS) k_seg_active(const int32_t* __restr
 }
 
 int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const double* y, const double* z,
-                    const int32_t* seg, const int64_t* seg_off_dev, int64_t n, int nseg, const SegPrm* prm_dev,
+                    const int32_t* seg, const int64_t* seg_off_dev, int64_t n, int nseg, SegPrm* prm_dev,
                     uint8_t* keep) {
   if (n == 0) return DFU_OK;
+  k_seg_resolve<<<(nseg + G_THREADS - 1) / G_THREADS, G_THREADS, 0, st>>>(prm_dev, seg_off_dev, nseg);
+  DFU_LAUNCH_CHECK(ctx);
   DFU_SLOT(ctx, active, uint8_t*, sb + GRID_SLOTS - 1, n);
   DFU_SLOT(ctx, cellv, double*, sb + GRID_SLOTS, (size_t)nseg * 8);
   const int64_t span = n > nseg ? n : nseg;

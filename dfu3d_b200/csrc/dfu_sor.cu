@@ -890,6 +890,7 @@ __global__ void __launch_bounds__(256) k_sor_mask(const double* __restrict__ mea
 
 extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host, int k,
                               double std_ratio, uint8_t* out_keep, double* out_mean, double* out_stats_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || nseg <= 0 || !seg_off_host || !out_keep) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_sor_filter: bad argument");
   if (k < 1 || k > SOR_KMAX) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "dfu_sor_filter: k = %d (supported: 1..%d)", k, SOR_KMAX);
   if (nseg > 65535) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_sor_filter: %d segments (max 65535)", nseg);

@@ -46,6 +46,7 @@ static int check_grid_err(dfu_ctx* ctx, cudaStream_t st, int sb, const char* wha
 extern "C" int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, int nseg, const int64_t* seg_off_host,
                                  const double* radius_host, const int32_t* nb_host, const int32_t* every_k_host,
                                  uint8_t* out_keep, int32_t* out_count) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || nseg <= 0 || !seg_off_host || !radius_host || !nb_host || !out_keep)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_radius_filter: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
@@ -60,7 +61,7 @@ extern "C" int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, 
   DFU_SLOT(ctx, seg_off, int64_t*, SA_SEGOFF, (size_t)(nseg + 1) * 8);
   DFU_SLOT(ctx, prm, SegPrm*, SA_PRM, (size_t)nseg * sizeof(SegPrm));
   std::vector<SegPrm> ph(nseg);
-  for (int s = 0; s < nseg; s++) ph[s] = SegPrm{radius_host[s], nb_host[s], every_k_host ? every_k_host[s] : 1, 1, 0};
+  for (int s = 0; s < nseg; s++) ph[s] = dfu_seg_prm(radius_host[s], nb_host[s], every_k_host ? every_k_host[s] : 1, 1);
   DFU_CUDA(ctx, cudaMemcpyAsync(seg_off, seg_off_host, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(prm, ph.data(), (size_t)nseg * sizeof(SegPrm), cudaMemcpyHostToDevice, st));
   k_rows_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(xyz, 3, n, seg_off, nseg, x, y, z, seg);
@@ -78,6 +79,7 @@ extern "C" int dfu_radius_filter(dfu_ctx* ctx, void* stream, const double* xyz, 
 
 extern "C" int dfu_nn_gate(dfu_ctx* ctx, void* stream, const double* query_xyz, int64_t nq, const double* ref_xyz, int64_t nr,
                            double max_dist, uint8_t* out_keep) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || nq < 0 || nr < 0 || !out_keep) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_nn_gate: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
   if (nq == 0) return DFU_OK;
@@ -109,6 +111,7 @@ extern "C" int dfu_nn_gate(dfu_ctx* ctx, void* stream, const double* query_xyz, 
 extern "C" int dfu_lshape_fit_sync(dfu_ctx* ctx, void* stream, const double* xy, int64_t n, double R0, double Rd,
                                    const double* angles_cs_host, int na, int32_t* out_cluster, double* rect_out_host,
                                    int64_t capacity, int64_t* n_clusters_host) {
+  DFU_ON_DEVICE(ctx);
   if (!ctx || n < 0 || !angles_cs_host || na <= 0 || na > DFU_N_ANGLES_MAX || !n_clusters_host)
     return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_lshape_fit_sync: bad argument");
   cudaStream_t st = (cudaStream_t)stream;

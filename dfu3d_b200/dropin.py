@@ -155,8 +155,14 @@ class Calibration(object):
         self._apply(4, [p], p.shape[0], [out])
         return self._ret(out, was_np)
 
-    def corners3d_to_img_boxes(self, corners3d):       # :146-164 — off the fusion path; kept for API completeness
-        raise NotImplementedError('corners3d_to_img_boxes is not on the fusion / pseudo-box path (SURVEY.md §8a)')
+    def corners3d_to_img_boxes(self, corners3d):       # :146-164 — (N, 8, 3) rect-frame corners -> boxes (N, 4), corners (N, 8, 2)
+        c, was_np = self._dev(corners3d, torch.float64, 3)
+        n = c.shape[0] // 8
+        xy = torch.empty((c.shape[0], 2), dtype=torch.float64, device=c.device)
+        self._apply(7, [c], c.shape[0], [xy])
+        xy = xy.reshape(n, 8, 2)
+        boxes = torch.cat([xy.min(1).values, xy.max(1).values], 1)       # x1, y1, x2, y2
+        return self._ret(boxes, was_np), self._ret(xy, was_np)
 
 
 # ----------------------------------------------------------------------------- S1 helpers (my_loader.py / vis_utils.py)
@@ -293,7 +299,14 @@ class LShapeFitting():
     """rectangle_fitting.py:23-191.  fitting() = adaptive-range clustering (R0 + Rd*|p|, connected components listed by
     minimum point index) + the 89-angle variance-criterion rectangle search, both in libdfu3d.so."""
 
+    class Criteria(object):               # rectangle_fitting.py:25-28
+        AREA = 1
+        CLOSENESS = 2
+        VARIANCE = 3
+
     def __init__(self):
+        self.criteria = self.Criteria.VARIANCE    # the only criterion the shipped path uses (rectangle_fitting.py:32)
+        self.min_dist_of_closeness_crit = 0.1
         self.dtheta_deg_for_serarch = 1.0
         self.R0 = 3.0
         self.Rd = 0.001
@@ -303,7 +316,10 @@ class LShapeFitting():
         ox = np.asarray(ox, np.float64).reshape(-1)
         if self.max_cluster_points is not None and ox.shape[0] > self.max_cluster_points:
             return None, None              # the reference's "break_signal == 1" outcome, by size instead of wall clock
-        cl, rect = ops.lshape_fit(ox, oy, self.R0, self.Rd)
+        if self.criteria != self.Criteria.VARIANCE:
+            raise NotImplementedError('LShapeFitting: only Criteria.VARIANCE is built (the reference ships with it, '
+                                      'rectangle_fitting.py:32); AREA / CLOSENESS would silently give other boxes')
+        cl, rect = ops.lshape_fit(ox, oy, self.R0, self.Rd, dtheta_deg=self.dtheta_deg_for_serarch)
         rects, idsets = [], []
         for k in range(rect.shape[0]):
             r = RectangleData()
@@ -319,9 +335,9 @@ def calc_cross_point(a, b, c):                         # my_loader.py:699-702 (s
     return x, y
 
 
-def calc_rect_contour(a, b, c):                        # my_loader.py:686-697
-    rect_c_x = [None] * 4
-    rect_c_y = [None] * 4
+def calc_rect_contour(a, b, c):                        # my_loader.py:686-697 (5-element lists, the last stays None)
+    rect_c_x = [None] * 5
+    rect_c_y = [None] * 5
     rect_c_x[0], rect_c_y[0] = calc_cross_point(a[0:2], b[0:2], c[0:2])
     rect_c_x[1], rect_c_y[1] = calc_cross_point(a[1:3], b[1:3], c[1:3])
     rect_c_x[2], rect_c_y[2] = calc_cross_point(a[2:4], b[2:4], c[2:4])
@@ -429,6 +445,57 @@ def depth2pointsrgbpm(depth, image, image_ori, calib, lidar, thing_classes, mask
         for line in res.label_lines[0]:
             f.write(line)
     _last_forvis = [[r[8], r[9], r[10], r[7], r[6], r[5], r[11]] for r in res.boxes if r[20] == 0]
+    torch.cuda.current_stream(dev).synchronize()
+    return res.cloud.cpu().numpy()
+
+
+# ----------------------------------------------------------------------------- earlier variants vis_utils.py:14 also imports
+def _backproject_np(depth, calib, thr):
+    """depth[depth < thr] = 0 in place (as the reference does), then the float64 back-projection of the non-zero pixels
+    in row-major order: (rows, cols, p_lidar [M, 3])."""
+    depth[depth < thr] = 0
+    H, W = depth.shape[0], depth.shape[1]
+    d = torch.from_numpy(np.ascontiguousarray(np.asarray(depth, np.float32).reshape(1, H, W)))
+    xyz, pix, _ = ops.backproject(d, [calib.as_tuple()], min_depth=float(np.nextafter(np.float32(0), np.float32(1))))
+    torch.cuda.current_stream(xyz.device).synchronize()
+    pix = pix.cpu().numpy().astype(np.int64)
+    return pix // W, pix % W, xyz.cpu().numpy()
+
+
+def depth2points(depth, calib):
+    """my_loader.py:142-150: threshold 0.1, back-projection of every remaining pixel, float64 [M, 3]."""
+    return _backproject_np(depth, calib, 0.1)[2]
+
+
+def depth2pointsrgb(depth, image, calib):
+    """my_loader.py:152-164: [x y z R G B] (colours NOT divided by 3), float64 [M, 6]."""
+    rows, cols, p = _backproject_np(depth, calib, 0.1)
+    new_p = np.zeros((p.shape[0], 6))
+    new_p[:, 0:3] = p
+    new_p[:, 3:] = np.asarray(image)[rows, cols]
+    return new_p
+
+
+def depth2pointsrgbp(depth, image, calib, lidar):
+    """my_loader.py:415-442: the fused cloud without instances: threshold 0.01, height gate, la_sampling2, LiDAR rows with
+    intensity x 10.  Same kernels as depth2pointsrgbpm minus the per-instance stage; `lidar` is used as given."""
+    pipe = pipeline.FusionPipeline(0, config=pipeline.FusionConfig(min_depth=0.01, instances=False))
+    dev = pipe.device
+    depth[depth < 0.01] = 0
+    H, W = depth.shape[0], depth.shape[1]
+    img = torch.as_tensor(np.ascontiguousarray(np.asarray(image)))
+    if img.dtype not in (torch.int32, torch.uint8):
+        img = img.to(torch.int32)
+    Hm, Wm = max(H, img.shape[0]), max(W, img.shape[1])
+    image_d = torch.zeros((1, Hm, Wm, 3), dtype=img.dtype, device=dev)
+    image_d[0, :img.shape[0], :img.shape[1]] = img.to(dev)
+    lid = _lidar4(np.asarray(lidar), _lib.default_context(0))
+    vb = pipeline.ViewBatch(
+        lidar=lid, sweeps=[(0, lid.shape[0])], view_sweep=[0], calibs=[calib.as_tuple()], planes=[None],
+        depth=torch.from_numpy(np.ascontiguousarray(np.asarray(depth, np.float32).reshape(1, H, W))).to(dev), image=image_d,
+        masks=torch.zeros((0, Hm, Wm), dtype=torch.uint8, device=dev), n_inst=[0], classes=[np.zeros(0, np.int64)],
+        boxes2d=[np.zeros((0, 4), np.float32)])
+    res = pipe.run(vb, cloud_dtype=torch.float64, instances=False, no_fov_cull=True)
     torch.cuda.current_stream(dev).synchronize()
     return res.cloud.cpu().numpy()
 

@@ -94,9 +94,14 @@ def nn_gate(query, ref, max_dist, ctx=None):
 _ANGLES = None
 
 
-def search_angles_cs():
-    """cos / sin of the 89 angles of rectangle_fitting.py:117-122 (host numpy, as the reference evaluates them)."""
+def search_angles_cs(dtheta_deg=1.0):
+    """cos / sin of the search angles of rectangle_fitting.py:117-122 (89 for the reference's 1 degree step; host numpy,
+    as the reference evaluates them)."""
     global _ANGLES
+    if dtheta_deg != 1.0:
+        dtheta = np.deg2rad(dtheta_deg)
+        th = np.arange(0.0, np.pi / 2.0 - dtheta, dtheta)
+        return np.ascontiguousarray(np.stack([np.cos(th), np.sin(th)], 1)), th
     if _ANGLES is None:
         dtheta = np.deg2rad(1.0)
         th = np.arange(0.0, np.pi / 2.0 - dtheta, dtheta)
@@ -104,7 +109,7 @@ def search_angles_cs():
     return _ANGLES
 
 
-def lshape_fit(ox, oy, R0=3.0, Rd=0.001, ctx=None):
+def lshape_fit(ox, oy, R0=3.0, Rd=0.001, ctx=None, dtheta_deg=1.0):
     """LShapeFitting.fitting arithmetic (rectangle_fitting.py:39-191): (cluster id per point numbered by minimum point
     index [n] int32 numpy, rect [K, 16] float64 numpy: a[4] b[4] c[4] theta best-cost runner-up n)."""
     ctx = ctx or _lib.default_context(0)
@@ -112,7 +117,9 @@ def lshape_fit(ox, oy, R0=3.0, Rd=0.001, ctx=None):
     n = xy.shape[0]
     if n == 0:
         return np.zeros(0, np.int32), np.zeros((0, 16))
-    ang, _ = search_angles_cs()
+    ang, _ = search_angles_cs(dtheta_deg)
+    if ang.shape[0] < 1 or ang.shape[0] > 96:
+        raise ValueError('dtheta_deg_for_serarch = %r gives %d search angles (supported: 1..96)' % (dtheta_deg, ang.shape[0]))
     xyd = torch.from_numpy(xy).to(ctx.device)
     cl = torch.zeros(n, dtype=torch.int32, device=ctx.device)
     rect = np.zeros((n, 16))

@@ -40,6 +40,7 @@ class FusionConfig:
     label_names: list = field(default_factory=lambda: list(NUSC_NAMES))
     allow_voxel_overflow: bool = False
     instances: bool = True                 # False: the per-instance / GenerateAnns stage is not run
+    legacy: bool = False                   # True: my_loader0.py schedule (:748-766) and GenerateAnns (:811-930)
 
     @staticmethod
     def preset(name):
@@ -51,11 +52,21 @@ class FusionConfig:
             return FusionConfig()
         if name == 'kitti':
             return FusionConfig(bounds=(1216, 352), plane_range=(-30.0, 80.0, -30.0, 80.0), instances=False)
+        if name == 'kitti_legacy':
+            # my_loader0.py: KITTI plane range (:470); no bounds test in the label loop (:680) -- PIL raises beyond the
+            # 1216 x 352 mask, so the crop is the bound; class-agnostic count-dependent filters; the class name is
+            # written as given (label_names = None: the batch's thing_classes)
+            return FusionConfig(bounds=(1216, 352), plane_range=(-30.0, 80.0, -30.0, 80.0), legacy=True, label_names=None)
         raise KeyError(name)
 
     def instance_schedule(self, cls_name):
         """Per-class filter schedule of my_loader.py:581-599.
         Returns dict(lidar_enabled, lidar_nb, lidar_r, pseudo_nb, pseudo_r, car_aspect_rule)."""
+        if self.legacy:
+            # my_loader0.py:748-766, every class alike: LiDAR (20, r = 2 if n > 50 else 3); pseudo points
+            # uniform_down_sample(8 if n > 500, 4 if n > 100, none) then (20, 3).  The counts are read on the device.
+            return dict(lidar_enabled=1, lidar_nb=20, lidar_r=2.0, lidar_n0=50, lidar_r_small=3.0, pseudo_nb=20, pseudo_r=3.0,
+                        pseudo_n_hi=500, pseudo_k_hi=8, pseudo_n_mid=100, pseudo_k_mid=4, car_aspect_rule=1, anns_mode=1)
         if cls_name in NUSC_VEHICLES:
             return dict(lidar_enabled=1, lidar_nb=1, lidar_r=3.0, pseudo_nb=1, pseudo_r=3.0,
                         car_aspect_rule=int(cls_name == 'Car'))
@@ -155,9 +166,9 @@ class FusionResult:
 
 
 class FusionPipeline(object):
-    def __init__(self, device=0, config=None):
+    def __init__(self, device=0, config=None, ctx=None):
         self.cfg = config or FusionConfig()
-        self.ctx = _lib.default_context(device)
+        self.ctx = ctx or _lib.default_context(device)
         self.device = self.ctx.device
         self.lib = self.ctx.lib
         self._angles, _ = search_angles_cs()
@@ -264,6 +275,13 @@ class FusionPipeline(object):
             t['pseudo_nb'] = sch['pseudo_nb']
             t['pseudo_every_k'] = sch.get('pseudo_every_k', 1)
             t['car_aspect_rule'] = sch['car_aspect_rule']
+            t['anns_mode'] = sch.get('anns_mode', 0)
+            t['lidar_n0'] = sch.get('lidar_n0', -1)
+            t['lidar_r_small'] = sch.get('lidar_r_small', sch['lidar_r'])
+            t['pseudo_n_hi'] = sch.get('pseudo_n_hi', -1)
+            t['pseudo_k_hi'] = sch.get('pseudo_k_hi', 1)
+            t['pseudo_n_mid'] = sch.get('pseudo_n_mid', -1)
+            t['pseudo_k_mid'] = sch.get('pseudo_k_mid', 1)
             t['lidar_r'] = sch['lidar_r']
             t['pseudo_r'] = sch['pseudo_r']
             t['gate_dist'] = cfg.gate_dist
@@ -297,7 +315,7 @@ class FusionPipeline(object):
             vb._boxes2d_flat = b2
         res.box2d = b2[res.boxes[:, 1].astype(np.int64)] if res.boxes.shape[0] else np.zeros((0, 4), np.float32)
         if want_lines:
-            res.label_lines = format_label_lines(self.cfg.label_names, res.boxes, vb, b2, V)
+            res.label_lines = format_label_lines(self.cfg.label_names or vb.thing_classes, res.boxes, vb, b2, V)
         return res
 
 
@@ -475,7 +493,11 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
             ev.record(s_in)
         return dst, ev
 
-    hc = st.get('cloud_host')
+    # two pinned output buffers used alternately: the result of a call stays valid until the call after the next one
+    # (a saver thread may still be writing batch i to disk while batch i + 1 is computed)
+    st['flip'] = st.get('flip', 0) ^ 1
+    hkey = 'cloud_host%d' % st['flip']
+    hc = st.get(hkey)
     results, pending = [], upload(0)
     row_base, rows_needed, d2h_ev = 0, 0, []
     for i in range(len(metas)):
@@ -498,7 +520,7 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
             new = torch.empty((est, 8), dtype=res.cloud.dtype, pin_memory=True)
             if hc is not None and row_base and hc.dtype == new.dtype:
                 new[:row_base].copy_(hc[:row_base])
-            hc = st['cloud_host'] = new
+            hc = st[hkey] = new
         with torch.cuda.stream(s_out):
             s_out.wait_event(e)
             hc[row_base:row_base + n].copy_(res.cloud, non_blocking=True)
@@ -510,28 +532,7 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
         row_base += n
     s_out.synchronize()
     main.synchronize()
-    # ---- merge the per-group results into one FusionResult (views, instances and rows renumbered batch-wide)
-    row_off = [np.zeros(1, np.int64)]
-    boxes, segc, b2d, lines = [], [], [], []
-    for (res, base), (meta, _, (v0, v1), (m0, m1)) in zip(results, metas):
-        row_off.append(res.row_off[1:] + base)
-        if res.boxes is not None and res.boxes.shape[0]:
-            bx = res.boxes.copy()
-            bx[:, 0] += v0
-            bx[:, 1] += m0
-            boxes.append(bx)
-            b2d.append(res.box2d)
-        if res.seg_counts is not None:
-            segc.append(res.seg_counts)
-        if res.label_lines is not None:
-            lines += res.label_lines
-    out = FusionResult(cloud=None, row_off=np.concatenate(row_off),
-                       counts_project=np.concatenate([r.counts_project for r, _ in results], 0),
-                       counts_densify=np.concatenate([r.counts_densify for r, _ in results], 0))
-    out.boxes = np.concatenate(boxes, 0) if boxes else np.zeros((0, _lib.BOX_DOUBLES))
-    out.box2d = np.concatenate(b2d, 0) if b2d else np.zeros((0, 4), np.float32)
-    out.seg_counts = np.concatenate(segc, 0) if segc else None
-    out.label_lines = lines if want_lines else None
+    out = _merge_results(results, metas, want_lines)
     out.cloud_host = hc[:row_base]
     out.d2h_bytes = out.cloud_host.numel() * out.cloud_host.element_size() + out.boxes.nbytes
     return out
@@ -556,5 +557,90 @@ def _batch_stats(self, vb, res):
     return st
 
 
+def _merge_results(results, metas, want_lines):
+    """Per-group FusionResults -> one (views, instances and rows renumbered batch-wide).  results: [(res, row_base)]."""
+    row_off = [np.zeros(1, np.int64)]
+    boxes, segc, b2d, lines = [], [], [], []
+    for (res, base), (meta, _, (v0, v1), (m0, m1)) in zip(results, metas):
+        row_off.append(res.row_off[1:] + base)
+        if res.boxes is not None and res.boxes.shape[0]:
+            bx = res.boxes.copy()
+            bx[:, 0] += v0
+            bx[:, 1] += m0
+            boxes.append(bx)
+            b2d.append(res.box2d)
+        if res.seg_counts is not None:
+            segc.append(res.seg_counts)
+        if res.label_lines is not None:
+            lines += res.label_lines
+    out = FusionResult(cloud=None, row_off=np.concatenate(row_off),
+                       counts_project=np.concatenate([r.counts_project for r, _ in results], 0),
+                       counts_densify=np.concatenate([r.counts_densify for r, _ in results], 0))
+    out.boxes = np.concatenate(boxes, 0) if boxes else np.zeros((0, _lib.BOX_DOUBLES))
+    out.box2d = np.concatenate(b2d, 0) if b2d else np.zeros((0, 4), np.float32)
+    out.seg_counts = np.concatenate(segc, 0) if segc else None
+    out.label_lines = lines if want_lines else None
+    return out
+
+
+class _Holder(object):
+    def __init__(self, meta):
+        self.meta = meta
+
+
+def _run_split(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=True, parts=2):
+    """`run` on a device-resident batch cut frame-wise into `parts` groups that run CONCURRENTLY, each on its own
+    stream, library context and host thread (ctypes releases the GIL inside the library): while one group's host code
+    waits for a count or sizes the next stage, the other group's kernels keep the GPU busy.  Frames share nothing, so
+    the result equals `run` on the whole batch (tests/test_gpu_instances.py::test_run_split_equals_run)."""
+    import concurrent.futures as cf
+    holder = vb.__dict__.setdefault('_split_holder', _Holder(vb))
+    metas = _chunk_metas(holder, int(os.environ.get('DFU3D_SPLIT_PARTS', parts)))
+    if len(metas) == 1:
+        return self.run(vb, cloud_dtype=cloud_dtype, instances=instances, want_lines=want_lines)
+    st = self.__dict__.setdefault('_split', {})
+    while len(st.setdefault('workers', [])) < len(metas):
+        st['workers'].append((FusionPipeline(self.device.index, config=self.cfg, ctx=_lib.Context(self.device.index)),
+                              torch.cuda.Stream(self.device)))
+    if 'pool' not in st:
+        st['pool'] = cf.ThreadPoolExecutor(max_workers=8)
+    main = torch.cuda.current_stream(self.device)
+    dev = self.device
+
+    def job(i):
+        meta, (l0, l1), (v0, v1), (m0, m1) = metas[i]
+        sub, stream = st['workers'][i]
+        torch.cuda.set_device(dev)
+        stream.wait_stream(main)
+        with torch.cuda.stream(stream):
+            meta.lidar, meta.depth, meta.image, meta.masks = vb.lidar[l0:l1], vb.depth[v0:v1], vb.image[v0:v1], vb.masks[m0:m1]
+            meta.labelmap = None
+            res = sub.run(meta, cloud_dtype=cloud_dtype, instances=instances, want_lines=want_lines)
+            stream.synchronize()
+        return res
+    futs = [st['pool'].submit(job, i) for i in range(1, len(metas))]
+    res0 = job(0)
+    parts_res = [res0] + [f.result() for f in futs]
+    results, base = [], 0
+    for r in parts_res:
+        results.append((r, base))
+        base += int(r.cloud.shape[0])
+    out = _merge_results(results, metas, want_lines and instances and self.cfg.instances)
+    if not (instances and self.cfg.instances):
+        out.boxes = None
+        out.label_lines = None
+    out.cloud = torch.cat([r.cloud for r in parts_res], 0)
+    return out
+
+
+def _total_launches(self):
+    n = self.ctx.launches
+    for sub, _ in self.__dict__.get('_split', {}).get('workers', []):
+        n += sub.ctx.launches
+    return n
+
+
+FusionPipeline.run_split = _run_split
+FusionPipeline.total_launches = _total_launches
 FusionPipeline.run_host = _run_host
 FusionPipeline.batch_stats = _batch_stats

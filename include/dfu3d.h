@@ -75,10 +75,20 @@ typedef struct dfu_inst_params {
   int32_t lidar_nb, lidar_every_k;
   int32_t pseudo_nb, pseudo_every_k;
   int32_t car_aspect_rule;   /* 1: skip boxes with aspect > 5 (my_loader.py:651) */
-  int32_t pad;
+  int32_t anns_mode;         /* 0: GenerateAnns of my_loader.py:633-684; 1: of my_loader0.py:811-930 (kitti_legacy: height
+                                floor 1.56, 'prior_linecorner' centre shift, every box forced to 3.9 x 1.6, boxes closer
+                                than 10 m skipped) */
   double  lidar_r, pseudo_r;
   double  gate_dist;         /* BallQuery C (my_loader.py:603: 0.1) */
   double  cluster_R0, cluster_Rd;   /* rectangle_fitting.py:36-37 */
+  /* count-dependent schedules (my_loader0.py:739-766), evaluated on the device from the instance's point counts:
+   * LiDAR radius = lidar_r if n > lidar_n0 else lidar_r_small (lidar_n0 < 0: always lidar_r);
+   * pseudo stride = pseudo_k_hi if n > pseudo_n_hi, pseudo_k_mid if n > pseudo_n_mid, else pseudo_every_k
+   * (pseudo_n_hi < 0: always pseudo_every_k) */
+  double  lidar_r_small;
+  int32_t lidar_n0;
+  int32_t pseudo_n_hi, pseudo_k_hi, pseudo_n_mid, pseudo_k_mid;
+  int32_t pad;
 } dfu_inst_params;
 
 int  dfu_create(dfu_ctx** out, int device);
@@ -122,7 +132,8 @@ int dfu_project_label(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_d
  *   op 3 img_to_rect    in0 int64 u[n], in1 int64 v[n], in2 float d[n] -> out0 double [n][3]
  *   op 4 rect_to_lidar  in0 double [n][3]                          -> out0 double [n][3]
  *   op 5 lidar_to_img   in0 float  [n][3]                          -> out0 float  [n][2], out1 float [n]
- *   op 6 get_fov_flag   in0 float rect [n][3], in1 int32 {H, W} (device) -> out0 uint8 [n]   (vis_utils.py:108-123) */
+ *   op 6 get_fov_flag   in0 float rect [n][3], in1 int32 {H, W} (device) -> out0 uint8 [n]   (vis_utils.py:108-123)
+ *   op 7 corners3d_to_img_boxes  in0 double corners [n][3] (rect frame) -> out0 double [n][2] image x, y (:146-164) */
 int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int op, const void* in0, const void* in1,
                     const void* in2, int64_t n, void* out0, void* out1);
 
@@ -230,7 +241,7 @@ int dfu_lshape_fit_sync(dfu_ctx* ctx, void* stream, const double* xy /*[n][2]*/,
 /* GenerateAnns (my_loader.py:633-684) on one object's fused points (float64 [n][3]): adaptive-range clustering,
  * rectangle search and the box arithmetic, one record per cluster in cluster order (fields 4..20 as in
  * dfu_fuse_instances_sync; field 20 = skipped by the Car aspect rule of :651).  view_host supplies the calibration
- * for the lidar_to_rect of :679. */
+ * for the lidar_to_rect of :679.  car_aspect_rule: bit 0 = the rule of :651, bit 1 = anns_mode 1 (my_loader0.py:811-930). */
 int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host, const double* points, int64_t n,
                            int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int n_angles,
                            double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host);

@@ -147,7 +147,7 @@ def _patched(ml, plane, tmpdir):
         ml.estimate_plane = real_est
 
 
-def run_depth2pointsrgbpm(frame, plane=None, quiet=True):
+def run_depth2pointsrgbpm(frame, plane=None, quiet=True, variant='my_loader'):
     """Runs the reference ``depth2pointsrgbpm`` (my_loader.py:502-617) on a synthetic view.
 
     ``frame``: dict with lidar [N,4] f32 (NOT yet FOV culled), P2/R0/V2C, depth [H,W] f32,
@@ -156,7 +156,7 @@ def run_depth2pointsrgbpm(frame, plane=None, quiet=True):
     the cropped image shape, then the call.  Returns dict(all_points, label_text, lidar_fov, depth).
     """
     import torch
-    ck, ml, rf = load()
+    ck, ml, rf = load(variant)
     H, W = frame['depth'].shape[:2]
     calib = make_calib(frame['P2'], frame['R0'], frame['V2C'])
     lidar = np.asarray(frame['lidar'], np.float32)
@@ -170,6 +170,7 @@ def run_depth2pointsrgbpm(frame, plane=None, quiet=True):
     classes = torch.as_tensor(np.asarray(frame['classes'], np.int64))
     scores = torch.as_tensor(np.asarray(frame['scores'], np.float32))
     boxes = fakes.FakeBoxes(frame['boxes2d'])
+    ld = None if variant == 'my_loader' else np.zeros((H, W), np.float32)      # my_loader0.py:632 prints its shape
     with tempfile.TemporaryDirectory() as tmp:
         os.makedirs(os.path.join(tmp, 'calib'))
         os.makedirs(os.path.join(tmp, 'label'))
@@ -178,10 +179,10 @@ def run_depth2pointsrgbpm(frame, plane=None, quiet=True):
             if quiet:
                 with open(os.devnull, 'w') as dn, contextlib.redirect_stdout(dn):
                     out = ml.depth2pointsrgbpm(depth, image, image1, calib, lidar, list(frame['thing_classes']),
-                                               masks, classes, scores, boxes, None, '000000')
+                                               masks, classes, scores, boxes, ld, '000000')
             else:
                 out = ml.depth2pointsrgbpm(depth, image, image1, calib, lidar, list(frame['thing_classes']),
-                                           masks, classes, scores, boxes, None, '000000')
+                                           masks, classes, scores, boxes, ld, '000000')
         with open(os.path.join(tmp, 'label', '000000.txt')) as f:
             text = f.read()
     return {'all_points': out, 'label_text': text, 'lidar_fov': lidar, 'depth': depth}

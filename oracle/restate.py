@@ -320,8 +320,10 @@ def rect_contour(a, b, c):                                                # my_l
     return xs, ys
 
 
-def generate_anns(cls_name, pts, cls_idx, box2d, calib, names=NUSC_NAMES):
-    """GenerateAnns (my_loader.py:633-684), nuScenes preset (center_type=None).  Returns a list of
+def generate_anns(cls_name, pts, cls_idx, box2d, calib, names=NUSC_NAMES, legacy=False):
+    """GenerateAnns (my_loader.py:633-684), nuScenes preset (center_type=None); ``legacy``: my_loader0.py:811-930
+    (center_type 'prior_linecorner': height floor, aspect rule for every class, centre shift of short rectangles, every
+    box 3.9 x 1.6, boxes closer than 10 m dropped, the class NAME is written as given).  Returns a list of
     records dict(alpha, box2d, h, w, l, x, y, z, ry, cluster, n, near_tie) and the label lines."""
     recs, lines = [], []
     if pts.shape[0] == 0:
@@ -339,23 +341,35 @@ def generate_anns(cls_name, pts, cls_idx, box2d, calib, names=NUSC_NAMES):
         cy = (ry_[0] + ry_[2]) / 2
         cz = zmax / 2 - 1.5
         height = zmax
+        if legacy and height < 1.0:
+            height = 1.56                                                     # my_loader0.py:832
         l1 = np.sqrt((rx[0] - rx[3]) ** 2 + (ry_[0] - ry_[3]) ** 2)
         l2 = np.sqrt((rx[0] - rx[1]) ** 2 + (ry_[0] - ry_[1]) ** 2)
         with np.errstate(all='ignore'):
-            if cls_name == 'Car' and (l1 / l2 > 5 or l2 / l1 > 5):
+            if (cls_name == 'Car' or legacy) and (l1 / l2 > 5 or l2 / l1 > 5):
                 continue
+        rot3 = np.arctan((ry_[3] - ry_[0]) / (rx[3] - rx[0] + 1e-8))
+        rot1 = np.arctan((ry_[1] - ry_[0]) / (rx[1] - rx[0] + 1e-8))
         if l1 >= l2:
             length, width = l1, l2
-            rot = np.arctan((ry_[3] - ry_[0]) / (rx[3] - rx[0] + 1e-8))
+            rot = rot3
         else:
             length, width = l2, l1
-            rot = np.arctan((ry_[1] - ry_[0]) / (rx[1] - rx[0] + 1e-8))
+            rot = rot1
+        if legacy:                                                            # my_loader0.py:848-857,889-898,876,916,918
+            if width < 1.5 and length < 2:
+                rot = rot1 if l1 >= l2 else rot3
+                cx = (3.9 - length) / 2 * np.cos(rot) + cx
+                cy = (3.9 - length) / 2 * np.sin(rot) + cy
+            length, width = 3.9, 1.6
+            if np.sqrt(cx ** 2 + cy ** 2) < 10:
+                continue
         rot = -rot - np.pi / 2
         theta = np.arctan((-cx / (cy + 1e-8)))
         alpha = rot - theta
         hom = np.hstack((np.array([[cx, cy, cz]]), np.ones((1, 1), np.float32)))
         (crx, cry, crz), = np.dot(hom, calib.M43)
-        lines.append(names[cls_idx] + ' 0 0 ' + str(alpha) + ' ' + str(x_min) + ' ' + str(y_min) + ' ' + str(x_max) +
+        lines.append((cls_name if legacy else names[cls_idx]) + ' 0 0 ' + str(alpha) + ' ' + str(x_min) + ' ' + str(y_min) + ' ' + str(x_max) +
                      ' ' + str(y_max) + ' ' + str(height) + ' ' + str(width) + ' ' + str(length) + ' ' + str(crx) +
                      ' ' + str(cry) + ' ' + str(crz) + ' ' + str(rot) + '\n')
         recs.append(dict(alpha=alpha, box2d=(x_min, y_min, x_max, y_max), h=height, w=width, l=length, x=crx, y=cry,
@@ -389,14 +403,24 @@ def ball_gate(pseudo, lidar, C=0.1):
     return keep
 
 
+def legacy_filter_params(nL, nP):
+    """my_loader0.py:748-766 ('multi-modal'): LiDAR (nb 20, r = 2 if n > 50 else 3); pseudo points
+    uniform_down_sample(8 if n > 500, 4 if n > 100) then (nb 20, r 3).  Returns ((nb, r), (every_k, nb, r))."""
+    return (20, 2.0 if nL > 50 else 3.0), (8 if nP > 500 else (4 if nP > 100 else 1), 20, 3.0)
+
+
 PRESETS = {   # SURVEY.md 8(a) "Variants": literals of my_loader.py vs my_loader_KittiPandasetWaymo.py
     'nuscenes': dict(bounds=(1600, 900), only_range=((-54, 54), (-54, 54)), instances=True),       # my_loader.py:471,526
     'kitti': dict(bounds=(1216, 352), only_range=((-30, 80), (-30, 80)), instances=False),         # ..Waymo.py:470,709; GenerateAnns call commented out (:831)
+    # my_loader0.py: no bounds test in the label loop (:680; PIL raises beyond the 1216 x 352 mask, so in-bounds inputs only),
+    # KITTI plane range (:470), count-dependent filters (:748-766), GenerateAnns of :811-930
+    'kitti_legacy': dict(bounds=(1216, 352), only_range=((-30, 80), (-30, 80)), instances=True, legacy=True),
 }
 
 
 def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes, boxes2d, plane,
-                      bounds=(1600, 900), return_debug=False, only_range=((-54, 54), (-54, 54)), instances=True):
+                      bounds=(1600, 900), return_debug=False, only_range=((-54, 54), (-54, 54)), instances=True,
+                      legacy=False):
     """Restatement of my_loader.py:502-617 (nuScenes preset).  ``lidar`` is already FOV culled
     (vis_utils.py:152-154); ``plane`` replaces the unseeded RANSAC of :511 (Q8).  Returns
     (all_points [N+M',8] float64, label lines, records, debug dict)."""
@@ -424,15 +448,21 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
         mrow = masks[i][rows, cols][low]
         P = new_p0[rep_y][mrow[rep_y] > 0][:, :3]
         L = lidar_mask[lab[i]][:, :3].astype(np.float64)
-        (l_on, l_nb, l_r), (p_nb, p_r) = instance_filter_params(cls_name)
-        L1 = L[fakes.radius_outlier_mask(L, l_nb, l_r)] if l_on else np.zeros((0, 3))
-        P1 = P[fakes.radius_outlier_mask(P, p_nb, p_r)]
+        if legacy:
+            (l_nb, l_r), (p_k, p_nb, p_r) = legacy_filter_params(L.shape[0], P.shape[0])
+            L1 = L[fakes.radius_outlier_mask(L, l_nb, l_r)]
+            Pd = P[::p_k]
+            P1 = Pd[fakes.radius_outlier_mask(Pd, p_nb, p_r)]
+        else:
+            (l_on, l_nb, l_r), (p_nb, p_r) = instance_filter_params(cls_name)
+            L1 = L[fakes.radius_outlier_mask(L, l_nb, l_r)] if l_on else np.zeros((0, 3))
+            P1 = P[fakes.radius_outlier_mask(P, p_nb, p_r)]
         if L1.shape[0] > 0 and P1.shape[0] > 0:
             P2 = P1[ball_gate(P1, L1, 0.1)]
         else:
             P2 = P1
         pts = np.concatenate([L1, P2], 0)
-        r, ln = generate_anns(cls_name, pts, int(classes[i]), boxes2d[i], calib)
+        r, ln = generate_anns(cls_name, pts, int(classes[i]), boxes2d[i], calib, legacy=legacy)
         for rec in r:
             rec['inst'] = i
         recs += r
@@ -462,3 +492,53 @@ def run_view(inp, plane=None, return_debug=False, preset='nuscenes'):
     out = depth2pointsrgbpm(depth, image, calib, lidar, inp['thing_classes'], inp['masks'], inp['classes'],
                             inp['boxes2d'], pl, return_debug=return_debug, **PRESETS[preset])
     return (fov,) + tuple(out)
+
+
+# ----------------------------------------------------------------------------- earlier variants (my_loader.py:142-164,415-442)
+def depth2points(depth, calib):
+    """my_loader.py:142-150 (threshold 0.1)."""
+    d3 = depth.reshape(depth.shape[0], depth.shape[1], 1)
+    d3[d3 < 0.1] = 0
+    uv = d3.nonzero()
+    return calib.rect_to_lidar(calib.img_to_rect(uv[1], uv[0], d3[d3 > 0]))
+
+
+def depth2pointsrgb(depth, image, calib):
+    """my_loader.py:152-164."""
+    d3 = depth.reshape(depth.shape[0], depth.shape[1], 1)
+    d3[d3 < 0.1] = 0
+    uv = d3.nonzero()
+    new_p = np.zeros((uv[0].shape[0], 6))
+    new_p[:, 0:3] = calib.rect_to_lidar(calib.img_to_rect(uv[1], uv[0], d3[d3 > 0]))
+    new_p[:, 3:] = image[uv[0], uv[1]]
+    return new_p
+
+
+def depth2pointsrgbp(depth, image, calib, lidar):
+    """my_loader.py:415-442: threshold 0.01, height gate, la_sampling2 (restated spconv voxeliser), LiDAR rows x 10."""
+    d3 = depth.reshape(depth.shape[0], depth.shape[1], 1)
+    d3[d3 < 0.01] = 0
+    uv = d3.nonzero()
+    new_p = np.zeros((uv[0].shape[0], 8))
+    new_p[:, 0:3] = calib.rect_to_lidar(calib.img_to_rect(uv[1], uv[0], d3[d3 > 0]))
+    new_p[:, 4:7] = image[uv[0], uv[1]] / 3
+    new_p = new_p[new_p[:, 2] < 1.]
+    rep_z, _, _ = angular_dedup(new_p)
+    new_p = new_p[rep_z].copy()
+    new_p[:, -1] = 1
+    lidar = np.asarray(lidar)
+    new_lidar = np.zeros((lidar.shape[0], 8))
+    new_lidar[:, 0:4] = lidar[:, 0:4]
+    new_lidar[:, 3] *= 10
+    new_lidar[:, -1] = 2
+    return np.concatenate([new_lidar, new_p], 0)
+
+
+def corners3d_to_img_boxes(P2, corners3d):
+    """calibration_kitti.py:146-164."""
+    n = corners3d.shape[0]
+    hom = np.concatenate((corners3d, np.ones((n, 8, 1))), axis=2)
+    img = np.matmul(hom, np.asarray(P2, np.float32).T)
+    x, y = img[:, :, 0] / img[:, :, 2], img[:, :, 1] / img[:, :, 2]
+    boxes = np.stack([x.min(1), y.min(1), x.max(1), y.max(1)], 1)
+    return boxes, np.stack([x, y], 2)

@@ -36,7 +36,7 @@ def test_built_for_sm100a_only(lib_built):
 
 
 def test_struct_sizes_match_header():
-    assert _lib.VIEW_DTYPE.itemsize == 248 and _lib.FUSION_DTYPE.itemsize == 104 and _lib.INST_DTYPE.itemsize == 72
+    assert _lib.VIEW_DTYPE.itemsize == 248 and _lib.FUSION_DTYPE.itemsize == 104 and _lib.INST_DTYPE.itemsize == 104
 
 
 def test_no_cpu_fallback():

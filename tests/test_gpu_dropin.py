@@ -153,3 +153,72 @@ def test_save_depth_as_points_round_trip(tmp_path):
     loader = dropin.MyLoader(root)
     rgb, d = loader[0]
     assert len(loader) == 1 and rgb.shape[:2] == d.shape[:2]
+
+
+def test_names_the_reference_callers_import_resolve():
+    """`import dfu3d_b200.dropin as my_loader` must satisfy vis_utils.py:7-14 and kitti_loader.py:15."""
+    for name in ('depth2pointsrgb', 'depth2pointsrgbp', 'depth2pointsrgbpm', 'depth2points', 'MyLoader', 'Calibration',
+                 'get_calib_from_file', 'get_fov_flag', 'load_depth_input', 'GenerateAnns', 'LShapeFitting', 'BallQuery',
+                 'estimate_plane', 'above_plane', 'calc_rect_contour', 'calc_cross_point', 'save_depth_as_points'):
+        assert callable(getattr(dropin, name)), name
+    xs, ys = dropin.calc_rect_contour([1.0, 0.0, 1.0, 0.0], [0.0, 1.0, 0.0, 1.0], [0.0, 0.0, 2.0, 3.0])
+    assert len(xs) == 5 and len(ys) == 5 and xs[4] is None and ys[4] is None      # my_loader.py:687-688
+    assert (xs[0], ys[0], xs[2], ys[2]) == (0.0, 0.0, 2.0, 3.0)
+
+
+@pytest.mark.parametrize('path', GOLDEN[:2], ids=[os.path.basename(p)[:-4] for p in GOLDEN[:2]])
+def test_earlier_variants_match_oracle(path):
+    """depth2points / depth2pointsrgb / depth2pointsrgbp (my_loader.py:142-164,415-442) through the CUDA library vs the
+    restatements that tests/test_oracle_vs_reference.py pins to the reference's own functions."""
+    inp, ref_fov, ref_all, ref_text = load_golden(path)
+    calib = _calib(inp)
+    oc = restate.Calib(inp['P2'], inp['R0'], inp['V2C'])
+    H, W = inp['depth'].shape
+    img = inp['image'][:H, :W]
+    d = lambda: np.array(inp['depth'], np.float32).reshape(H, W, 1)
+    dd = d()
+    got = dropin.depth2points(dd, calib)
+    want = restate.depth2points(d(), oc)
+    assert got.shape == want.shape and got.dtype == np.float64
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-9)
+    assert float(dd[dd > 0].min()) >= 0.1                                       # thresholded in place like the reference
+    got = dropin.depth2pointsrgb(d(), img, calib)
+    want = restate.depth2pointsrgb(d(), img, oc)
+    np.testing.assert_allclose(got[:, :3], want[:, :3], rtol=1e-5, atol=1e-9)
+    assert np.array_equal(got[:, 3:], want[:, 3:])
+    lidar = inp['lidar'][ref_fov]
+    got = dropin.depth2pointsrgbp(d(), img, calib, lidar)
+    want = restate.depth2pointsrgbp(d(), img, oc, lidar)
+    assert got.shape == want.shape
+    n = lidar.shape[0]
+    assert np.array_equal(got[:n], want[:n])
+    np.testing.assert_allclose(got[n:, :3], want[n:, :3], rtol=1e-5, atol=1e-9)
+    assert np.array_equal(got[n:, 3:], want[n:, 3:])
+
+
+def test_corners3d_to_img_boxes_matches_oracle():
+    inp, _, _, _ = load_golden(GOLDEN[0])
+    calib = _calib(inp)
+    rng = np.random.default_rng(0)
+    c3 = rng.uniform(-10, 10, size=(40, 8, 3)) + np.array([0, 0, 25.0])
+    boxes, corners = calib.corners3d_to_img_boxes(c3)
+    ob, oc = restate.corners3d_to_img_boxes(inp['P2'], c3)
+    assert boxes.shape == (40, 4) and corners.shape == (40, 8, 2)
+    np.testing.assert_allclose(corners, oc, rtol=1e-12, atol=1e-9)
+    np.testing.assert_allclose(boxes, ob, rtol=1e-12, atol=1e-9)
+
+
+def test_lshape_fitting_honours_its_attributes():
+    rng = np.random.default_rng(2)
+    ox = np.r_[rng.uniform(10, 14, 120), np.full(60, 14.0) + rng.normal(0, 0.02, 60)]
+    oy = np.r_[np.full(120, 3.0) + rng.normal(0, 0.02, 120), rng.uniform(3, 5, 60)]
+    f = dropin.LShapeFitting()
+    r1, ids1 = f.fitting(ox, oy)
+    f.dtheta_deg_for_serarch = 5.0                    # 17 angles instead of 89: the rectangle comes from the coarser table
+    r5, ids5 = f.fitting(ox, oy)
+    assert ids1 == ids5 and len(r1) == len(r5) == 1
+    th5 = np.degrees(np.arctan2(r5[0].b[0], r5[0].a[0])) % 5.0
+    assert min(th5, 5.0 - th5) < 1e-9
+    f.criteria = f.Criteria.AREA
+    with pytest.raises(NotImplementedError):
+        f.fitting(ox, oy)

@@ -53,6 +53,35 @@ def test_instances_match_oracle(seed, shape, scale):
         assert fa[:3] == fb[:3] and fa[4:8] == fb[4:8]
 
 
+@pytest.mark.parametrize('seed,scale', [(43, 0.09), (46, 0.2), (47, 0.3), (41, 0.25)])
+def test_kitti_legacy_preset_matches_oracle(seed, scale):
+    """FusionConfig.preset('kitti_legacy') = my_loader0.py: count-dependent radius (r = 2 if n > 50 else 3) and
+    uniform_down_sample stride (8 / 4 / none by count) resolved on the device, GenerateAnns with 'prior_linecorner',
+    forced 3.9 x 1.6 and the < 10 m skip -- against the restatement that tests/test_oracle_vs_reference.py pins to
+    my_loader0.py executed in place."""
+    from dfu3d_b200 import synth
+    fr = helpers.small_frame(seed, 'kitti', scale=scale)
+    vw = fr['views'][0]
+    vw['thing_classes'] = ['Car', 'Pedestrian', 'Cyclist']
+    vw['classes'] = np.asarray(vw['classes']) % 3
+    inp = synth.view_as_reference_inputs(fr, 0)
+    fov, allp, lines, recs, dbg = restate.run_view(inp, return_debug=True, preset='kitti_legacy')
+    pipe = pipeline.FusionPipeline(0, config=pipeline.FusionConfig.preset('kitti_legacy'))
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, cloud_dtype=torch.float64)
+    for i, d in enumerate(dbg['inst']):
+        got = res.seg_counts[i]
+        assert (got[0], got[1], got[2], got[3], got[4]) == (d['nL'], d['nP'], d['nL1'], d['nP1'], d['nP2']), (i, got, d)
+    ncmp = compare_boxes(res, recs)
+    got_lines = res.label_lines[0]
+    assert len(got_lines) == len(lines)
+    for a, b in zip(got_lines, lines):
+        fa, fb = a.split(), b.split()
+        assert fa[:3] == fb[:3] and fa[4:8] == fb[4:8] and fa[9:11] == ['1.6', '3.9']
+    strides = sorted(set(8 if d['nP'] > 500 else (4 if d['nP'] > 100 else 1) for d in dbg['inst']))
+    print('legacy: instances', len(dbg['inst']), 'boxes', len(recs), 'compared', ncmp, 'strides seen', strides)
+
+
 def test_batch_equals_single_views():
     """A batch of views gives, view by view, what each view gives alone (frame-wise independence)."""
     frs = [helpers.small_frame(s, 'nuscenes', scale=0.25) for s in (3, 4, 5)]
@@ -172,6 +201,30 @@ def test_run_host_pipelined_equals_resident(chunks):
         assert np.array_equal(res.seg_counts, ref.seg_counts)
         assert res.label_lines == ref.label_lines
         assert res.d2h_bytes == ref_cloud.nbytes + ref.boxes.nbytes
+    # the pinned output alternates between two buffers: the previous result survives the next call
+    a = pipe.run_host(hb, cloud_dtype=torch.float16, chunks=chunks)
+    snap = a.cloud_host.numpy().copy()
+    b = pipe.run_host(hb, cloud_dtype=torch.float16, chunks=chunks)
+    assert a.cloud_host.data_ptr() != b.cloud_host.data_ptr() and np.array_equal(a.cloud_host.numpy(), snap)
+
+
+@pytest.mark.parametrize('parts', [2, 3])
+def test_run_split_equals_run(parts):
+    """The concurrent frame-group run (own stream, context and host thread per group) returns exactly what the plain
+    run returns, call after call."""
+    frs = [helpers.small_frame(s, 'nuscenes', scale=0.25, n_cams=2) for s in (3, 4, 5, 7)]
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames(frs, pipe.device)
+    ref = pipe.run(vb, cloud_dtype=torch.float16)
+    for _ in range(3):
+        vb.labelmap = None
+        res = pipe.run_split(vb, cloud_dtype=torch.float16, parts=parts)
+        assert torch.equal(res.cloud, ref.cloud)
+        assert np.array_equal(res.row_off, ref.row_off)
+        assert np.array_equal(res.boxes, ref.boxes) and np.array_equal(res.box2d, ref.box2d)
+        assert np.array_equal(res.seg_counts, ref.seg_counts)
+        assert np.array_equal(res.counts_project, ref.counts_project) and np.array_equal(res.counts_densify, ref.counts_densify)
+        assert res.label_lines == ref.label_lines
 
 
 def test_densify_rare_paths_give_the_same_cloud(monkeypatch):

@@ -83,3 +83,48 @@ def test_plane_mask_and_sparse_depth():
     rgb_r, d_r = ml.load_depth_input(rc, img, inp['lidar'])
     rgb_o, d_o = restate.load_depth_input(oc, img, inp['lidar'])
     assert np.array_equal(rgb_r, rgb_o) and np.array_equal(d_r, d_o)
+
+
+def test_earlier_variants_and_corner_boxes():
+    """depth2points / depth2pointsrgb / depth2pointsrgbp (my_loader.py:142-164,415-442; imported by vis_utils.py:14) and
+    Calibration.corners3d_to_img_boxes (calibration_kitti.py:146-164): the restatements equal the reference's own code."""
+    inp = _view(35, 'nuscenes', 0.06)
+    _, ml, _ = ref_harness.load('my_loader')
+    rc = ref_harness.make_calib(inp['P2'], inp['R0'], inp['V2C'])
+    oc = restate.Calib(inp['P2'], inp['R0'], inp['V2C'])
+    H, W = inp['depth'].shape[:2]
+    img = inp['image'][:H, :W]
+    d = lambda: np.array(inp['depth'], np.float32).reshape(H, W, 1)
+    assert np.array_equal(ml.depth2points(d(), rc), restate.depth2points(d(), oc))
+    assert np.array_equal(ml.depth2pointsrgb(d(), img, rc), restate.depth2pointsrgb(d(), img, oc))
+    a = ml.depth2pointsrgbp(d(), img, rc, inp['lidar'])
+    b = restate.depth2pointsrgbp(d(), img, oc, inp['lidar'])
+    assert a.shape == b.shape and a.shape[0] > inp['lidar'].shape[0]
+    np.testing.assert_allclose(a, b, rtol=1e-12, atol=0)
+    rng = np.random.default_rng(0)
+    c3 = rng.uniform(-10, 10, size=(40, 8, 3)) + np.array([0, 0, 25.0])
+    rb, rcn = rc.corners3d_to_img_boxes(c3)
+    ob, ocn = restate.corners3d_to_img_boxes(inp['P2'], c3)
+    assert np.array_equal(rb, ob) and np.array_equal(rcn, ocn)
+
+
+@pytest.mark.parametrize('seed,scale,thin', [(43, 0.09, 8), (45, 0.08, 6)])
+def test_kitti_legacy_whole_view(seed, scale, thin):
+    """my_loader0.py (the older KITTI loader: count-dependent radius / stride schedule :748-766, GenerateAnns with
+    'prior_linecorner', forced 3.9 x 1.6, < 10 m skip :811-930) executed in place vs the 'kitti_legacy' restatement."""
+    inp = _view(seed, 'kitti', scale, thin=thin)
+    inp['thing_classes'] = ['Car', 'Pedestrian', 'Cyclist']
+    inp['classes'] = np.asarray(inp['classes']) % 3
+    ref = ref_harness.run_depth2pointsrgbpm(inp, plane=inp['plane'], variant='my_loader0')
+    fov, allp, lines, recs = restate.run_view(inp, preset='kitti_legacy')
+    nF = int(fov.sum())
+    assert allp.shape == ref['all_points'].shape
+    assert np.array_equal(allp[:nF], ref['all_points'][:nF])
+    np.testing.assert_allclose(allp[nF:, :3], ref['all_points'][nF:, :3], rtol=1e-5, atol=1e-9)
+    ref_lines = ref['label_text'].splitlines(True)
+    assert len(lines) == len(ref_lines), (len(lines), len(ref_lines))
+    for a, b in zip(lines, ref_lines):
+        fa, fb = a.split(), b.split()
+        assert fa[:3] == fb[:3] and fa[4:8] == fb[4:8]
+        np.testing.assert_allclose(np.array(fa[3:4] + fa[8:], float), np.array(fb[3:4] + fb[8:], float), rtol=1e-9, atol=1e-9)
+    print('legacy boxes', len(lines))
