@@ -36,11 +36,15 @@ struct DfuGrid {
   unsigned long long* ukey;      // [ncell] unique keys
   int32_t* ustart;               // [ncell+1] first sorted position of each cell
   int32_t* segcell;              // [nseg+1] first cell of each segment (cells of a segment are contiguous)
+  unsigned long long* hkey;      // [hmask+1] open-addressing hash of the cell keys (empty: ~0) -> hval = cell ordinal
+  int32_t* hval;
+  unsigned hmask;
+  int dims;                      // 2 (z == NULL: every cz is 1) or 3
   int32_t* ncell;                // device scalar
   int32_t* errflag;              // device scalar: != 0 if a coordinate overflowed 16 bits
 };
 
-#define GRID_SLOTS 15   /* + 1 (cell edges) used by the operators: reserve GRID_SLOTS + 1 */
+#define GRID_SLOTS 16   /* + 1 (cell edges) used by the operators: reserve GRID_SLOTS + 1 */
 // slot_base .. slot_base+GRID_SLOTS-1 are used.  z may be NULL (2-D grid).  active may be NULL (all active).
 int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* x, const double* y, const double* z,
                    const int32_t* seg, const uint8_t* active, int64_t n, int nseg, const double* cell_dev, DfuGrid* g);
@@ -53,6 +57,21 @@ __device__ __forceinline__ double dfu_unorder_f64(unsigned long long b) {
 __device__ __forceinline__ unsigned long long dfu_grid_key(int seg, int cx, int cy, int cz) {
   return ((unsigned long long)(unsigned)seg << 48) | ((unsigned long long)(unsigned)cx << 32) |
          ((unsigned long long)(unsigned)cy << 16) | (unsigned long long)(unsigned)cz;
+}
+
+// cell ordinal of a key, or -1: one or two probes instead of a 20-step binary search of the cell table
+__device__ __forceinline__ unsigned dfu_hash_u64(unsigned long long k) {
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+  return (unsigned)k;
+}
+__device__ __forceinline__ int dfu_grid_find(const DfuGrid& g, unsigned long long key) {
+  unsigned h = dfu_hash_u64(key) & g.hmask;
+  while (true) {
+    const unsigned long long k = __ldg(g.hkey + h);
+    if (k == key) return __ldg(g.hval + h);
+    if (k == ~0ull) return -1;
+    h = (h + 1) & g.hmask;
+  }
 }
 
 // first index in a[0..n) with a[i] >= v

@@ -89,7 +89,9 @@ __global__ void __launch_bounds__(G_THREADS) k_grid_heads(const unsigned long lo
 __global__ void __launch_bounds__(G_THREADS) k_grid_cells(const unsigned long long* __restrict__ skey, int64_t n,
                                                           int32_t* __restrict__ pcell, unsigned long long* __restrict__ ukey,
                                                           int32_t* __restrict__ ustart, int32_t* __restrict__ ncell,
-                                                          int32_t* __restrict__ segcell, int nseg) {
+                                                          int32_t* __restrict__ segcell, int nseg,
+                                                          unsigned long long* __restrict__ hkey, int32_t* __restrict__ hval,
+                                                          unsigned hmask) {
   const int64_t t = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (t >= n) return;
   const int c = pcell[t] - 1;
@@ -97,6 +99,12 @@ __global__ void __launch_bounds__(G_THREADS) k_grid_cells(const unsigned long lo
   if (t == 0 || skey[t] != skey[t - 1]) {
     ukey[c] = skey[t];
     ustart[c] = (int32_t)t;
+    const unsigned long long k = skey[t];
+    if (k != ~0ull) {                        // inactive points (key ~0 = the empty marker) own no cell
+      unsigned h = dfu_hash_u64(k) & hmask;
+      while (atomicCAS(hkey + h, ~0ull, k) != ~0ull) h = (h + 1) & hmask;      // keys are unique: never finds itself
+      hval[h] = c;
+    }
     // first cell of every segment that starts here (inactive points carry segment 0xffff and sort last)
     int s1 = (int)(skey[t] >> 48);
     if (s1 > nseg) s1 = nseg;
@@ -131,12 +139,17 @@ int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const
   DFU_SLOT(ctx, scal, int32_t*, sb + 11, 64);
   DFU_SLOT(ctx, segcell, int32_t*, sb + 13, (size_t)(nseg + 2) * 4);
   g->segcell = segcell;
+  size_t hcap = 64;
+  while (hcap < (size_t)m * 2) hcap <<= 1;
+  DFU_SLOT(ctx, htab, unsigned long long*, sb + 14, hcap * 12);
+  g->hkey = htab; g->hval = (int32_t*)(htab + hcap); g->hmask = (unsigned)(hcap - 1); g->dims = z ? 3 : 2;
   g->n = n; g->nseg = nseg; g->cell = cell_dev; g->segmin = segmin; g->skey = skey; g->sidx = sidx;
   g->sx = sx; g->sy = sy; g->sz = sz; g->pcell = pcell; g->ukey = ukey; g->ustart = ustart;
   g->ncell = scal; g->errflag = scal + 1;
   DFU_CUDA(ctx, cudaMemsetAsync(scal, 0, 4, st));   // ncell only; errflag (scal[1]) is reset by dfu_grid_err_reset
   DFU_CUDA(ctx, cudaMemsetAsync(ustart, 0, 8, st));
   DFU_CUDA(ctx, cudaMemsetAsync(segcell, 0, (size_t)(nseg + 2) * 4, st));
+  DFU_CUDA(ctx, cudaMemsetAsync(htab, 0xFF, hcap * 8, st));
   if (n == 0) return DFU_OK;
   DFU_CUDA(ctx, cudaMemsetAsync(segmin, 0xFF, (size_t)nseg * 3 * 8, st));
   const unsigned nb = (unsigned)((n + G_THREADS - 1) / G_THREADS);
@@ -155,7 +168,7 @@ int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, const
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tb, pcell, pcell, (int)n, st));
   ctx->launches += 2;
-  k_grid_cells<<<nb, G_THREADS, 0, st>>>(skey, n, pcell, ukey, ustart, g->ncell, segcell, nseg);
+  k_grid_cells<<<nb, G_THREADS, 0, st>>>(skey, n, pcell, ukey, ustart, g->ncell, segcell, nseg, g->hkey, g->hval, g->hmask);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }
@@ -177,30 +190,24 @@ __device__ __forceinline__ int grid_lb(const unsigned long long* __restrict__ a,
 template <int MODE>
 __device__ __forceinline__ bool grid_walk(const DfuGrid& g, int ncell, int s, double px, double py, double pz, double lim,
                                           int nb) {
+  (void)ncell;
   const double c = g.cell[s];
   const int cx = dfu_cell_coord(px, dfu_unorder_f64(g.segmin[3 * s + 0]), c);
   const int cy = dfu_cell_coord(py, dfu_unorder_f64(g.segmin[3 * s + 1]), c);
   const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
   if (cx < 0 || cy < 0 || cz < 0) return false;   // far outside the reference bounding box (or an empty segment)
   int count = 0;
-  // all 27 cells lie in the three x-rows cx-1 .. cx+1 = ONE range of the cell table: two searches over the whole
-  // table, then every column search runs inside that (much shorter) range
-  // the cells of a segment are one range of the table: the row searches run inside it
-  const int sc0 = __ldg(g.segcell + s), sc1 = __ldg(g.segcell + s + 1);
-  (void)ncell;
-  const int xr0 = grid_lb(g.ukey, sc0, sc1, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
-  const int xr1 = grid_lb(g.ukey, xr0, sc1, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));   // cell coordinates never exceed 65534
-  if (xr1 <= xr0) return false;
-  // the query's own (x, y) column first: with a small nb the walk usually ends there
-  for (int o = 0; o < 9; o++) {
-    const int dx = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) / 3 - 1), dy = (o == 0) ? 0 : ((o <= 4 ? o - 1 : o) % 3 - 1);
-    const int ex = cx + dx, ey = cy + dy;
-    if (ex < 1 || ey < 1) continue;
-    const int zlo = cz - 1 < 1 ? 1 : cz - 1;
-    const int c0 = grid_lb(g.ukey, xr0, xr1, dfu_grid_key(s, ex, ey, zlo));
-    const int c1 = grid_lb(g.ukey, c0, xr1, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
-    if (c1 <= c0) continue;
-    const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
+  // 27 (9 for a 2-D grid) hashed cell look-ups, the query's own cell first: with a small nb the walk usually ends there
+  const int nz = g.dims == 3 ? 3 : 1;
+  for (int o = 0; o < 9 * nz; o++) {
+    const int oo = o / nz, zz = o % nz;
+    const int dx = (oo == 0) ? 0 : ((oo <= 4 ? oo - 1 : oo) / 3 - 1), dy = (oo == 0) ? 0 : ((oo <= 4 ? oo - 1 : oo) % 3 - 1);
+    const int dz = zz == 0 ? 0 : (zz == 1 ? -1 : 1);
+    const int ex = cx + dx, ey = cy + dy, ez = cz + dz;
+    if (ex < 1 || ey < 1 || ez < 1) continue;
+    const int ci = dfu_grid_find(g, dfu_grid_key(s, ex, ey, ez));
+    if (ci < 0) continue;
+    const int lo = __ldg(g.ustart + ci), hi = __ldg(g.ustart + ci + 1);
     for (int j = lo; j < hi; j++) {
       const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
                    az = __dsub_rn(__ldg(g.sz + j), pz);
@@ -259,7 +266,7 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_walk(DfuGrid g, const SegP
                                                            uint8_t* __restrict__ keep) {
   const int lane = threadIdx.x & 31;
   const int nw = (gridDim.x * G_THREADS) >> 5;
-  const int ncell = *g.ncell, nt = *ntodo;
+  const int nt = *ntodo;
   for (int e = (blockIdx.x * G_THREADS + threadIdx.x) >> 5; e < nt; e += nw) {
     const int t = todo[e];
     const int s = (int)(g.skey[t] >> 48);
@@ -272,22 +279,26 @@ __global__ void __launch_bounds__(G_THREADS) k_radius_walk(DfuGrid g, const SegP
     const int cz = dfu_cell_coord(pz, dfu_unorder_f64(g.segmin[3 * s + 2]), c);
     bool kp = false;
     if (cx >= 0 && cy >= 0 && cz >= 0) {
-      const int sc0 = __ldg(g.segcell + s), sc1 = __ldg(g.segcell + s + 1);
-      const int xr0 = grid_lb(g.ukey, sc0, sc1, dfu_grid_key(s, cx - 1 < 1 ? 1 : cx - 1, 0, 0));
-      const int xr1 = grid_lb(g.ukey, xr0, sc1, dfu_grid_key(s, cx + 2 > 65535 ? 65535 : cx + 2, 0, 0));
+      // lane l < 27 looks up cell l of the 3x3x3 block (9 cells of a 2-D grid): one or two hash probes each, in parallel
+      const int nz = g.dims == 3 ? 3 : 1;
+      int lo = 0, hi = 0;
+      if (lane < 9 * nz) {
+        const int ex = cx + (lane / nz) / 3 - 1, ey = cy + (lane / nz) % 3 - 1, ez = cz + (nz == 3 ? lane % 3 - 1 : 0);
+        if (ex >= 1 && ey >= 1 && ez >= 1) {
+          const int ci = dfu_grid_find(g, dfu_grid_key(s, ex, ey, ez));
+          if (ci >= 0) { lo = __ldg(g.ustart + ci); hi = __ldg(g.ustart + ci + 1); }
+        }
+      }
+      unsigned have = __ballot_sync(0xffffffffu, hi > lo);
       int count = 0;
-      for (int o = 0; o < 9 && !kp; o++) {
-        const int ex = cx + o / 3 - 1, ey = cy + o % 3 - 1;
-        if (ex < 1 || ey < 1) continue;
-        const int zlo = cz - 1 < 1 ? 1 : cz - 1;
-        const int c0 = grid_lb(g.ukey, xr0, xr1, dfu_grid_key(s, ex, ey, zlo));
-        const int c1 = grid_lb(g.ukey, c0, xr1, dfu_grid_key(s, ex, ey, cz + 1) + 1ull);
-        if (c1 <= c0) continue;
-        const int lo = __ldg(g.ustart + c0), hi = __ldg(g.ustart + c1);
-        for (int j0 = lo; j0 < hi && !kp; j0 += 32) {
+      while (have && !kp) {
+        const int src = __ffs(have) - 1;
+        have &= have - 1;
+        const int clo = __shfl_sync(0xffffffffu, lo, src), chi = __shfl_sync(0xffffffffu, hi, src);
+        for (int j0 = clo; j0 < chi && !kp; j0 += 32) {
           const int j = j0 + lane;
           bool in = false;
-          if (j < hi) {
+          if (j < chi) {
             const double ax = __dsub_rn(__ldg(g.sx + j), px), ay = __dsub_rn(__ldg(g.sy + j), py),
                          az = __dsub_rn(__ldg(g.sz + j), pz);
             in = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az)) < r2;
