@@ -134,6 +134,11 @@ __device__ __forceinline__ unsigned long long dfu_order_f64(double v) {
   return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
 }
 
+__device__ __forceinline__ double dfu_unorder_f64(unsigned long long b) {
+  b = (b & 0x8000000000000000ull) ? (b & 0x7fffffffffffffffull) : ~b;
+  return __longlong_as_double((long long)b);
+}
+
 // The reference's float32 [x y z 1]·M (K = 4) as OpenBLAS evaluates it: one accumulator, k ascending,
 // FMA, first term a rounded product (measured; see oracle/restate.py:_sgemm_fma).
 __device__ __forceinline__ float dfu_row4_f32(float a0, float a1, float a2, float a3, const float* M, int j, int ld) {

@@ -49,10 +49,6 @@ struct DfuGrid {
 int dfu_grid_build(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* x, const double* y, const double* z,
                    const int32_t* seg, const uint8_t* active, int64_t n, int nseg, const double* cell_dev, DfuGrid* g);
 
-__device__ __forceinline__ double dfu_unorder_f64(unsigned long long b) {
-  b = (b & 0x8000000000000000ull) ? (b & 0x7fffffffffffffffull) : ~b;
-  return __longlong_as_double((long long)b);
-}
 
 __device__ __forceinline__ unsigned long long dfu_grid_key(int seg, int cx, int cy, int cz) {
   return ((unsigned long long)(unsigned)seg << 48) | ((unsigned long long)(unsigned)cx << 32) |

@@ -40,10 +40,19 @@
 #define SOR_KMAX 64
 #define SOR_KFAST 32        /* k_sor_tile handles k <= 32 */
 #define SOR_CHUNK 4096      /* points per partial sum of the mu / sigma reductions */
+#ifndef SOR_WARPS
 #define SOR_WARPS 2         /* warps (tiles in flight) per CTA of k_sor_tile */
+#endif
+#ifndef SOR_CG
 #define SOR_CG 32           /* groups staged per chunk (one bit of the lane's mask each) */
+#endif
+#ifndef SOR_LCAP20
+#define SOR_LCAP20 40       /* column entries per lane of the k <= 20 instantiation */
+#endif
 #define SOR_NBIN 16
+#ifndef SOR_FRONT
 #define SOR_FRONT 384       /* level-1 frontier capacity per tile */
+#endif
 #define SOR_MAXLEV 10
 #define SOR_DEFER 9.0f      /* lanes whose squared bound exceeds 9 x the tile median go to k_sor_single */
 enum { SO_SEGOFF = 170, SO_POFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_REC, SO_TMP, SO_SPI,
@@ -420,11 +429,12 @@ __device__ __forceinline__ void sor_pass(const SorTree& T, SorWarpSmem<LCAP>& w,
   float4 qlo, qhi;
   sor_search_box(L, qlo, qhi);
   int ng = 0;
-  for (int f0 = 0; f0 < nf || ng > 0; f0 += 4) {
+  const int NPS = SOR_CG >= 32 ? 4 : SOR_CG / 8;      // level-1 nodes expanded per step: at most SOR_CG groups
+  for (int f0 = 0; f0 < nf || ng > 0; f0 += NPS) {
     const int fi = f0 + (lane >> 3);
     bool hit = false;
     int g = -1;
-    if (fi < nf) {
+    if (fi < nf && (lane >> 3) < NPS) {
       g = w.front[fsel][fi] * 8 + (lane & 7);
       if (g >= gfirst && g <= glast) hit = sor_box_hits(T.lv[0][g], qlo, qhi);
     }
@@ -435,7 +445,7 @@ __device__ __forceinline__ void sor_pass(const SorTree& T, SorWarpSmem<LCAP>& w,
     if (hit && rank < room) w.grp[ng + rank] = g;
     __syncwarp();
     const int filled = nb < room ? ng + nb : SOR_CG;
-    if (filled == SOR_CG || (f0 + 4 >= nf && filled > 0)) {
+    if (filled == SOR_CG || (f0 + NPS >= nf && filled > 0)) {
       sor_consume<LCAP>(T, w, filled, phase, L, lane);
       if (hit && rank >= room) w.grp[rank - room] = g;
       ng = nb > room ? nb - room : 0;
@@ -994,12 +1004,12 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
     DFU_PROF(ctx, st, PT_SOR_KNN);
     const int grid_single = 148 * 8;
     if (k <= SOR_KFAST) {
-      int grid = 148 * 8;
+      int grid = 148 * 16;
       if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
       if (k <= 20) {
-        const size_t smem = sizeof(SorWarpSmem<40>) * SOR_WARPS;
-        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<20, 40>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_sor_tile<20, 40><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
+        const size_t smem = sizeof(SorWarpSmem<SOR_LCAP20>) * SOR_WARPS;
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<20, SOR_LCAP20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_sor_tile<20, SOR_LCAP20><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
       } else {
         const size_t smem = sizeof(SorWarpSmem<64>) * SOR_WARPS;
         DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
