@@ -368,42 +368,107 @@ int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* x, cons
   return DFU_OK;
 }
 
-__global__ void __launch_bounds__(G_THREADS) k_gate_cells(const double* __restrict__ maxdist, double* __restrict__ cell, int nseg) {
-  const int i = blockIdx.x * G_THREADS + threadIdx.x;
-  if (i < nseg) cell[i] = maxdist[i] * (1.0 + 9.313225746154785e-10);
+// ---------------------------------------------------------------- NN gate on a hashed cell list (no sort)
+// The gate's reference points (the kept LiDAR points of an instance) are sparse: a 0.1 m cell holds one to three of them.
+// So the cells are not sorted into ranges at all: every active reference point is pushed onto the singly linked list of its
+// cell (open-addressing hash keyed by segment + absolute cell coordinates, atomicExch on the list head), and a query
+// probes its 27 cells and walks their short lists.  Round 1 built a second sorted grid for this (8 radix passes over
+// every (point, instance) pair of the batch).
+__device__ __forceinline__ bool gate_cell(double v, double cell, int& c) {
+  const double f = floor(v / cell);
+  if (!(f >= -32760.0 && f <= 32760.0)) return false;      // NaN / a cloud more than 32 k cells from the origin
+  c = (int)f + 32768;
+  return true;
 }
 
-__global__ void __launch_bounds__(G_THREADS) k_gate(DfuGrid g, const double* __restrict__ qx, const double* __restrict__ qy,
+__global__ void __launch_bounds__(G_THREADS) k_gate_insert(const double* __restrict__ rx, const double* __restrict__ ry,
+                                                           const double* __restrict__ rz, const int32_t* __restrict__ rseg,
+                                                           const uint8_t* __restrict__ ractive, int64_t nr,
+                                                           const double* __restrict__ maxdist, unsigned long long* __restrict__ hkey,
+                                                           int32_t* __restrict__ head, int32_t* __restrict__ next, unsigned hmask,
+                                                           int32_t* __restrict__ errflag) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  if (i >= nr || (ractive && !ractive[i])) return;
+  const int s = rseg[i];
+  const double cell = maxdist[s] * (1.0 + 9.313225746154785e-10);
+  int cx, cy, cz;
+  if (!(cell > 0.0) || !gate_cell(rx[i], cell, cx) || !gate_cell(ry[i], cell, cy) || !gate_cell(rz[i], cell, cz)) {
+    atomicOr(errflag, 1);
+    return;
+  }
+  const unsigned long long k = dfu_grid_key(s, cx, cy, cz);
+  unsigned h = dfu_hash_u64(k) & hmask;
+  while (true) {
+    const unsigned long long prev = atomicCAS(hkey + h, ~0ull, k);
+    if (prev == ~0ull || prev == k) break;
+    h = (h + 1) & hmask;
+  }
+  next[i] = atomicExch(head + h, (int32_t)i);
+}
+
+__global__ void __launch_bounds__(G_THREADS) k_gate(const double* __restrict__ qx, const double* __restrict__ qy,
                                                     const double* __restrict__ qz, const int32_t* __restrict__ qseg, int64_t nq,
-                                                    const double* __restrict__ maxdist, uint8_t* __restrict__ keep) {
+                                                    const double* __restrict__ rx, const double* __restrict__ ry,
+                                                    const double* __restrict__ rz, const double* __restrict__ maxdist,
+                                                    const unsigned long long* __restrict__ hkey, const int32_t* __restrict__ head,
+                                                    const int32_t* __restrict__ next, unsigned hmask, uint8_t* __restrict__ keep) {
   const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (i >= nq) return;
   const int s = qseg[i];
-  // an empty reference segment has segmin = +inf-ish bits -> dfu_cell_coord fails -> false
-  if (g.segmin[3 * s] == ~0ull) { keep[i] = 0; return; }
-  keep[i] = grid_walk<1>(g, *g.ncell, s, qx[i], qy[i], qz[i], maxdist[s], 0) ? 1 : 0;
+  const double lim = maxdist[s], cell = lim * (1.0 + 9.313225746154785e-10);
+  const double px = qx[i], py = qy[i], pz = qz[i];
+  int cx, cy, cz;
+  bool kp = false;
+  if (cell > 0.0 && gate_cell(px, cell, cx) && gate_cell(py, cell, cy) && gate_cell(pz, cell, cz)) {
+    for (int o = 0; o < 27 && !kp; o++) {
+      // the query's own cell first
+      const int oo = o == 0 ? 13 : (o <= 13 ? o - 1 : o);
+      const unsigned long long k = dfu_grid_key(s, cx + oo / 9 - 1, cy + (oo / 3) % 3 - 1, cz + oo % 3 - 1);
+      unsigned h = dfu_hash_u64(k) & hmask;
+      int j = -1;
+      while (true) {
+        const unsigned long long hk = __ldg(hkey + h);
+        if (hk == k) { j = __ldg(head + h); break; }
+        if (hk == ~0ull) break;
+        h = (h + 1) & hmask;
+      }
+      for (; j >= 0 && !kp; j = __ldg(next + j)) {
+        const double ax = __dsub_rn(__ldg(rx + j), px), ay = __dsub_rn(__ldg(ry + j), py), az = __dsub_rn(__ldg(rz + j), pz);
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ax, ax), __dmul_rn(ay, ay)), __dmul_rn(az, az));
+        kp = __dsqrt_rn(d2) < lim;       // BallQuery: sqrt of the sum of squares, strict (my_loader.py:489-494)
+      }
+    }
+  }
+  keep[i] = kp ? 1 : 0;
 }
 
 int dfu_gate_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* qx, const double* qy, const double* qz,
                   const int32_t* qseg, int64_t nq, const double* rx, const double* ry, const double* rz,
                   const int32_t* rseg, const uint8_t* ractive, int64_t nr, int nseg, const double* maxdist_dev,
                   uint8_t* keep) {
+  (void)nseg;
   if (nq == 0) return DFU_OK;
   if (nr == 0) {
     DFU_CUDA(ctx, cudaMemsetAsync(keep, 0, nq, st));
     return DFU_OK;
   }
-  DFU_SLOT(ctx, cellv, double*, sb + GRID_SLOTS, (size_t)nseg * 8);
-  k_gate_cells<<<(nseg + G_THREADS - 1) / G_THREADS, G_THREADS, 0, st>>>(maxdist_dev, cellv, nseg);
-  DFU_LAUNCH_CHECK(ctx);
-  DfuGrid g;
+  if (nr >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_DATA, "gate: too many points");
+  size_t hcap = 64;
+  while (hcap < (size_t)nr * 2) hcap <<= 1;
+  DFU_SLOT(ctx, htab, unsigned long long*, sb + 14, hcap * 12);
+  DFU_SLOT(ctx, next, int32_t*, sb + 1, (size_t)nr * 8);
+  DFU_SLOT(ctx, scal, int32_t*, sb + 11, 64);
+  int32_t* head = (int32_t*)(htab + hcap);
   {
     DFU_PROF(ctx, st, PT_GRID_BUILD);
-    int rc = dfu_grid_build(ctx, st, sb, rx, ry, rz, rseg, ractive, nr, nseg, cellv, &g);
-    if (rc) return rc;
+    DFU_CUDA(ctx, cudaMemsetAsync(htab, 0xFF, hcap * 12, st));      // keys: empty, heads: -1
+    k_gate_insert<<<(unsigned)((nr + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(rx, ry, rz, rseg, ractive, nr, maxdist_dev, htab,
+                                                                                       head, next, (unsigned)(hcap - 1), scal + 1);
+    DFU_LAUNCH_CHECK(ctx);
   }
   DFU_PROF(ctx, st, PT_GATE);
-  k_gate<<<(unsigned)((nq + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(g, qx, qy, qz, qseg, nq, maxdist_dev, keep);
+  k_gate<<<(unsigned)((nq + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(qx, qy, qz, qseg, nq, rx, ry, rz, maxdist_dev, htab, head, next,
+                                                                             (unsigned)(hcap - 1), keep);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }
