@@ -59,6 +59,7 @@ _SIGS = {
     'dfu_project_label': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
     'dfu_calib_apply': (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, C.c_int64, _P, _P]),
     'dfu_pack_masks': (C.c_int, [_P, _P, C.c_int, _P, _P, C.c_int, C.c_int, C.c_int, _P]),
+    'dfu_widen_labelmap': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P]),
     'dfu_sparse_depth': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, _P, _P]),
     'dfu_fuse_begin': (C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P, _P, _P]),
     'dfu_fuse_project_sync': (C.c_int, [_P, _P]),

@@ -262,6 +262,38 @@ extern "C" int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view*
   return DFU_OK;
 }
 
+// compact label maps (1 or 2 bytes per pixel, bit j = instance j) -> the uint32 label words the kernels read;
+// 16 pixels per thread, 128-bit loads and stores
+template <typename T>
+__global__ void __launch_bounds__(256) k_widen_labelmap(const T* __restrict__ src, int64_t n, uint32_t* __restrict__ dst) {
+  const int64_t i0 = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 16;
+  if (i0 + 16 <= n && ((((uintptr_t)src + i0 * sizeof(T)) | (uintptr_t)(dst + i0)) & 15) == 0) {
+    T v[16];
+    const uint4* s4 = reinterpret_cast<const uint4*>(src + i0);
+    uint4* vv = reinterpret_cast<uint4*>(v);
+#pragma unroll
+    for (int j = 0; j < (int)sizeof(T); j++) vv[j] = __ldg(s4 + j);
+    uint4* d4 = reinterpret_cast<uint4*>(dst + i0);
+#pragma unroll
+    for (int j = 0; j < 4; j++) d4[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  } else {
+    for (int64_t i = i0; i < i0 + 16 && i < n; i++) dst[i] = (uint32_t)src[i];
+  }
+}
+
+extern "C" int dfu_widen_labelmap(dfu_ctx* ctx, void* stream, const void* src, int bytes_per_pixel, int64_t n, uint32_t* labelmap) {
+  DFU_ON_DEVICE(ctx);
+  if (!ctx || n < 0 || (n > 0 && (!src || !labelmap)) || (bytes_per_pixel != 1 && bytes_per_pixel != 2))
+    return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_widen_labelmap: bad argument (bytes_per_pixel must be 1 or 2)");
+  if (n == 0) return DFU_OK;
+  DFU_PROF(ctx, (cudaStream_t)stream, PT_PACK_MASKS);
+  const unsigned nb = (unsigned)((n + 4095) / 4096);
+  if (bytes_per_pixel == 1) k_widen_labelmap<uint8_t><<<nb, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)src, n, labelmap);
+  else k_widen_labelmap<uint16_t><<<nb, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)src, n, labelmap);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
 extern "C" int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, int max_lidar_cnt,
                                 const dfu_fusion_params* prm, const void* lidar_xyzi, double* out_depth) {
   DFU_ON_DEVICE(ctx);

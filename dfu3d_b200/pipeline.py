@@ -410,9 +410,13 @@ class HostBatch:
     masks: torch.Tensor
     meta: ViewBatch            # everything that is not a tensor (tensor fields are None)
     h2d_bytes: int = 0
+    labelmap: torch.Tensor = None   # compact entry: bit-packed masks [V, Hm, Wm] uint8 / int16 (bit j = instance j); masks is None
 
     @staticmethod
-    def from_device(vb):
+    def from_device(vb, compact=False, pipe=None):
+        """Pinned host copies of the batch.  compact=False: the reference's layout (one uint8 plane per instance).
+        compact=True: the instance masks as ONE bit-packed word per pixel (uint8 for <= 8 instances per view, int16 for
+        <= 16) -- what a caller that already holds packed masks would pass; the per-instance planes are not uploaded."""
         def pin(t):
             h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
             h.copy_(t)
@@ -420,8 +424,19 @@ class HostBatch:
         meta = ViewBatch(lidar=None, sweeps=vb.sweeps, view_sweep=vb.view_sweep, calibs=vb.calibs, planes=vb.planes,
                          depth=None, image=None, masks=None, n_inst=vb.n_inst, classes=vb.classes, boxes2d=vb.boxes2d,
                          thing_classes=vb.thing_classes)
-        hb = HostBatch(lidar=pin(vb.lidar), depth=pin(vb.depth), image=pin(vb.image), masks=pin(vb.masks), meta=meta)
-        hb.h2d_bytes = sum(t.numel() * t.element_size() for t in (hb.lidar, hb.depth, hb.image, hb.masks))
+        if not compact:
+            hb = HostBatch(lidar=pin(vb.lidar), depth=pin(vb.depth), image=pin(vb.image), masks=pin(vb.masks), meta=meta)
+            hb.h2d_bytes = sum(t.numel() * t.element_size() for t in (hb.lidar, hb.depth, hb.image, hb.masks))
+            return hb
+        mx = max(list(vb.n_inst) + [0])
+        if mx > 16:
+            raise ValueError('compact host batch: %d instances in a view (the packed word holds 16)' % mx)
+        pipe = pipe or FusionPipeline(vb.depth.device.index or 0)
+        lm = pipe.pack_masks(vb)                                      # [V, Hm, Wm] int32 on the device
+        vb.labelmap = None
+        packed = lm.to(torch.uint8) if mx <= 8 else lm.to(torch.int16)
+        hb = HostBatch(lidar=pin(vb.lidar), depth=pin(vb.depth), image=pin(vb.image), masks=None, meta=meta, labelmap=pin(packed))
+        hb.h2d_bytes = sum(t.numel() * t.element_size() for t in (hb.lidar, hb.depth, hb.image, hb.labelmap))
         return hb
 
 
@@ -485,8 +500,8 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
         with torch.cuda.stream(s_in):
             if i - 2 in done:
                 s_in.wait_event(done[i - 2])          # the staging buffers of this parity are free again
-            srcs = (hb.lidar[l0:l1], hb.depth[v0:v1], hb.image[v0:v1], hb.masks[m0:m1])
-            dst = [dbuf(n, par, h) for n, h in zip(('lidar', 'depth', 'image', 'masks'), srcs)]
+            srcs = (hb.lidar[l0:l1], hb.depth[v0:v1], hb.image[v0:v1], hb.masks[m0:m1] if hb.labelmap is None else hb.labelmap[v0:v1])
+            dst = [dbuf(n, par, h) for n, h in zip(('lidar', 'depth', 'image', 'masks' if hb.labelmap is None else 'packed'), srcs)]
             for d, h in zip(dst, srcs):
                 d.copy_(h, non_blocking=True)
             ev = torch.cuda.Event()
@@ -505,8 +520,17 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
         pending = upload(i + 1) if i + 1 < len(metas) else None
         meta = metas[i][0]
         main.wait_event(ev)
-        meta.lidar, meta.depth, meta.image, meta.masks = dst
         meta.labelmap = None
+        if hb.labelmap is None:
+            meta.lidar, meta.depth, meta.image, meta.masks = dst
+        else:
+            # compact entry: widen the packed words to the uint32 label map on the device (no per-instance planes at all)
+            meta.lidar, meta.depth, meta.image, packed = dst
+            meta.masks = packed[:0]
+            lm = torch.empty(packed.shape, dtype=torch.int32, device=dev)
+            self.ctx.check(self.lib.dfu_widen_labelmap(self.ctx.h, self.ctx.stream, _lib.dptr(packed), packed.element_size(),
+                                                       packed.numel(), _lib.dptr(lm)))
+            meta.labelmap = lm
         res = self.run(meta, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
         e = torch.cuda.Event()
         e.record(main)

@@ -142,6 +142,12 @@ int dfu_calib_apply(dfu_ctx* ctx, void* stream, const dfu_view* view_host, int o
 int dfu_pack_masks(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, const void* masks, int is_f32,
                    int Hm, int Wm, uint32_t* labelmap);
 
+/* Compact alternative to dfu_pack_masks for callers that already hold BIT-PACKED instance masks (bit j of a pixel's word =
+ * instance j of the view): src uint8 (<= 8 instances per view) or uint16 (<= 16) [V][Hm][Wm] -> labelmap uint32.  The
+ * reference layout is one full plane per instance (vis_utils.py:218, my_loader.py:522-530); packed words are what travels
+ * over PCIe in the compact end-to-end entry (pipeline.HostBatch.from_device(compact=True)). */
+int dfu_widen_labelmap(dfu_ctx* ctx, void* stream, const void* src, int bytes_per_pixel, int64_t n, uint32_t* labelmap);
+
 /* load_depth_input (my_loader.py:102-122): FOV cull, truncating pixel index, last-writer-wins
  * scatter of the rect depth into out_depth [V][H][W] (float64, zero elsewhere). */
 int dfu_sparse_depth(dfu_ctx* ctx, void* stream, int V, const dfu_view* views_dev, int max_lidar_cnt,

@@ -201,6 +201,12 @@ def test_run_host_pipelined_equals_resident(chunks):
         assert np.array_equal(res.seg_counts, ref.seg_counts)
         assert res.label_lines == ref.label_lines
         assert res.d2h_bytes == ref_cloud.nbytes + ref.boxes.nbytes
+    # compact entry: bit-packed masks (one byte per pixel) instead of one plane per instance -- same result, fewer bytes
+    hc = pipeline.HostBatch.from_device(vb, compact=True, pipe=pipe)
+    assert hc.masks is None and hc.labelmap.dtype == torch.uint8 and hc.h2d_bytes < hb.h2d_bytes
+    res = pipe.run_host(hc, cloud_dtype=torch.float16, chunks=chunks)
+    assert np.array_equal(res.cloud_host.numpy(), ref_cloud) and np.array_equal(res.boxes, ref.boxes)
+    assert res.label_lines == ref.label_lines
     # the pinned output alternates between two buffers: the previous result survives the next call
     a = pipe.run_host(hb, cloud_dtype=torch.float16, chunks=chunks)
     snap = a.cloud_host.numpy().copy()
