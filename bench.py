@@ -287,6 +287,7 @@ def main():
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
+    json_fd = None
     torch.cuda.set_device(local)
     numa = bind_to_gpu_numa(local) if world > 1 else None
     dev = torch.device('cuda', local)
@@ -296,18 +297,14 @@ def main():
         if 'DFU_NCCL_DEBUG' in os.environ:
             os.environ['NCCL_DEBUG'] = os.environ['DFU_NCCL_DEBUG']
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-        # NCCL writes its banner to fd 1 when the communicator is created (first collective): keep it off stdout
+        # NCCL logs to fd 1 (banner at communicator creation, INFO lines at every collective and at destroy when
+        # NCCL_DEBUG is set): fd 1 is pointed at stderr for the whole run and the ONE JSON line goes to the saved descriptor
         sys.stdout.flush()
-        saved = os.dup(1)
+        json_fd = os.dup(1)
         os.dup2(2, 1)
-        try:
-            dist.init_process_group('nccl', device_id=dev)
-            dist.barrier()
-            torch.cuda.synchronize()
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved, 1)
-            os.close(saved)
+        dist.init_process_group('nccl', device_id=dev)
+        dist.barrier()
+        torch.cuda.synchronize()
     pipe = pipeline.FusionPipeline(local)
 
     # ---- synthetic batch, generated on the device (identical generator for the CPU arm)
@@ -469,7 +466,10 @@ def main():
                 'dtype': 'f64', 'data': 'synthetic', 'config': workload_config(a), 'e2e': e2e,
                 'gpu_launches': int(launches), 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
                 'kernels': kernels, 'batch': st, 'filters': filt, 'numa_node_rank0': numa}
-        print(json.dumps(line))
+        if json_fd is None:
+            print(json.dumps(line))
+        else:
+            os.write(json_fd, (json.dumps(line) + '\n').encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -290,7 +290,8 @@ __global__ void __launch_bounds__(256) k_densify_amb(const dfu_view* __restrict_
 __global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, int bpv, S2Prm q, const float* __restrict__ depth,
                                                           const unsigned* __restrict__ key, VoxCell* __restrict__ table,
                                                           unsigned* __restrict__ blkbits,
-                                                          unsigned long long* __restrict__ stats) {
+                                                          unsigned long long* __restrict__ stats, uint2* __restrict__ ovf,
+                                                          unsigned ovf_cap, unsigned long long* __restrict__ ovf_cnt) {
   const S2View& vw = c_view[blockIdx.y];
   const int v = v0 + blockIdx.y;
   const int npix = q.H * q.W;
@@ -317,10 +318,80 @@ __global__ void __launch_bounds__(S2_THREADS) k_densify_b(int v0, int bpv, S2Prm
       if (dfu_order_f64(Z) == mm.x) atomicMin(&c->argz, (unsigned)pix);
       if (dfu_order_f64(Y) == mm.y) atomicMin(&c->argy, (unsigned)pix);
       opener = (fc.x == (unsigned)pix);
-      if (opener && (fc.y + 1u > (unsigned)q.max_per_voxel)) atomicAdd(stats + v * 8 + 3, 1ull);   // error path, rare
+      if (opener && (fc.y + 1u > (unsigned)q.max_per_voxel)) {
+        // more points than the voxeliser keeps (my_loader.py:73): listed for k_vox_overflow, which redoes the two
+        // arg-mins over the FIRST max_per_voxel points in input order
+        atomicAdd(stats + v * 8 + 3, 1ull);
+        const unsigned long long slot = atomicAdd(ovf_cnt, 1ull);
+        if (slot < ovf_cap) ovf[slot] = make_uint2((unsigned)v, k);
+      }
     }
     const unsigned bal = __ballot_sync(0xffffffffu, opener);
     if ((threadIdx.x & 31) == 0) blkbits[((size_t)v * bpv + blk) * (S2_THREADS / 32) + (threadIdx.x >> 5)] = bal;
+  }
+}
+
+// Voxels with more than max_per_voxel points (rare: surfaces seen edge-on from the LiDAR origin but face-on from the
+// camera).  The reference's voxeliser keeps the first max_per_voxel points of a voxel in INPUT order and la_sampling2 / 20
+// take the arg-min over those only (my_loader.py:69-83,253-257,268-272).  Input order = pixel order, so: one CTA per listed
+// voxel scans the view's keys forward from the voxel's opening pixel, collects its first max_per_voxel pixels in
+// order, back-projects them exactly and replaces the cell's two arg-mins (first minimum in that order).
+#define S2_OVF_MAX 256
+__global__ void __launch_bounds__(256) k_vox_overflow(const dfu_view* __restrict__ views, S2Prm q, const float* __restrict__ depth,
+                                                      const unsigned* __restrict__ key, VoxCell* __restrict__ table,
+                                                      const uint2* __restrict__ ovf, unsigned ovf_cap,
+                                                      const unsigned long long* __restrict__ ovf_cnt) {
+  __shared__ unsigned s_pix[S2_OVF_MAX];
+  __shared__ unsigned long long s_val[2][S2_OVF_MAX];
+  __shared__ int s_wsum[8], s_found;
+  const int npix = q.H * q.W;
+  const unsigned long long total = *ovf_cnt;
+  const unsigned n = total < ovf_cap ? (unsigned)total : ovf_cap;
+  const int keep = q.max_per_voxel < S2_OVF_MAX ? q.max_per_voxel : S2_OVF_MAX;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (unsigned e = blockIdx.x; e < n; e += gridDim.x) {
+    const int v = (int)ovf[e].x;
+    const unsigned k = ovf[e].y;
+    VoxCell* c = table + (size_t)v * NCELL + k;
+    const unsigned* kv = key + (size_t)v * npix;
+    __syncthreads();
+    if (threadIdx.x == 0) s_found = 0;
+    __syncthreads();
+    for (int p0 = (int)c->first; p0 < npix; p0 += 256) {
+      const int pix = p0 + threadIdx.x;
+      const bool m = pix < npix && __ldg(kv + pix) == k;
+      const unsigned bal = __ballot_sync(0xffffffffu, m);
+      if (lane == 0) s_wsum[warp] = __popc(bal);
+      __syncthreads();
+      int base = s_found, tot = 0;
+      for (int w = 0; w < 8; w++) { if (w < warp) base += s_wsum[w]; tot += s_wsum[w]; }
+      const int pos = base + __popc(bal & ((1u << lane) - 1u));
+      if (m && pos < keep) s_pix[pos] = (unsigned)pix;
+      __syncthreads();
+      if (threadIdx.x == 0) s_found += tot;
+      __syncthreads();
+      if (s_found >= keep) break;
+    }
+    const int nf = s_found < keep ? s_found : keep;
+    // exact back-projection of the kept pixels; first minimum in input order = smallest (value, position)
+    if ((int)threadIdx.x < S2_OVF_MAX) {
+      unsigned long long vz = ~0ull, vy = ~0ull;
+      if ((int)threadIdx.x < nf) {
+        const int pix = (int)s_pix[threadIdx.x], row = pix / q.W, col = pix - row * q.W;
+        double X, Y, Z;
+        dfu_backproject(views[v], col, row, __ldg(depth + (size_t)v * npix + pix), X, Y, Z);
+        vz = dfu_order_f64(Z); vy = dfu_order_f64(Y);
+      }
+      s_val[0][threadIdx.x] = vz; s_val[1][threadIdx.x] = vy;
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      const unsigned long long* a = s_val[threadIdx.x];
+      int best = 0;
+      for (int i = 1; i < nf; i++)
+        if (a[i] < a[best]) best = i;                 // strict: the first minimum stays
+      if (threadIdx.x == 0) c->argz = s_pix[best]; else c->argy = s_pix[best];
+    }
   }
 }
 
@@ -537,7 +608,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   dfu_view* vd = (dfu_view*)ctx->slot[SL_VIEWS];
   DFU_SLOT(ctx, key, unsigned*, SL_KEY, V * npix * sizeof(unsigned));
   DFU_SLOT(ctx, table, VoxCell*, SL_TABLE, (size_t)V * NCELL * sizeof(VoxCell));
-  DFU_SLOT(ctx, stats, unsigned long long*, SL_VOXCNT, V * 8 * sizeof(unsigned long long));
+  DFU_SLOT(ctx, stats, unsigned long long*, SL_VOXCNT, (V * 8 + 8) * sizeof(unsigned long long));   // [V][8] + the overflow-list counter
   DFU_SLOT(ctx, blkcnt, int32_t*, SL_BLKCNT, (int64_t)V * bpv * sizeof(int32_t));
   DFU_SLOT(ctx, blkoff, int64_t*, SL_BLKOFF, ((int64_t)V * bpv + 1) * sizeof(int64_t));
   DFU_SLOT(ctx, blkbits, unsigned*, SL_VOXCELL, (size_t)V * bpv * (S2_THREADS / 32) * sizeof(unsigned));
@@ -548,6 +619,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   if (const char* e = getenv("DFU3D_S2_CAPQ")) capq = (unsigned)atoi(e);   // test hook: forces the overflow (scan) path
   DFU_SLOT(ctx, ambq, uint2*, SL_AMBQ, (size_t)S2_NQ * (capq + 1) * sizeof(uint2) + S2_NQ * sizeof(unsigned));
   unsigned* ambcnt = (unsigned*)(ambq + (size_t)S2_NQ * capq);
+  const unsigned ovf_cap = (unsigned)S2_NQ * capq;      // pass B re-uses the (by then consumed) queue as the list of overflowing voxels
   {
     DFU_PROF(ctx, st, PT_MISC);
     const size_t tbytes = (size_t)V * NCELL * sizeof(VoxCell);
@@ -557,7 +629,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     }
     ctx->table_clean_ptr = nullptr;   // dirty until pass C has been queued
     ctx->table_clean_bytes = 0;
-    DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, V * 8 * sizeof(unsigned long long), st));
+    DFU_CUDA(ctx, cudaMemsetAsync(stats, 0, (V * 8 + 8) * sizeof(unsigned long long), st));
     DFU_CUDA(ctx, cudaMemsetAsync(ambcnt, 0, S2_NQ * sizeof(unsigned), st));
   }
   // float64 view constants (host copy owned by the context: it must outlive the asynchronous symbol copies)
@@ -585,7 +657,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     }
     if (V <= S2_CVIEWS) {
       DFU_PROF(ctx, st, PT_DENSIFY_B);
-      k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats);
+      k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats, ambq, ovf_cap, stats + V * 8);
       DFU_LAUNCH_CHECK(ctx);
     }
     DFU_CUDA(ctx, cudaEventRecord(ev, st));
@@ -598,9 +670,14 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     DFU_CUDA(ctx, cudaStreamWaitEvent(st, ev, 0));
     DFU_CUDA(ctx, cudaMemcpyToSymbolAsync(c_view, hc + v0, sizeof(S2View) * (size_t)nv, 0, cudaMemcpyHostToDevice, st));
     DFU_PROF(ctx, st, PT_DENSIFY_B);
-    k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats);
+    k_densify_b<<<grid, S2_THREADS, 0, st>>>(v0, bpv, q, ctx->depth, key, table, blkbits, stats, ambq, ovf_cap, stats + V * 8);
     DFU_LAUNCH_CHECK(ctx);
     DFU_CUDA(ctx, cudaEventRecord(ev, st));
+  }
+  {
+    DFU_PROF(ctx, st, PT_DENSIFY_B);
+    k_vox_overflow<<<148 * 4, 256, 0, st>>>(vd, q, ctx->depth, key, table, ambq, ovf_cap, stats + V * 8);
+    DFU_LAUNCH_CHECK(ctx);
   }
   {
     DFU_PROF(ctx, st, PT_MISC);
@@ -612,11 +689,11 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     DFU_LAUNCH_CHECK(ctx);
   }
   // read back offsets + stats (one sync)
-  size_t nb = (V + 1) * sizeof(int64_t) + V * 8 * sizeof(unsigned long long);
+  size_t nb = (V + 1) * sizeof(int64_t) + (V * 8 + 8) * sizeof(unsigned long long);
   char* pin = (char*)dfu_pinned(ctx, nb);
   if (!pin) return DFU_ERR_CUDA;
   DFU_CUDA(ctx, cudaMemcpyAsync(pin, voxoff, (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(pin + (V + 1) * sizeof(int64_t), stats, V * 8 * sizeof(unsigned long long),
+  DFU_CUDA(ctx, cudaMemcpyAsync(pin + (V + 1) * sizeof(int64_t), stats, (V * 8 + 8) * sizeof(unsigned long long),
                                 cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaStreamSynchronize(st));
   memcpy(ctx->off_vox, pin, (V + 1) * sizeof(int64_t));
@@ -660,10 +737,15 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   ctx->stage |= 4;
   if (total_miss > 0)
     return dfu_set_err(ctx, DFU_ERR_DATA, "%lld points fell outside the angular voxel table", (long long)total_miss);
-  if (total_over > 0 && !allow_overflow)
-    return dfu_set_err(ctx, DFU_ERR_DATA,
-                       "%lld angular voxels hold more than max_per_voxel points (the reference keeps only the first "
-                       "ones in input order; not reproduced)", (long long)total_over);
+  // voxels with more than max_per_voxel points were re-resolved over their first max_per_voxel points in input order
+  // (k_vox_overflow), as the reference's voxeliser does; only a list that did not fit is an error
+  (void)allow_overflow;
+  if (total_over > 0 && ctx->prm.max_per_voxel > S2_OVF_MAX)
+    return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "max_per_voxel = %d with overflowing voxels (supported: up to %d)",
+                       ctx->prm.max_per_voxel, S2_OVF_MAX);
+  if ((int64_t)hs[V * 8] > (int64_t)ovf_cap)
+    return dfu_set_err(ctx, DFU_ERR_DATA, "%lld angular voxels hold more than max_per_voxel points (list capacity %u)",
+                       (long long)hs[V * 8], ovf_cap);
   return DFU_OK;
 }
 

@@ -81,3 +81,28 @@ def test_kitti_preset_matches_oracle():
     assert np.array_equal(cloud[:nF], allp[:nF])
     np.testing.assert_allclose(cloud[nF:, :3], allp[nF:, :3], rtol=1e-5, atol=1e-9)
     assert np.array_equal(cloud[nF:, 3:], allp[nF:, 3:])
+
+
+@pytest.mark.parametrize('seed,mpv', [(3, 12), (4, 10), (5, 16)])
+def test_overflowing_voxels_keep_the_first_points_in_input_order(seed, mpv):
+    """the reference's voxeliser keeps the first max_num_points_per_voxel points of an angular voxel in
+    input order and la_sampling2 / 20 take the arg-min over those only (my_loader.py:69-83,253-257,268-272).  A small
+    max_per_voxel makes thousands of voxels overflow on an ordinary view; representatives must stay index-exact."""
+    fr = synth.make_frame(seed, 'nuscenes', n_cams=1, max_inst=4)        # full resolution: ~6 pixels per angular voxel
+    inp = synth.view_as_reference_inputs(fr, 0)
+    from oracle import restate
+    fov, allp, lines, recs, dbg = restate.run_view(inp, return_debug=True, max_per_voxel=mpv)
+    assert dbg['overflow'] > 50
+    pipe = pipeline.FusionPipeline(0, config=pipeline.FusionConfig(max_per_voxel=mpv))
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, cloud_dtype=torch.float64, instances=True)
+    assert int(res.counts_densify[0, 3]) == dbg['overflow']
+    nv = int(res.counts_densify[0, 2])
+    rz, ry, xz, xy = helpers.emit_voxels(pipe, nv)
+    assert np.array_equal(rz, dbg['rep_z_pix']) and np.array_equal(ry, dbg['rep_y_pix'])
+    cloud = res.cloud.cpu().numpy()
+    nF = int(fov.sum())
+    assert cloud.shape == allp.shape
+    np.testing.assert_allclose(cloud[nF:, :3], allp[nF:, :3], rtol=1e-5, atol=1e-9)
+    for i, d in enumerate(dbg['inst']):
+        assert tuple(res.seg_counts[i][:2]) == (d['nL'], d['nP'])
