@@ -126,10 +126,15 @@ __global__ void __launch_bounds__(I_THREADS) k_seg_count(const int32_t* __restri
   seg_warp_add(cnt, (i < np && keep[i]) ? seg[i] : -1);
 }
 
+// ractive: kept LiDAR points (the gate's reference set); qactive: kept pseudo points (the only queries whose answer
+// k_fuse_flags reads)
 __global__ void __launch_bounds__(I_THREADS) k_ref_active(const int32_t* __restrict__ seg, const uint8_t* __restrict__ keep,
-                                                          int64_t np, uint8_t* __restrict__ ractive) {
+                                                          int64_t np, uint8_t* __restrict__ ractive, uint8_t* __restrict__ qactive) {
   const int64_t i = (int64_t)blockIdx.x * I_THREADS + threadIdx.x;
-  if (i < np) ractive[i] = (keep[i] && !(seg[i] & 1)) ? 1 : 0;
+  if (i < np) {
+    ractive[i] = (keep[i] && !(seg[i] & 1)) ? 1 : 0;
+    qactive[i] = (keep[i] && (seg[i] & 1)) ? 1 : 0;
+  }
 }
 
 // final membership: LiDAR side = radius keep; pseudo side = radius keep and (gate or no kept LiDAR point)  (:602-605)
@@ -490,9 +495,9 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   DFU_CUDA(ctx, cudaMemsetAsync(zmax, 0, (size_t)G * 8, st));
   k_seg_count<<<NBLK(NP), I_THREADS, 0, st>>>(seg, keep, NP, cnt1);
   DFU_LAUNCH_CHECK(ctx);
-  k_ref_active<<<NBLK(NP), I_THREADS, 0, st>>>(seg, keep, NP, ract);
+  k_ref_active<<<NBLK(NP), I_THREADS, 0, st>>>(seg, keep, NP, ract, (uint8_t*)flag);      // flag (int32 [NP]) is written later: its bytes hold qactive until then
   DFU_LAUNCH_CHECK(ctx);
-  rc = dfu_gate_keep(ctx, st, OPS_A, px, py, pz, inst, NP, px, py, pz, inst, ract, NP, G, gprm, gate);
+  rc = dfu_gate_keep(ctx, st, OPS_A, px, py, pz, inst, NP, px, py, pz, inst, ract, NP, G, gprm, gate, (const uint8_t*)flag);
   if (rc) return rc;
   k_fuse_flags<<<NBLK(NP), I_THREADS, 0, st>>>(seg, keep, gate, cnt1, NP, flag, cnt2);
   DFU_LAUNCH_CHECK(ctx);

@@ -96,7 +96,7 @@ int dfu_radius_keep(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* 
 int dfu_gate_keep(dfu_ctx* ctx, cudaStream_t st, int slot_base, const double* qx, const double* qy, const double* qz,
                   const int32_t* qseg, int64_t nq, const double* rx, const double* ry, const double* rz,
                   const int32_t* rseg, const uint8_t* ractive, int64_t nr, int nseg, const double* maxdist_dev,
-                  uint8_t* keep);
+                  uint8_t* keep, const uint8_t* qactive = nullptr);   // qactive (nullable): queries whose answer is needed
 
 // Adaptive-range clustering + rectangle search on point sets ("instances"): x,y [n], inst [n] ascending,
 // inst_off_dev [ninst+1].  Results stay in ctx slots; see dfu_cluster.cu.

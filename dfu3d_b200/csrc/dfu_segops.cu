@@ -381,14 +381,29 @@ __device__ __forceinline__ bool gate_cell(double v, double cell, int& c) {
   return true;
 }
 
+// number of active reference points -> scal[3]; the hash then uses the smallest power of two >= 2 x that count (<= the
+// allocated capacity), so that the probes of ~2 M queries stay inside a few MB of L2 instead of a table sized for every pair
+__global__ void __launch_bounds__(G_THREADS) k_gate_count(const uint8_t* __restrict__ ractive, int64_t nr, int32_t* __restrict__ nact) {
+  const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
+  const bool a = i < nr && (!ractive || ractive[i]);
+  const unsigned m = __ballot_sync(0xffffffffu, a);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(nact, __popc(m));
+}
+__device__ __forceinline__ unsigned gate_mask(int nact, unsigned cap_mask) {
+  unsigned want = nact > 16 ? (unsigned)nact * 2u : 32u;
+  unsigned m = 0xffffffffu >> __clz(want - 1u);          // pow2ceil(want) - 1
+  return m < cap_mask ? m : cap_mask;
+}
+
 __global__ void __launch_bounds__(G_THREADS) k_gate_insert(const double* __restrict__ rx, const double* __restrict__ ry,
                                                            const double* __restrict__ rz, const int32_t* __restrict__ rseg,
                                                            const uint8_t* __restrict__ ractive, int64_t nr,
                                                            const double* __restrict__ maxdist, unsigned long long* __restrict__ hkey,
-                                                           int32_t* __restrict__ head, int32_t* __restrict__ next, unsigned hmask,
-                                                           int32_t* __restrict__ errflag) {
+                                                           int32_t* __restrict__ head, int32_t* __restrict__ next, unsigned cap_mask,
+                                                           int32_t* __restrict__ errflag, const int32_t* __restrict__ nact) {
   const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (i >= nr || (ractive && !ractive[i])) return;
+  const unsigned hmask = gate_mask(*nact, cap_mask);
   const int s = rseg[i];
   const double cell = maxdist[s] * (1.0 + 9.313225746154785e-10);
   int cx, cy, cz;
@@ -411,9 +426,13 @@ __global__ void __launch_bounds__(G_THREADS) k_gate(const double* __restrict__ q
                                                     const double* __restrict__ rx, const double* __restrict__ ry,
                                                     const double* __restrict__ rz, const double* __restrict__ maxdist,
                                                     const unsigned long long* __restrict__ hkey, const int32_t* __restrict__ head,
-                                                    const int32_t* __restrict__ next, unsigned hmask, uint8_t* __restrict__ keep) {
+                                                    const int32_t* __restrict__ next, unsigned cap_mask,
+                                                    const uint8_t* __restrict__ qactive, uint8_t* __restrict__ keep,
+                                                    const int32_t* __restrict__ nact) {
   const int64_t i = (int64_t)blockIdx.x * G_THREADS + threadIdx.x;
   if (i >= nq) return;
+  const unsigned hmask = gate_mask(*nact, cap_mask);
+  if (qactive && !qactive[i]) { keep[i] = 0; return; }      // the caller does not need this query's answer
   const int s = qseg[i];
   const double lim = maxdist[s], cell = lim * (1.0 + 9.313225746154785e-10);
   const double px = qx[i], py = qy[i], pz = qz[i];
@@ -445,7 +464,7 @@ __global__ void __launch_bounds__(G_THREADS) k_gate(const double* __restrict__ q
 int dfu_gate_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* qx, const double* qy, const double* qz,
                   const int32_t* qseg, int64_t nq, const double* rx, const double* ry, const double* rz,
                   const int32_t* rseg, const uint8_t* ractive, int64_t nr, int nseg, const double* maxdist_dev,
-                  uint8_t* keep) {
+                  uint8_t* keep, const uint8_t* qactive) {
   (void)nseg;
   if (nq == 0) return DFU_OK;
   if (nr == 0) {
@@ -462,13 +481,16 @@ int dfu_gate_keep(dfu_ctx* ctx, cudaStream_t st, int sb, const double* qx, const
   {
     DFU_PROF(ctx, st, PT_GRID_BUILD);
     DFU_CUDA(ctx, cudaMemsetAsync(htab, 0xFF, hcap * 12, st));      // keys: empty, heads: -1
+    DFU_CUDA(ctx, cudaMemsetAsync(scal + 3, 0, 4, st));
+    k_gate_count<<<(unsigned)((nr + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(ractive, nr, scal + 3);
+    DFU_LAUNCH_CHECK(ctx);
     k_gate_insert<<<(unsigned)((nr + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(rx, ry, rz, rseg, ractive, nr, maxdist_dev, htab,
-                                                                                       head, next, (unsigned)(hcap - 1), scal + 1);
+                                                                                       head, next, (unsigned)(hcap - 1), scal + 1, scal + 3);
     DFU_LAUNCH_CHECK(ctx);
   }
   DFU_PROF(ctx, st, PT_GATE);
   k_gate<<<(unsigned)((nq + G_THREADS - 1) / G_THREADS), G_THREADS, 0, st>>>(qx, qy, qz, qseg, nq, rx, ry, rz, maxdist_dev, htab, head, next,
-                                                                             (unsigned)(hcap - 1), keep);
+                                                                             (unsigned)(hcap - 1), qactive, keep, scal + 3);
   DFU_LAUNCH_CHECK(ctx);
   return DFU_OK;
 }
