@@ -455,6 +455,7 @@ def main():
                     if tr:
                         roof['filters']['traffic'] = tr['dram_bytes_per_launch']
                         roof['filters']['traffic_source'] = tr.get('source')
+                        roof['filters']['traffic_points'] = tr.get('points')    # the capture's cloud, not this leg's
                 except Exception:
                     pass
         cpu = None
