@@ -70,6 +70,7 @@ _SIGS = {
     'dfu_fuse_instances_sync': (C.c_int, [_P, _P, C.c_int, _P, C.c_int, _P, C.c_int64, _P, _P]),
     'dfu_backproject_sync': (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.c_int, _P, _P, C.c_int64, _P]),
     'dfu_split_cloud_sync': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, _P, _P, _P]),
+    'dfu_split_cloud_static': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, _P, _P, _P]),
     'dfu_voxelize_sync': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, _P, C.c_int, C.c_int, _P, _P, _P, _P]),
     'dfu_points_in_boxes': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, C.c_int, _P]),
     'dfu_crop_boxes_sync': (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, C.c_int, _P, _P, C.c_int64, _P]),

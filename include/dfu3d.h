@@ -287,6 +287,20 @@ int dfu_crop_boxes_sync(dfu_ctx* ctx, void* stream, const float* points, int C, 
 int dfu_split_cloud_sync(dfu_ctx* ctx, void* stream, const float* cloud, int C, int64_t n, const float* range_host,
                          float* out_lidar, float* out_pseudo, int64_t* counts_host);
 
+/* Allocation-free variant of dfu_split_cloud_sync.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * allocation).  Same rows, same order and same counts as dfu_split_cloud_sync, but: its scratch is a fixed 256 KB
+ * `static __device__` array inside the library (held by every GPU that loads the library until exit), so
+ * n <= DFU_SPLIT_STATIC_MAX_ROWS (more: DFU_ERR_CAPACITY, nothing launched); it calls no cudaMalloc / cudaFree / allocating
+ * library routine, uses no context scratch, does not synchronise and copies nothing to the host: counts_dev is a
+ * caller-owned DEVICE int64[2] (LiDAR rows, pseudo rows) valid once `stream` reaches this point.  ctx may be NULL (error
+ * text is then not recorded and the calling thread's current device is used).  All calls on a device share the array:
+ * calls that overlap on the GPU (different streams without an event between them) race.  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress): make it before starting a graph capture. */
+#define DFU_SPLIT_STATIC_MAX_ROWS 4194304
+int dfu_split_cloud_static(dfu_ctx* ctx, void* stream, const float* cloud, int C, int64_t n, const float* range_host,
+                           float* out_lidar, float* out_pseudo, int64_t* counts_dev);
+
 /* Hard voxelisation of transform_points_to_voxels (processor/data_processor_virtual.py:133-185; VoxelGeneratorWrapper
  * :16-58 -> spconv points_to_voxel): float32 bins floor((p - lo) / vsize), voxels numbered by first appearance, the
  * first max_points points of a voxel in input order, voxels beyond max_voxels dropped.  voxels float
