@@ -54,9 +54,12 @@
 #define SOR_FRONT 384       /* level-1 frontier capacity per tile */
 #endif
 #define SOR_MAXLEV 10
+#ifndef SOR_SWEEP
+#define SOR_SWEEP 1       /* 1: k_sor_sweep (float32 screen), 0: k_sor_tile (all-float64 work list) */
+#endif
 #define SOR_DEFER 9.0f      /* lanes whose squared bound exceeds 9 x the tile median go to k_sor_single */
 enum { SO_SEGOFF = 170, SO_POFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_REC, SO_TMP, SO_SPI,
-       SO_MEAN, SO_PART, SO_SEGSTAT, SO_SEGCH, SO_PYR, SO_TODO, SO_SCAL };
+       SO_MEAN, SO_PART, SO_SEGSTAT, SO_SEGCH, SO_PYR, SO_TODO, SO_SCAL, SO_FREC };
 
 struct SorBox { float4 lo, hi; };   // 32 bytes
 // 8 consecutive points of the sorted, padded array + their bounding box: ONE contiguous 224-byte record, so that a run
@@ -66,9 +69,14 @@ struct __align__(16) SorGroup {
   SorBox box;
 };
 static_assert(sizeof(SorGroup) == 224, "SorGroup must be 224 bytes");
+// float32 copy of a group for the screening sweep: coordinates relative to the segment's box minimum (pads: +inf)
+struct __align__(16) SorGroupF { float x[8], y[8], z[8]; };
+static_assert(sizeof(SorGroupF) == 96, "SorGroupF must be 96 bytes");
 
 struct SorTree {
   const SorGroup* rec;               // [NP / 8]
+  const SorGroupF* frec;             // [NP / 8] float32 screening copy
+  const unsigned long long* box;     // [nseg][6] ordered-bit min xyz, max xyz of the segments
   const int32_t* spi;                // [NP] original index, -1 for pads
   const int64_t* seg_off;            // [nseg+1]
   const int64_t* poff;               // [nseg+1] padded offsets (multiples of 32)
@@ -193,12 +201,16 @@ __global__ void __launch_bounds__(256) k_sor_keys(const double* __restrict__ row
   idx[i] = (int32_t)i;
 }
 
+// float32 screening coordinate: the same expression in k_sor_gather (points) and k_sor_sweep (queries)
+__device__ __forceinline__ float sor_rel_f32(double v, double origin) { return __double2float_rn(__dsub_rn(v, origin)); }
+
 // one warp per tile of the PADDED sorted domain: group records in sorted order (+inf pads), original index (-1 pads),
 // and the bounding box of every group of 8 points, rounded outwards to float (in the record and in lv[0])
 __global__ void __launch_bounds__(256) k_sor_gather(const int32_t* __restrict__ sidx, const double* __restrict__ rows,
                                                     const int64_t* __restrict__ seg_off, const int64_t* __restrict__ poff, int nseg,
                                                     int ntiles, SorGroup* __restrict__ rec, int32_t* __restrict__ spi,
-                                                    SorBox* __restrict__ gbox) {
+                                                    SorBox* __restrict__ gbox, const unsigned long long* __restrict__ box,
+                                                    SorGroupF* __restrict__ frec) {
   const int tile = (int)(((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5);
   if (tile >= ntiles) return;
   const int lane = threadIdx.x & 31;
@@ -215,6 +227,12 @@ __global__ void __launch_bounds__(256) k_sor_gather(const int32_t* __restrict__ 
   SorGroup& G = rec[t >> 3];
   G.x[lane & 7] = px; G.y[lane & 7] = py; G.z[lane & 7] = pz;
   spi[t] = i;
+  {
+    SorGroupF& F = frec[t >> 3];
+    F.x[lane & 7] = sor_rel_f32(px, dfu_unorder_f64(box[6 * s]));
+    F.y[lane & 7] = sor_rel_f32(py, dfu_unorder_f64(box[6 * s + 1]));
+    F.z[lane & 7] = sor_rel_f32(pz, dfu_unorder_f64(box[6 * s + 2]));
+  }
   float lx = i >= 0 ? __double2float_rd(px) : INFINITY, ly = i >= 0 ? __double2float_rd(py) : INFINITY,
         lz = i >= 0 ? __double2float_rd(pz) : INFINITY;
   float hx = i >= 0 ? __double2float_ru(px) : -INFINITY, hy = i >= 0 ? __double2float_ru(py) : -INFINITY,
@@ -267,9 +285,14 @@ struct __align__(128) SorWarpSmem {
   double opx[32], opy[32], opz[32];                         // the lanes' queries, readable by every lane of the warp
   double oshi[32], oslo[32], ow[32], oinvw[32];             // neighbours: d2 <= shi; shells: 16 equal parts of (slo, shi]
   int nl[32];                                               // neighbours found per lane in the current pass (may exceed LCAP)
-  int front[2][SOR_FRONT];                                  // pyramid frontiers (ping-pong)
-  int grp[SOR_CG];                                          // group ids of the chunk, ascending
-  unsigned short pair[SOR_CG * 32];                         // (owner lane << 8 | staged group): the chunk's work list
+  union {
+    struct {
+      int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
+      int grp[SOR_CG];                                      // group ids of the chunk, ascending
+      unsigned short pair[SOR_CG * 32];                     // (owner lane << 8 | staged group): the chunk's work list
+    };
+    unsigned key[LCAP][32];                                 // step 4 (the walk is over): order keys of the lanes' columns
+  };
   unsigned long long mbar;
 };
 
@@ -653,37 +676,520 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* 
       if (ties) L.active = false;
       if (!__any_sync(full, L.walk)) break;
     }
-    // ---- 4. the k' smallest in ascending order; sequential sum of square roots
+    // ---- 4. the k' smallest in ascending order; sequential sum of square roots.
+    // The order is found on 32-bit keys: key = (T << 6) | slot with T = trunc(d2 * (2^26 - 2) / shi), a monotone
+    // non-decreasing map of d2 (every column entry is <= shi), so T_a < T_b implies d2_a < d2_b and ascending keys
+    // visit the column in ascending d2 except INSIDE a run of equal T.  Such a run is harmless when the doubles come
+    // out non-descending anyway (checked on the fly) and when no entry left out ties with the last one taken while
+    // being smaller (checked after the last round); a lane that fails a check redoes the selection on the doubles.
     {
       const bool fin = L.active && !L.walk;
       const int nlf = fin ? nl : 0;
-      double acc = 0.0;
+      int nmax = nlf;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) nmax = max(nmax, __shfl_xor_sync(full, nmax, o));
+      nmax = (nmax + 3) & ~3;                  // <= LCAP (a multiple of 4)
+      const double sc = __ddiv_rn(67108862.0, L.shi);
+      for (int j = 0; j < nmax; j++) {
+        unsigned key = 0xffffffffu;
+        if (j < nlf) key = (__double2uint_rz(__dmul_rn(w.list[j][lane], sc)) << 6) | (unsigned)j;
+        w.key[j][lane] = key;
+      }
+      double acc = 0.0, prev = 0.0;
+      unsigned mlast = 0u;
+      bool redo = false;
       for (int r = 0; r < kk; r++) {
-        // four independent running minima over interleaved quarters of the column (a single compare-select chain of
-        // nlf links is pure latency); ties resolve to the same VALUE whichever slot wins
-        double b0 = inf, b1 = inf, b2 = inf, b3 = inf;
-        int i0 = 0, i1 = 0, i2 = 0, i3 = 0;
-        for (int j = 0; j < nlf; j += 4) {
-          const double x0 = w.list[j][lane];
-          const double x1 = j + 1 < nlf ? w.list[j + 1][lane] : inf;
-          const double x2 = j + 2 < nlf ? w.list[j + 2][lane] : inf;
-          const double x3 = j + 3 < nlf ? w.list[j + 3][lane] : inf;
-          if (x0 < b0) { b0 = x0; i0 = j; }
-          if (x1 < b1) { b1 = x1; i1 = j + 1; }
-          if (x2 < b2) { b2 = x2; i2 = j + 2; }
-          if (x3 < b3) { b3 = x3; i3 = j + 3; }
+        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
+        for (int j = 0; j < nmax; j += 4) {
+          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
+          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
         }
-        if (b1 < b0) { b0 = b1; i0 = i1; }
-        if (b3 < b2) { b2 = b3; i2 = i3; }
-        if (b2 < b0) { b0 = b2; i0 = i2; }
-        acc = __dadd_rn(acc, __dsqrt_rn(b0));
-        if (fin) w.list[i0][lane] = inf;
-        __syncwarp();                       // keep the warp together (the lanes' columns differ in length)
+        const unsigned m = min(min(m0, m1), min(m2, m3));
+        if (fin) {                              // nlf >= kk: m is a real key
+          const int slot = (int)(m & 63u);
+          const double d = w.list[slot][lane];
+          redo |= d < prev;
+          prev = d;
+          acc = __dadd_rn(acc, __dsqrt_rn(d));
+          w.key[slot][lane] = 0xffffffffu;
+          mlast = m;
+        }
+      }
+      // entries left out that share T with the last one taken
+      bool chk = fin && !redo;
+      while (__any_sync(full, chk)) {
+        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
+        for (int j = 0; j < nmax; j += 4) {
+          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
+          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
+        }
+        const unsigned m = min(min(m0, m1), min(m2, m3));
+        if (chk) {
+          if ((m >> 6) != (mlast >> 6)) chk = false;          // also the sentinel: T = 2^26 - 1 is never a real T
+          else if (w.list[m & 63u][lane] < prev) { redo = true; chk = false; }
+          else w.key[m & 63u][lane] = 0xffffffffu;
+        }
+      }
+      if (__any_sync(full, redo)) {              // rare: exact selection on the doubles (the column is intact)
+        const int nr = redo ? nlf : 0;
+        double acc2 = 0.0;
+        for (int r = 0; r < kk; r++) {
+          double b0 = inf;
+          int i0 = 0;
+          for (int j = 0; j < nr; j++) {
+            const double x = w.list[j][lane];
+            if (x < b0) { b0 = x; i0 = j; }
+          }
+          acc2 = __dadd_rn(acc2, __dsqrt_rn(b0));
+          if (redo) w.list[i0][lane] = inf;
+        }
+        if (redo) acc = acc2;
       }
       if (fin) mean_out[orig] = __ddiv_rn(acc, (double)kk);
+      __syncwarp();
     }
     sor_defer(L.active && L.walk, t, todo, ntodo, 2, lane);      // still narrowing after 40 passes: cannot happen
     __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- the sweep kernel (float32 screen, exact finish)
+// One warp per tile of 32 consecutive sorted queries, like k_sor_tile, but the candidates are SCREENED in float32:
+// every lane sweeps every staged point (the point is a shared-memory broadcast, the arithmetic is 7 float
+// instructions, all 32 lanes busy, no atomics, no work list) and appends the points inside its own ball to its own
+// column as (float d2, sorted position).  When a column is about to fill, the warp tightens: each lane guesses a
+// smaller radius from the density it has seen, verifies by counting that at least k entries lie inside, compacts the
+// column and shrinks its ball, so one sweep over the tile's search region suffices.  Only the few dozen survivors
+// are evaluated exactly (float64, from the group records) and the k smallest of those are summed in ascending
+// order: the float32 stage decides WHICH points are looked at, never a value.
+//
+// Error model of the screen.  Coordinates are stored as float32 relative to the segment's box minimum, E = largest
+// extent of the box, delta = 2^-22 E.  Per axis |float difference - true difference| <= 2^-23 E + 2^-24 |dx| (+ the
+// float64 subtraction, 2^-53 relative), hence for a pair at true distance d
+//     |d2f - d2| <= 4 delta d + 1e-6 d^2 + 4 delta^2      (twice what the rounding analysis gives)
+//   * a point with d2 <= B passes the screen  d2f <= S(B) = B + 4 delta sqrt(B) + 1e-6 B + 4 delta^2;
+//   * a point with d2f <= X has d <= dmax(X), the positive root of (1 - 1e-6) d^2 - 4 delta d - (X + 4 delta^2) = 0,
+//     so k entries with d2f <= X prove that the k-th neighbour lies within B' = dmax(X)^2.
+#ifndef SOR_SCG
+#define SOR_SCG 64          /* float groups staged per chunk of the sweep */
+#endif
+#ifndef SOR_SLCAP20
+#define SOR_SLCAP20 64      /* column entries per lane (k <= 20) */
+#endif
+
+template <int LCAP>
+struct __align__(128) SorSweepSmem {
+  union {
+    SorGroup win[12];                                       // step 1: the curve window, exact coordinates
+    struct {
+      SorGroupF fst[SOR_SCG];                               // step 3: staged float groups
+      int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
+      int grp[SOR_SCG];                                     // group ids of the chunk, ascending
+    };
+    unsigned key[LCAP][32];                                 // step 4: order keys of the columns
+  };
+  uint2 ent[LCAP][32];                                      // (float d2 bits, sorted position); step 4: the exact d2 (double)
+  unsigned long long mbar;
+};
+
+struct SorErr { double A, D; };                             // 4 delta, 4 delta^2
+#define SOR_ERR_C 1e-6
+
+__device__ __forceinline__ float sor_screen(double B, const SorErr& e) {
+  const double s = __fma_rn(e.A, __dsqrt_ru(B), B) + SOR_ERR_C * B + e.D;
+  return __double2float_ru(s * (1.0 + 1e-12));
+}
+__device__ __forceinline__ double sor_proven(float X, const SorErr& e) {
+  const double c = 1.0 - SOR_ERR_C, x = (double)X + e.D;
+  const double d = (e.A + __dsqrt_ru(__fma_rn(e.A, e.A, 4.0 * c * x) * (1.0 + 1e-12))) / (2.0 * c);
+  return d * d * (1.0 + 1e-12);
+}
+
+struct SorSweepLane {
+  double px, py, pz;      // the query
+  double B;               // proven squared bound of the k-th neighbour distance
+  float fx, fy, fz;       // float32 screening coordinates of the query
+  float thr;              // screen threshold S(B); < 0: the lane does not sweep
+  bool active;
+};
+
+__device__ __forceinline__ void sor_sweep_box(const SorSweepLane& L, float4& qlo, float4& qhi) {
+  const unsigned full = 0xffffffffu;
+  qlo = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  qhi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+  if (L.thr >= 0.f) {
+    const double r = __dsqrt_ru(L.B) * (1.0 + 1e-12);
+    qlo = make_float4(__double2float_rd(L.px - r), __double2float_rd(L.py - r), __double2float_rd(L.pz - r), 0.f);
+    qhi = make_float4(__double2float_ru(L.px + r), __double2float_ru(L.py + r), __double2float_ru(L.pz + r), 0.f);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    qlo.x = fminf(qlo.x, __shfl_xor_sync(full, qlo.x, o)); qlo.y = fminf(qlo.y, __shfl_xor_sync(full, qlo.y, o));
+    qlo.z = fminf(qlo.z, __shfl_xor_sync(full, qlo.z, o)); qhi.x = fmaxf(qhi.x, __shfl_xor_sync(full, qhi.x, o));
+    qhi.y = fmaxf(qhi.y, __shfl_xor_sync(full, qhi.y, o)); qhi.z = fmaxf(qhi.z, __shfl_xor_sync(full, qhi.z, o));
+  }
+}
+
+// entries of the lane's column with d2f <= X (the column holds cnt entries; cmax = the warp's largest cnt, rounded up)
+template <int LCAP>
+__device__ __forceinline__ int sor_count_le(const SorSweepSmem<LCAP>& w, int cnt, int cmax, float X, int lane) {
+  int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+  for (int j = 0; j < cmax; j += 4) {
+    c0 += (j < cnt && __uint_as_float(w.ent[j][lane].x) <= X) ? 1 : 0;
+    c1 += (j + 1 < cnt && __uint_as_float(w.ent[j + 1][lane].x) <= X) ? 1 : 0;
+    c2 += (j + 2 < cnt && __uint_as_float(w.ent[j + 2][lane].x) <= X) ? 1 : 0;
+    c3 += (j + 3 < cnt && __uint_as_float(w.ent[j + 3][lane].x) <= X) ? 1 : 0;
+  }
+  return (c0 + c1) + (c2 + c3);
+}
+
+// Shrink the balls of the lanes that hold at least kk + 8 entries.  Returns true in the lanes that MUST shrink
+// (column nearly full) and could not (more than LCAP - 8 entries share one float distance): they are deferred.
+template <int LCAP>
+__device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane& L, int& cnt, int kk, const SorErr& er, int lane) {
+  const unsigned full = 0xffffffffu;
+  const bool want = L.thr >= 0.f && cnt >= kk + 8, need = cnt > LCAP - 8;
+  int cmax = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(full, cmax, o));
+  cmax = (cmax + 3) & ~3;
+  // count(<= lo) < kk <= count(<= hi); first guess: the entries grow like the area of the ball (points on a surface)
+  float lo = -1.f, hi = L.thr, X = want ? L.thr * ((float)(kk + 4) / (float)cnt) : 0.f;
+  int chi = cnt;
+  bool exhausted = false;
+  for (int a = 0; a < 48; a++) {
+    const bool open = want && !exhausted && chi > kk + 12 && a < 3;
+    const bool forced = want && !exhausted && need && chi > LCAP - 24;
+    if (!__any_sync(full, open || forced)) break;
+    const int c = sor_count_le<LCAP>(w, cnt, cmax, X, lane);
+    if (open || forced) {
+      if (c >= kk) { hi = X; chi = c; } else lo = X;
+      // next guess: proportional to the area while nothing below is known, then bisection
+      const float nx = lo < 0.f ? hi * ((float)(kk + 4) / (float)chi) : 0.5f * (lo + hi);
+      if (nx > lo && nx < hi) X = nx; else exhausted = true;      // adjacent floats: nothing left to try
+    }
+  }
+  bool stuck = false;
+  if (want && hi < L.thr) {
+    const double Bn = sor_proven(hi, er);
+    if (Bn < L.B) {
+      L.B = Bn;
+      const float tn = sor_screen(Bn, er);
+      L.thr = tn < L.thr ? tn : L.thr;
+    }
+  }
+  // compaction (lane-private, in place)
+  int wj = 0;
+  for (int j = 0; j < cmax; j++) {
+    if (j < cnt) {
+      const uint2 e = w.ent[j][lane];
+      if (__uint_as_float(e.x) <= L.thr) { w.ent[wj][lane] = e; wj++; }
+    }
+  }
+  cnt = wj;
+  stuck = need && cnt > LCAP - 8;
+  return stuck;
+}
+
+// sweep the ng staged groups: every lane against every point
+template <int LCAP>
+__device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, int ng, SorSweepLane& L, int& cnt, int kk, const SorErr& er,
+                                                int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int lane) {
+  const unsigned full = 0xffffffffu;
+  bool tightened = false;
+  for (int g = 0; g < ng; g++) {
+    if (__any_sync(full, cnt > LCAP - 8)) {
+      const bool stuck = sor_tighten<LCAP>(w, L, cnt, kk, er, lane);
+      sor_defer(stuck, t, todo, ntodo, 2, lane);
+      if (stuck) { L.active = false; L.thr = -1.f; cnt = 0; }
+      tightened = true;
+    }
+    const SorGroupF& G = w.fst[g];
+    const unsigned pos0 = (unsigned)w.grp[g] * 8u;
+    const float4 xa = *reinterpret_cast<const float4*>(&G.x[0]), xb = *reinterpret_cast<const float4*>(&G.x[4]);
+    const float4 ya = *reinterpret_cast<const float4*>(&G.y[0]), yb = *reinterpret_cast<const float4*>(&G.y[4]);
+    const float4 za = *reinterpret_cast<const float4*>(&G.z[0]), zb = *reinterpret_cast<const float4*>(&G.z[4]);
+    const float gx[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const float gy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    const float gz[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      const float dx = gx[q] - L.fx, dy = gy[q] - L.fy, dz = gz[q] - L.fz;
+      const float d = dx * dx + dy * dy + dz * dz;
+      if (d <= L.thr) {                                     // at most 8 appends between two fill checks
+        w.ent[cnt][lane] = make_uint2(__float_as_uint(d), pos0 + q);
+        cnt++;
+      }
+    }
+  }
+  return tightened;
+}
+
+template <int KCAP, int LCAP>
+__global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double* __restrict__ mean_out, int32_t* __restrict__ todo,
+                                                              int32_t* __restrict__ ntodo, int32_t* __restrict__ tile_ctr) {
+  extern __shared__ __align__(128) unsigned char sor_smem_raw[];
+  SorSweepSmem<LCAP>& w = reinterpret_cast<SorSweepSmem<LCAP>*>(sor_smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const unsigned full = 0xffffffffu;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  if (lane == 0) dfu_mbar_init(&w.mbar, 1);
+  __syncwarp();
+  unsigned phase = 0;
+  const int W = T.k > 32 ? T.k : 32;
+  for (;;) {
+    int tile = 0;
+    if (lane == 0) tile = atomicAdd(tile_ctr, 1);
+    tile = __shfl_sync(full, tile, 0);
+    if (tile >= T.ntiles) break;
+    const int64_t t0 = (int64_t)tile * 32, t = t0 + lane;
+    const int s = sor_seg_of(T.poff, T.nseg, t0);
+    const int64_t ps = T.poff[s], pe = T.poff[s + 1];
+    const int ns = (int)(T.seg_off[s + 1] - T.seg_off[s]);
+    const int kk = ns < T.k ? ns : T.k;
+    SorSweepLane L;
+    const int orig = T.spi[t];
+    L.active = orig >= 0;
+    // segment origin and error constants
+    double ox, oy, oz;
+    SorErr er;
+    {
+      const double lx = dfu_unorder_f64(T.box[6 * s]), ly = dfu_unorder_f64(T.box[6 * s + 1]), lz = dfu_unorder_f64(T.box[6 * s + 2]);
+      const double ex = dfu_unorder_f64(T.box[6 * s + 3]) - lx, ey = dfu_unorder_f64(T.box[6 * s + 4]) - ly,
+                   ez = dfu_unorder_f64(T.box[6 * s + 5]) - lz;
+      const double E = fmax(fmax(ex, ey), fmax(ez, 1e-30));
+      const double delta = E * (1.0 / 4194304.0);
+      ox = lx; oy = ly; oz = lz;
+      er.A = 4.0 * delta; er.D = 4.0 * delta * delta;
+    }
+    // ---- 1. bound from the curve neighbours (exact coordinates): positions t-32 .. t+32, staged from [t0-32, t0+64)
+    {
+      const int64_t a = t0 - 32 > ps ? t0 - 32 : ps, b = t0 + 64 < pe ? t0 + 64 : pe;
+      const int off = (int)(a - (t0 - 32));
+      if (lane == 0) {
+        const uint32_t bytes = (uint32_t)((b - a) >> 3) * (uint32_t)sizeof(SorGroup);
+        dfu_mbar_arrive_expect_tx(&w.mbar, bytes);
+        dfu_bulk_g2s(w.win + (off >> 3), T.rec + (a >> 3), bytes, &w.mbar);
+      }
+      dfu_mbar_wait(&w.mbar, phase);
+      phase ^= 1u;
+      {
+        const int p = 32 + lane;
+        L.px = w.win[p >> 3].x[p & 7]; L.py = w.win[p >> 3].y[p & 7]; L.pz = w.win[p >> 3].z[p & 7];
+      }
+      float best[KCAP];
+#pragma unroll
+      for (int i = 0; i < KCAP; i++) best[i] = INFINITY;
+      const int last = (int)(b - (t0 - 32)) - 1;
+      const int jlo = off - (32 + lane) > -W ? off - (32 + lane) : -W;
+      const int jhi = last - (32 + lane) < W ? last - (32 + lane) : W;
+#pragma unroll 4
+      for (int j = jlo; j <= jhi; j++) {
+        const int p = 32 + lane + j;
+        const SorGroup& G = w.win[p >> 3];
+        float v = __double2float_ru(sor_d2(G.x[p & 7], G.y[p & 7], G.z[p & 7], L.px, L.py, L.pz));   // pads: +inf
+#pragma unroll
+        for (int i = 0; i < KCAP; i++) {
+          const float lo = fminf(best[i], v);
+          v = fmaxf(best[i], v);
+          best[i] = lo;
+        }
+      }
+      float kth = 0.f;
+#pragma unroll
+      for (int i = 0; i < KCAP; i++) kth = fmaxf(kth, i < kk ? best[i] : 0.f);
+      L.B = (double)kth;
+      __syncwarp();
+    }
+    // ---- 1b. lanes whose bound is far above the tile's median are handled one by one
+    {
+      float v = L.active ? (float)L.B : INFINITY;
+#pragma unroll
+      for (int k2 = 2; k2 <= 32; k2 <<= 1)
+#pragma unroll
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+          const float o = __shfl_xor_sync(full, v, j);
+          const bool up = (lane & k2) == 0 || k2 == 32, lower = (lane & j) == 0;
+          v = (lower == up) ? fminf(v, o) : fmaxf(v, o);
+        }
+      const int nv = __popc(__ballot_sync(full, L.active));
+      const float med = __shfl_sync(full, v, nv > 0 ? nv >> 1 : 0);
+      const bool far = L.active && (!(L.B < (double)INFINITY) || (float)L.B > SOR_DEFER * med);
+      sor_defer(far, t, todo, ntodo, 0, lane);
+      if (far) L.active = false;
+    }
+    if (!__any_sync(full, L.active)) continue;
+    L.fx = sor_rel_f32(L.px, ox); L.fy = sor_rel_f32(L.py, oy); L.fz = sor_rel_f32(L.pz, oz);
+    L.thr = L.active ? sor_screen(L.B, er) : -1.f;
+    // ---- 2. pyramid descent to the level-1 nodes that meet the tile's search box
+    const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
+    int fsel = 0, nf = 0;
+    float4 qlo, qhi;
+    sor_sweep_box(L, qlo, qhi);
+    {
+      int lev = 1;
+      while (lev < T.nlev - 1 && ((glast >> (3 * lev)) - (gfirst >> (3 * lev)) + 1) > 32) lev++;
+      const int nfirst = gfirst >> (3 * lev), nlast = glast >> (3 * lev);
+      bool overflow = false;
+      for (int b0 = nfirst; b0 <= nlast; b0 += 32) {
+        const int node = b0 + lane;
+        const bool hit = node <= nlast && sor_box_hits(T.lv[lev][node], qlo, qhi);
+        const unsigned bm = __ballot_sync(full, hit);
+        if (nf + __popc(bm) > SOR_FRONT) { overflow = true; break; }
+        if (hit) w.front[0][nf + __popc(bm & ((1u << lane) - 1u))] = node;
+        nf += __popc(bm);
+      }
+      __syncwarp();
+      while (!overflow && lev > 1) {
+        const int cl = lev - 1, cfirst = gfirst >> (3 * cl), clast = glast >> (3 * cl);
+        int nn = 0;
+        for (int f0 = 0; f0 < nf; f0 += 4) {
+          const int fi = f0 + (lane >> 3);
+          bool hit = false;
+          int c = -1;
+          if (fi < nf) {
+            c = w.front[fsel][fi] * 8 + (lane & 7);
+            if (c >= cfirst && c <= clast) hit = sor_box_hits(T.lv[cl][c], qlo, qhi);
+          }
+          const unsigned bm = __ballot_sync(full, hit);
+          if (nn + __popc(bm) > SOR_FRONT) { overflow = true; break; }
+          if (hit) w.front[fsel ^ 1][nn + __popc(bm & ((1u << lane) - 1u))] = c;
+          nn += __popc(bm);
+        }
+        __syncwarp();
+        fsel ^= 1; nf = nn; lev = cl;
+      }
+      if (overflow) {
+        sor_defer(L.active, t, todo, ntodo, 1, lane);
+        continue;
+      }
+    }
+    // ---- 3. one sweep over the groups that meet the (shrinking) search box
+    int cnt = 0;
+    {
+      int ng = 0;
+      for (int f0 = 0; f0 < nf || ng > 0; f0 += 4) {
+        const int fi = f0 + (lane >> 3);
+        bool hit = false;
+        int g = -1;
+        if (fi < nf) {
+          g = w.front[fsel][fi] * 8 + (lane & 7);
+          if (g >= gfirst && g <= glast) hit = sor_box_hits(T.lv[0][g], qlo, qhi);
+        }
+        const unsigned bm = __ballot_sync(full, hit);
+        const int room = SOR_SCG - ng, nb = __popc(bm);
+        const int rank = __popc(bm & ((1u << lane) - 1u));
+        if (hit && rank < room) w.grp[ng + rank] = g;
+        __syncwarp();
+        const int filled = nb < room ? ng + nb : SOR_SCG;
+        if (filled == SOR_SCG || (f0 + 4 >= nf && filled > 0)) {
+          // runs of consecutive groups -> one bulk copy each
+          if (lane == 0) dfu_mbar_arrive_expect_tx(&w.mbar, (uint32_t)filled * (uint32_t)sizeof(SorGroupF));
+          __syncwarp();
+#pragma unroll
+          for (int h = 0; h < SOR_SCG; h += 32) {
+            const int i = h + lane;
+            const int gi = i < filled ? w.grp[i] : -2;
+            const bool st = i < filled && (lane == 0 || w.grp[i - 1] + 1 != gi);
+            const unsigned starts = __ballot_sync(full, st);
+            if (st) {
+              const unsigned later = lane < 31 ? (starts >> (lane + 1)) : 0u;
+              const int lim = filled - h < 32 ? filled - h : 32;
+              const int len = later ? __ffs((int)later) : lim - lane;
+              dfu_bulk_g2s(w.fst + i, T.frec + gi, (uint32_t)len * (uint32_t)sizeof(SorGroupF), &w.mbar);
+            }
+          }
+          dfu_mbar_wait(&w.mbar, phase);
+          phase ^= 1u;
+          const bool tg = sor_sweep_chunk<LCAP>(w, filled, L, cnt, kk, er, t, todo, ntodo, lane);
+          __syncwarp();
+          if (tg) sor_sweep_box(L, qlo, qhi);
+          if (hit && rank >= room) w.grp[rank - room] = g;
+          ng = nb > room ? nb - room : 0;
+          __syncwarp();
+          if (!__any_sync(full, L.active)) break;
+        } else {
+          ng = filled;
+        }
+      }
+    }
+    // ---- 4. exact distances of the survivors (in place), the k' smallest in ascending order, sequential sum of roots
+    {
+      const bool fin = L.active;
+      const int nlf = fin ? cnt : 0;
+      int nmax = nlf;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) nmax = max(nmax, __shfl_xor_sync(full, nmax, o));
+      nmax = (nmax + 3) & ~3;
+      double (*list)[32] = reinterpret_cast<double (*)[32]>(w.ent);
+      for (int j = 0; j < nmax; j++) {
+        if (j < nlf) {
+          const unsigned pos = w.ent[j][lane].y;
+          const SorGroup& G = T.rec[pos >> 3];
+          list[j][lane] = sor_d2(G.x[pos & 7], G.y[pos & 7], G.z[pos & 7], L.px, L.py, L.pz);
+        }
+      }
+      __syncwarp();
+      // order keys: T = trunc(d2 * (2^26 - 2) / top) with top >= every entry, monotone non-decreasing in d2
+      const double top = fin ? sor_proven(L.thr, er) : 1.0;
+      const double sc = __ddiv_rn(67108862.0, top);
+      for (int j = 0; j < nmax; j++) {
+        unsigned key = 0xffffffffu;
+        if (j < nlf) key = (__double2uint_rz(__dmul_rn(list[j][lane], sc)) << 6) | (unsigned)j;
+        w.key[j][lane] = key;
+      }
+      double acc = 0.0, prev = 0.0;
+      unsigned mlast = 0u;
+      bool redo = false;
+      for (int r = 0; r < kk; r++) {
+        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
+        for (int j = 0; j < nmax; j += 4) {
+          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
+          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
+        }
+        const unsigned m = min(min(m0, m1), min(m2, m3));
+        if (fin) {
+          const int slot = (int)(m & 63u);
+          const double d = list[slot][lane];
+          redo |= d < prev;
+          prev = d;
+          acc = __dadd_rn(acc, __dsqrt_rn(d));
+          w.key[slot][lane] = 0xffffffffu;
+          mlast = m;
+        }
+      }
+      bool chk = fin && !redo;
+      while (__any_sync(full, chk)) {
+        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
+        for (int j = 0; j < nmax; j += 4) {
+          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
+          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
+        }
+        const unsigned m = min(min(m0, m1), min(m2, m3));
+        if (chk) {
+          if ((m >> 6) != (mlast >> 6)) chk = false;
+          else if (list[m & 63u][lane] < prev) { redo = true; chk = false; }
+          else w.key[m & 63u][lane] = 0xffffffffu;
+        }
+      }
+      if (__any_sync(full, redo)) {
+        const int nr = redo ? nlf : 0;
+        double acc2 = 0.0;
+        for (int r = 0; r < kk; r++) {
+          double b0 = inf;
+          int i0 = 0;
+          for (int j = 0; j < nr; j++) {
+            const double x = list[j][lane];
+            if (x < b0) { b0 = x; i0 = j; }
+          }
+          acc2 = __dadd_rn(acc2, __dsqrt_rn(b0));
+          if (redo) list[i0][lane] = inf;
+        }
+        if (redo) acc = acc2;
+      }
+      if (fin) mean_out[orig] = __ddiv_rn(acc, (double)kk);
+      __syncwarp();
+    }
   }
 }
 
@@ -953,6 +1459,7 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
   SOR_SLOT(skey, unsigned long long*, SO_SKEY, n * 8);
   SOR_SLOT(sidx, int32_t*, SO_SIDX, n * 4);
   SOR_SLOT(rec, SorGroup*, SO_REC, (size_t)(np / 8) * sizeof(SorGroup));
+  SOR_SLOT(frec, SorGroupF*, SO_FREC, (size_t)(np / 8) * sizeof(SorGroupF));
   SOR_SLOT(spi, int32_t*, SO_SPI, np * 4);
   SOR_SLOT(pyr, SorBox*, SO_PYR, (size_t)nodes * sizeof(SorBox));
   SOR_SLOT(todo, int32_t*, SO_TODO, np * 4);
@@ -973,7 +1480,7 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
     SorBox* p = pyr;
     for (int L = 0; L < T.nlev; L++) { T.lv[L] = p; p += T.nlv[L]; }
   }
-  T.rec = rec; T.spi = spi; T.seg_off = seg_off; T.poff = poff; T.nseg = nseg; T.ntiles = ntiles; T.k = k;
+  T.rec = rec; T.frec = frec; T.box = box; T.spi = spi; T.seg_off = seg_off; T.poff = poff; T.nseg = nseg; T.ntiles = ntiles; T.k = k;
   const unsigned nb = (unsigned)((n + 255) / 256);
   {
     DFU_PROF(ctx, st, PT_GRID_BUILD);
@@ -993,7 +1500,7 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
     DFU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, key, skey, idx, sidx, (int)n, 0, 48 + segbits, st));
     ctx->launches += 7;
     k_sor_gather<<<(unsigned)(((int64_t)ntiles * 32 + 255) / 256), 256, 0, st>>>(sidx, xyz, seg_off, poff, nseg, ntiles, rec, spi,
-                                                                                  (SorBox*)T.lv[0]);
+                                                                                  (SorBox*)T.lv[0], box, frec);
     DFU_LAUNCH_CHECK(ctx);
     for (int L = 1; L < T.nlev; L++) {
       k_sor_pyr<<<(T.nlv[L] + 255) / 256, 256, 0, st>>>(T.lv[L - 1], T.nlv[L - 1], (SorBox*)T.lv[L], T.nlv[L]);
@@ -1006,6 +1513,21 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
     if (k <= SOR_KFAST) {
       int grid = 148 * 16;
       if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
+#if SOR_SWEEP
+      grid = 148 * 8;
+      if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
+      if (k <= 20) {
+        const size_t smem = sizeof(SorSweepSmem<SOR_SLCAP20>) * SOR_WARPS;
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_sweep<20, SOR_SLCAP20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_sweep<20, SOR_SLCAP20>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        k_sor_sweep<20, SOR_SLCAP20><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
+      } else {
+        const size_t smem = sizeof(SorSweepSmem<64>) * SOR_WARPS;
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_sweep<32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_sweep<32, 64>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        k_sor_sweep<32, 64><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
+      }
+#else
       if (k <= 20) {
         const size_t smem = sizeof(SorWarpSmem<SOR_LCAP20>) * SOR_WARPS;
         DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<20, SOR_LCAP20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1015,6 +1537,7 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
         DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_sor_tile<32, 64><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
       }
+#endif
       DFU_LAUNCH_CHECK(ctx);
       k_sor_single<<<grid_single, 128, 0, st>>>(T, todo, scal + 1, 0, mean);
       DFU_LAUNCH_CHECK(ctx);
