@@ -780,11 +780,10 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* 
 template <int LCAP>
 struct __align__(128) SorSweepSmem {
   union {
-    SorGroup win[12];                                       // step 1: the curve window, exact coordinates
     struct {
-      SorGroupF fst[SOR_SCG];                               // step 3: staged float groups
+      SorGroupF fst[SOR_SCG];                               // staged float groups (step 1: the curve window)
       int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
-      int grp[SOR_SCG];                                     // group ids of the chunk, ascending
+      int grp[2 * SOR_SCG];                                 // group ids that passed the box test, up to two chunks
     };
     unsigned key[LCAP][32];                                 // step 4: order keys of the columns
   };
@@ -893,7 +892,7 @@ __device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane&
 
 // sweep the ng staged groups: every lane against every point
 template <int LCAP>
-__device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, int ng, SorSweepLane& L, int& cnt, int kk, const SorErr& er,
+__device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, const int* __restrict__ grp, int ng, SorSweepLane& L, int& cnt, int kk, const SorErr& er,
                                                 int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int lane) {
   const unsigned full = 0xffffffffu;
   bool tightened = false;
@@ -905,7 +904,7 @@ __device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, int ng, S
       tightened = true;
     }
     const SorGroupF& G = w.fst[g];
-    const unsigned pos0 = (unsigned)w.grp[g] * 8u;
+    const unsigned pos0 = (unsigned)grp[g] * 8u;
     const float4 xa = *reinterpret_cast<const float4*>(&G.x[0]), xb = *reinterpret_cast<const float4*>(&G.x[4]);
     const float4 ya = *reinterpret_cast<const float4*>(&G.y[0]), yb = *reinterpret_cast<const float4*>(&G.y[4]);
     const float4 za = *reinterpret_cast<const float4*>(&G.z[0]), zb = *reinterpret_cast<const float4*>(&G.z[4]);
@@ -951,7 +950,6 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
     const int orig = T.spi[t];
     L.active = orig >= 0;
     // segment origin and error constants
-    double ox, oy, oz;
     SorErr er;
     {
       const double lx = dfu_unorder_f64(T.box[6 * s]), ly = dfu_unorder_f64(T.box[6 * s + 1]), lz = dfu_unorder_f64(T.box[6 * s + 2]);
@@ -959,23 +957,27 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
                    ez = dfu_unorder_f64(T.box[6 * s + 5]) - lz;
       const double E = fmax(fmax(ex, ey), fmax(ez, 1e-30));
       const double delta = E * (1.0 / 4194304.0);
-      ox = lx; oy = ly; oz = lz;
       er.A = 4.0 * delta; er.D = 4.0 * delta * delta;
     }
-    // ---- 1. bound from the curve neighbours (exact coordinates): positions t-32 .. t+32, staged from [t0-32, t0+64)
+    // ---- 1. bound from the curve neighbours, float32: positions t-32 .. t+32 of the segment, staged from
+    //         [t0-32, t0+64); the k-th smallest screened distance X proves the bound B = sor_proven(X)
     {
       const int64_t a = t0 - 32 > ps ? t0 - 32 : ps, b = t0 + 64 < pe ? t0 + 64 : pe;
       const int off = (int)(a - (t0 - 32));
       if (lane == 0) {
-        const uint32_t bytes = (uint32_t)((b - a) >> 3) * (uint32_t)sizeof(SorGroup);
+        const uint32_t bytes = (uint32_t)((b - a) >> 3) * (uint32_t)sizeof(SorGroupF);
         dfu_mbar_arrive_expect_tx(&w.mbar, bytes);
-        dfu_bulk_g2s(w.win + (off >> 3), T.rec + (a >> 3), bytes, &w.mbar);
+        dfu_bulk_g2s(w.fst + (off >> 3), T.frec + (a >> 3), bytes, &w.mbar);
+      }
+      {
+        const SorGroup& G = T.rec[t >> 3];
+        L.px = G.x[lane & 7]; L.py = G.y[lane & 7]; L.pz = G.z[lane & 7];
       }
       dfu_mbar_wait(&w.mbar, phase);
       phase ^= 1u;
       {
         const int p = 32 + lane;
-        L.px = w.win[p >> 3].x[p & 7]; L.py = w.win[p >> 3].y[p & 7]; L.pz = w.win[p >> 3].z[p & 7];
+        L.fx = w.fst[p >> 3].x[p & 7]; L.fy = w.fst[p >> 3].y[p & 7]; L.fz = w.fst[p >> 3].z[p & 7];
       }
       float best[KCAP];
 #pragma unroll
@@ -986,8 +988,9 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
 #pragma unroll 4
       for (int j = jlo; j <= jhi; j++) {
         const int p = 32 + lane + j;
-        const SorGroup& G = w.win[p >> 3];
-        float v = __double2float_ru(sor_d2(G.x[p & 7], G.y[p & 7], G.z[p & 7], L.px, L.py, L.pz));   // pads: +inf
+        const SorGroupF& G = w.fst[p >> 3];
+        const float dx = G.x[p & 7] - L.fx, dy = G.y[p & 7] - L.fy, dz = G.z[p & 7] - L.fz;
+        float v = dx * dx + dy * dy + dz * dz;              // pads: +inf
 #pragma unroll
         for (int i = 0; i < KCAP; i++) {
           const float lo = fminf(best[i], v);
@@ -998,7 +1001,7 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
       float kth = 0.f;
 #pragma unroll
       for (int i = 0; i < KCAP; i++) kth = fmaxf(kth, i < kk ? best[i] : 0.f);
-      L.B = (double)kth;
+      L.B = L.active && kth < INFINITY ? sor_proven(kth, er) : inf;
       __syncwarp();
     }
     // ---- 1b. lanes whose bound is far above the tile's median are handled one by one
@@ -1019,7 +1022,6 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
       if (far) L.active = false;
     }
     if (!__any_sync(full, L.active)) continue;
-    L.fx = sor_rel_f32(L.px, ox); L.fy = sor_rel_f32(L.py, oy); L.fz = sor_rel_f32(L.pz, oz);
     L.thr = L.active ? sor_screen(L.B, er) : -1.f;
     // ---- 2. pyramid descent to the level-1 nodes that meet the tile's search box
     const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
@@ -1064,52 +1066,74 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
         continue;
       }
     }
-    // ---- 3. one sweep over the groups that meet the (shrinking) search box
+    // ---- 3. one sweep over the groups that meet the (shrinking) search box.  The level-1 nodes are visited from the
+    //         tile's own node outwards along the curve (the near groups hold most neighbours, so the first tightening
+    //         already brings the balls close to their final size and the far groups fail the box test), 8 nodes =
+    //         64 group boxes per step, the boxes of the next step in flight while this one is handled.
     int cnt = 0;
     {
+      const int own = (int)(t0 >> 6);
+      int m = 0;                                            // frontier nodes below the tile's own
+      for (int f0 = 0; f0 < nf; f0 += 32)
+        m += __popc(__ballot_sync(full, f0 + lane < nf && w.front[fsel][f0 + lane] < own));
+      const int nu = nf - m, nd = m, nalt = 2 * (nu < nd ? nu : nd);
+      const int nsteps = (nf + 7) >> 3;
       int ng = 0;
-      for (int f0 = 0; f0 < nf || ng > 0; f0 += 4) {
-        const int fi = f0 + (lane >> 3);
-        bool hit = false;
-        int g = -1;
-        if (fi < nf) {
-          g = w.front[fsel][fi] * 8 + (lane & 7);
-          if (g >= gfirst && g <= glast) hit = sor_box_hits(T.lv[0][g], qlo, qhi);
-        }
-        const unsigned bm = __ballot_sync(full, hit);
-        const int room = SOR_SCG - ng, nb = __popc(bm);
-        const int rank = __popc(bm & ((1u << lane) - 1u));
-        if (hit && rank < room) w.grp[ng + rank] = g;
-        __syncwarp();
-        const int filled = nb < room ? ng + nb : SOR_SCG;
-        if (filled == SOR_SCG || (f0 + 4 >= nf && filled > 0)) {
-          // runs of consecutive groups -> one bulk copy each
-          if (lane == 0) dfu_mbar_arrive_expect_tx(&w.mbar, (uint32_t)filled * (uint32_t)sizeof(SorGroupF));
-          __syncwarp();
+      SorBox bxa, bxb;
+      int ga = -1, gb = -1;
+      auto fetch = [&](int step) {
+        ga = -1; gb = -1;
 #pragma unroll
-          for (int h = 0; h < SOR_SCG; h += 32) {
-            const int i = h + lane;
-            const int gi = i < filled ? w.grp[i] : -2;
-            const bool st = i < filled && (lane == 0 || w.grp[i - 1] + 1 != gi);
-            const unsigned starts = __ballot_sync(full, st);
-            if (st) {
-              const unsigned later = lane < 31 ? (starts >> (lane + 1)) : 0u;
-              const int lim = filled - h < 32 ? filled - h : 32;
-              const int len = later ? __ffs((int)later) : lim - lane;
-              dfu_bulk_g2s(w.fst + i, T.frec + gi, (uint32_t)len * (uint32_t)sizeof(SorGroupF), &w.mbar);
-            }
+        for (int h = 0; h < 2; h++) {
+          const int i = step * 8 + h * 4 + (lane >> 3);     // position in the outward visiting order
+          int g = -1;
+          if (i < nf) {
+            const int fi = i < nalt ? ((i & 1) ? m - 1 - (i >> 1) : m + (i >> 1)) : (nu > nd ? m + (i - nd) : m - 1 - (i - nu));
+            g = w.front[fsel][fi] * 8 + (lane & 7);
+            if (g < gfirst || g > glast) g = -1;
           }
-          dfu_mbar_wait(&w.mbar, phase);
-          phase ^= 1u;
-          const bool tg = sor_sweep_chunk<LCAP>(w, filled, L, cnt, kk, er, t, todo, ntodo, lane);
-          __syncwarp();
+          if (h == 0) { ga = g; if (g >= 0) bxa = T.lv[0][g]; } else { gb = g; if (g >= 0) bxb = T.lv[0][g]; }
+        }
+      };
+      fetch(0);
+      for (int step = 0; step < nsteps; step++) {
+        const bool hita = ga >= 0 && sor_box_hits(bxa, qlo, qhi), hitb = gb >= 0 && sor_box_hits(bxb, qlo, qhi);
+        const int cga = ga, cgb = gb;
+        if (step + 1 < nsteps) fetch(step + 1);
+        const unsigned ma = __ballot_sync(full, hita), mb = __ballot_sync(full, hitb);
+        const unsigned below = (1u << lane) - 1u;
+        if (hita) w.grp[ng + __popc(ma & below)] = cga;
+        if (hitb) w.grp[ng + __popc(ma) + __popc(mb & below)] = cgb;
+        ng += __popc(ma) + __popc(mb);
+        __syncwarp();
+        if (ng >= SOR_SCG || (step + 1 == nsteps && ng > 0)) {
+          bool tg = false;
+          for (int c0 = 0; c0 < ng; c0 += SOR_SCG) {
+            const int filled = ng - c0 < SOR_SCG ? ng - c0 : SOR_SCG;
+            // runs of consecutive groups -> one bulk copy each
+            if (lane == 0) dfu_mbar_arrive_expect_tx(&w.mbar, (uint32_t)filled * (uint32_t)sizeof(SorGroupF));
+            __syncwarp();
+#pragma unroll
+            for (int h = 0; h < SOR_SCG; h += 32) {
+              const int i = h + lane;
+              const int gi = i < filled ? w.grp[c0 + i] : -2;
+              const bool st = i < filled && (lane == 0 || w.grp[c0 + i - 1] + 1 != gi);
+              const unsigned starts = __ballot_sync(full, st);
+              if (st) {
+                const unsigned later = lane < 31 ? (starts >> (lane + 1)) : 0u;
+                const int lim = filled - h < 32 ? filled - h : 32;
+                const int len = later ? __ffs((int)later) : lim - lane;
+                dfu_bulk_g2s(w.fst + i, T.frec + gi, (uint32_t)len * (uint32_t)sizeof(SorGroupF), &w.mbar);
+              }
+            }
+            dfu_mbar_wait(&w.mbar, phase);
+            phase ^= 1u;
+            tg |= sor_sweep_chunk<LCAP>(w, w.grp + c0, filled, L, cnt, kk, er, t, todo, ntodo, lane);
+            __syncwarp();
+          }
           if (tg) sor_sweep_box(L, qlo, qhi);
-          if (hit && rank >= room) w.grp[rank - room] = g;
-          ng = nb > room ? nb - room : 0;
-          __syncwarp();
+          ng = 0;
           if (!__any_sync(full, L.active)) break;
-        } else {
-          ng = filled;
         }
       }
     }
