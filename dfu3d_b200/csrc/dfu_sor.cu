@@ -70,8 +70,9 @@ struct __align__(16) SorGroup {
 };
 static_assert(sizeof(SorGroup) == 224, "SorGroup must be 224 bytes");
 // float32 copy of a group for the screening sweep: coordinates relative to the segment's box minimum (pads: +inf)
-struct __align__(16) SorGroupF { float x[8], y[8], z[8]; };
-static_assert(sizeof(SorGroupF) == 96, "SorGroupF must be 96 bytes");
+// and the box of those eight float triples (empty for an all-pad group)
+struct __align__(16) SorGroupF { float x[8], y[8], z[8]; float lo[3], hi[3], pad[2]; };
+static_assert(sizeof(SorGroupF) == 128, "SorGroupF must be 128 bytes");
 
 struct SorTree {
   const SorGroup* rec;               // [NP / 8]
@@ -229,9 +230,17 @@ __global__ void __launch_bounds__(256) k_sor_gather(const int32_t* __restrict__ 
   spi[t] = i;
   {
     SorGroupF& F = frec[t >> 3];
-    F.x[lane & 7] = sor_rel_f32(px, dfu_unorder_f64(box[6 * s]));
-    F.y[lane & 7] = sor_rel_f32(py, dfu_unorder_f64(box[6 * s + 1]));
-    F.z[lane & 7] = sor_rel_f32(pz, dfu_unorder_f64(box[6 * s + 2]));
+    const float rx = sor_rel_f32(px, dfu_unorder_f64(box[6 * s])), ry = sor_rel_f32(py, dfu_unorder_f64(box[6 * s + 1])),
+                rz = sor_rel_f32(pz, dfu_unorder_f64(box[6 * s + 2]));
+    F.x[lane & 7] = rx; F.y[lane & 7] = ry; F.z[lane & 7] = rz;
+    float ax = rx, ay = ry, az = rz, bx = i >= 0 ? rx : -INFINITY, by = i >= 0 ? ry : -INFINITY, bz = i >= 0 ? rz : -INFINITY;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+      ax = fminf(ax, __shfl_xor_sync(0xffffffffu, ax, o)); ay = fminf(ay, __shfl_xor_sync(0xffffffffu, ay, o));
+      az = fminf(az, __shfl_xor_sync(0xffffffffu, az, o)); bx = fmaxf(bx, __shfl_xor_sync(0xffffffffu, bx, o));
+      by = fmaxf(by, __shfl_xor_sync(0xffffffffu, by, o)); bz = fmaxf(bz, __shfl_xor_sync(0xffffffffu, bz, o));
+    }
+    if ((lane & 7) == 0) { F.lo[0] = ax; F.lo[1] = ay; F.lo[2] = az; F.hi[0] = bx; F.hi[1] = by; F.hi[2] = bz; F.pad[0] = F.pad[1] = 0.f; }
   }
   float lx = i >= 0 ? __double2float_rd(px) : INFINITY, ly = i >= 0 ? __double2float_rd(py) : INFINITY,
         lz = i >= 0 ? __double2float_rd(pz) : INFINITY;
@@ -845,9 +854,9 @@ __device__ __forceinline__ int sor_count_le(const SorSweepSmem<LCAP>& w, int cnt
 // Shrink the balls of the lanes that hold at least kk + 8 entries.  Returns true in the lanes that MUST shrink
 // (column nearly full) and could not (more than LCAP - 8 entries share one float distance): they are deferred.
 template <int LCAP>
-__device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane& L, int& cnt, int kk, const SorErr& er, int lane) {
+__device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane& L, int& cnt, int kk, const SorErr& er, int lane, int slack = 8) {
   const unsigned full = 0xffffffffu;
-  const bool want = L.thr >= 0.f && cnt >= kk + 8, need = cnt > LCAP - 8;
+  const bool want = L.thr >= 0.f && cnt >= kk + slack, need = cnt > LCAP - 8;
   int cmax = cnt;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(full, cmax, o));
@@ -857,7 +866,7 @@ __device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane&
   int chi = cnt;
   bool exhausted = false;
   for (int a = 0; a < 48; a++) {
-    const bool open = want && !exhausted && chi > kk + 12 && a < 3;
+    const bool open = want && !exhausted && chi > kk + slack + 4 && a < 3;
     const bool forced = want && !exhausted && need && chi > LCAP - 24;
     if (!__any_sync(full, open || forced)) break;
     const int c = sor_count_le<LCAP>(w, cnt, cmax, X, lane);
@@ -879,11 +888,12 @@ __device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane&
   }
   // compaction (lane-private, in place)
   int wj = 0;
-  for (int j = 0; j < cmax; j++) {
-    if (j < cnt) {
-      const uint2 e = w.ent[j][lane];
-      if (__uint_as_float(e.x) <= L.thr) { w.ent[wj][lane] = e; wj++; }
-    }
+  for (int j = 0; j < cmax; j += 4) {                       // wj <= j: a store never reaches an entry not yet loaded
+    const uint2 e0 = w.ent[j][lane], e1 = w.ent[j + 1][lane], e2 = w.ent[j + 2][lane], e3 = w.ent[j + 3][lane];
+    if (j < cnt && __uint_as_float(e0.x) <= L.thr) { w.ent[wj][lane] = e0; wj++; }
+    if (j + 1 < cnt && __uint_as_float(e1.x) <= L.thr) { w.ent[wj][lane] = e1; wj++; }
+    if (j + 2 < cnt && __uint_as_float(e2.x) <= L.thr) { w.ent[wj][lane] = e2; wj++; }
+    if (j + 3 < cnt && __uint_as_float(e3.x) <= L.thr) { w.ent[wj][lane] = e3; wj++; }
   }
   cnt = wj;
   stuck = need && cnt > LCAP - 8;
@@ -896,30 +906,58 @@ __device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, const int
                                                 int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int lane) {
   const unsigned full = 0xffffffffu;
   bool tightened = false;
+  float4 xa, xb, ya, yb, za, zb, ba, bb;
+  auto load = [&](int g) {
+    const SorGroupF& G = w.fst[g];
+    xa = *reinterpret_cast<const float4*>(&G.x[0]); xb = *reinterpret_cast<const float4*>(&G.x[4]);
+    ya = *reinterpret_cast<const float4*>(&G.y[0]); yb = *reinterpret_cast<const float4*>(&G.y[4]);
+    za = *reinterpret_cast<const float4*>(&G.z[0]); zb = *reinterpret_cast<const float4*>(&G.z[4]);
+    ba = *reinterpret_cast<const float4*>(&G.lo[0]); bb = *reinterpret_cast<const float4*>(&G.hi[1]);   // lo xyz hi x | hi y z
+  };
+  load(0);
   for (int g = 0; g < ng; g++) {
+    const float gx[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const float gy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    const float gz[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+    // squared distance from the query to the group's float box, by the same monotone operations as the point distances
+    // below: it is <= the screened distance of every point of the group, so a group no lane can reach is skipped
+    const float ex = fmaxf(fmaxf(ba.x - L.fx, L.fx - ba.w), 0.f), ey = fmaxf(fmaxf(ba.y - L.fy, L.fy - bb.x), 0.f),
+                ez = fmaxf(fmaxf(ba.z - L.fz, L.fz - bb.y), 0.f);
+    const float bd = __fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex)));
+    if (g + 1 < ng) load(g + 1);                            // the next group's broadcast loads overlap this group's arithmetic
+#ifdef SOR_STATS
+    if (lane == 0) atomicAdd(&g_sor_stats[1], 1ull);
+#endif
+    if (!__any_sync(full, bd <= L.thr)) continue;
     if (__any_sync(full, cnt > LCAP - 8)) {
+#ifdef SOR_STATS
+      if (lane == 0) atomicAdd(&g_sor_stats[3], 1ull);
+#endif
       const bool stuck = sor_tighten<LCAP>(w, L, cnt, kk, er, lane);
       sor_defer(stuck, t, todo, ntodo, 2, lane);
       if (stuck) { L.active = false; L.thr = -1.f; cnt = 0; }
       tightened = true;
     }
-    const SorGroupF& G = w.fst[g];
     const unsigned pos0 = (unsigned)grp[g] * 8u;
-    const float4 xa = *reinterpret_cast<const float4*>(&G.x[0]), xb = *reinterpret_cast<const float4*>(&G.x[4]);
-    const float4 ya = *reinterpret_cast<const float4*>(&G.y[0]), yb = *reinterpret_cast<const float4*>(&G.y[4]);
-    const float4 za = *reinterpret_cast<const float4*>(&G.z[0]), zb = *reinterpret_cast<const float4*>(&G.z[4]);
-    const float gx[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
-    const float gy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
-    const float gz[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+#ifdef SOR_STATS
+    const int cnt0 = cnt;
+#endif
 #pragma unroll
     for (int q = 0; q < 8; q++) {
       const float dx = gx[q] - L.fx, dy = gy[q] - L.fy, dz = gz[q] - L.fz;
-      const float d = dx * dx + dy * dy + dz * dz;
+      const float d = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
       if (d <= L.thr) {                                     // at most 8 appends between two fill checks
         w.ent[cnt][lane] = make_uint2(__float_as_uint(d), pos0 + q);
         cnt++;
       }
     }
+#ifdef SOR_STATS
+    {
+      const unsigned hm = __ballot_sync(full, cnt > cnt0);
+      if (lane == 0) { atomicAdd(&g_sor_stats[2], 1ull); atomicAdd(&g_sor_stats[6], (unsigned long long)__popc(hm)); }
+      atomicAdd(&g_sor_stats[7], (unsigned long long)(cnt - cnt0));
+    }
+#endif
   }
   return tightened;
 }
@@ -1079,6 +1117,7 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
       const int nu = nf - m, nd = m, nalt = 2 * (nu < nd ? nu : nd);
       const int nsteps = (nf + 7) >> 3;
       int ng = 0;
+      bool first = true;
       SorBox bxa, bxb;
       int ga = -1, gb = -1;
       auto fetch = [&](int step) {
@@ -1131,6 +1170,13 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
             tg |= sor_sweep_chunk<LCAP>(w, w.grp + c0, filled, L, cnt, kk, er, t, todo, ntodo, lane);
             __syncwarp();
           }
+          if (first) {                                      // the near groups are in: shrink every ball that can be shrunk
+            first = false;
+            const bool stuck = sor_tighten<LCAP>(w, L, cnt, kk, er, lane, 3);
+            sor_defer(stuck, t, todo, ntodo, 2, lane);
+            if (stuck) { L.active = false; L.thr = -1.f; cnt = 0; }
+            tg = true;
+          }
           if (tg) sor_sweep_box(L, qlo, qhi);
           ng = 0;
           if (!__any_sync(full, L.active)) break;
@@ -1141,17 +1187,30 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
     {
       const bool fin = L.active;
       const int nlf = fin ? cnt : 0;
+#ifdef SOR_STATS
+      if (lane == 0) atomicAdd(&g_sor_stats[0], 1ull);
+      atomicAdd(&g_sor_stats[4], (unsigned long long)nlf);
+      atomicAdd(&g_sor_stats[5], (unsigned long long)(fin ? 1 : 0));
+#endif
       int nmax = nlf;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) nmax = max(nmax, __shfl_xor_sync(full, nmax, o));
       nmax = (nmax + 3) & ~3;
       double (*list)[32] = reinterpret_cast<double (*)[32]>(w.ent);
-      for (int j = 0; j < nmax; j++) {
-        if (j < nlf) {
-          const unsigned pos = w.ent[j][lane].y;
-          const SorGroup& G = T.rec[pos >> 3];
-          list[j][lane] = sor_d2(G.x[pos & 7], G.y[pos & 7], G.z[pos & 7], L.px, L.py, L.pz);
+      for (int j = 0; j < nmax; j += 4) {                   // four entries' loads in flight
+        double cx[4], cy[4], cz[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          cx[u] = cy[u] = cz[u] = 0.0;
+          if (j + u < nlf) {
+            const unsigned pos = w.ent[j + u][lane].y;
+            const SorGroup& G = T.rec[pos >> 3];
+            cx[u] = G.x[pos & 7]; cy[u] = G.y[pos & 7]; cz[u] = G.z[pos & 7];
+          }
         }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (j + u < nlf) list[j + u][lane] = sor_d2(cx[u], cy[u], cz[u], L.px, L.py, L.pz);
       }
       __syncwarp();
       // order keys: T = trunc(d2 * (2^26 - 2) / top) with top >= every entry, monotone non-decreasing in d2

@@ -8,7 +8,7 @@ calibs = [(v['P2'], v['R0'], v['V2C']) for v in fr['views']]
 xyz, pix, counts = ops.backproject(depth, calibs)
 ops.sor_filter(xyz, 20, 2.0, return_stats=True)
 torch.cuda.synchronize()
-names = ['consumes', 'pairs', 'passes', 'groups_staged', 'frontier_nodes', 'walking_lanes']
+names = ['tiles', 'groups_swept', 'groups_with_a_hit', 'tightenings_in_sweep', 'final_entries', 'final_lanes', 'lanes_hit_per_group_sum', 'appends']
 n = xyz.shape[0]; tiles = n / 32
 for i, nm in enumerate(names):
     v = int(ctx.lib.dfu_sor_counter(ctx.h, 10 + i))
