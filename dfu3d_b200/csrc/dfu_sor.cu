@@ -792,7 +792,7 @@ struct __align__(128) SorSweepSmem {
     struct {
       SorGroupF fst[SOR_SCG];                               // staged float groups (step 1: the curve window)
       int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
-      int grp[2 * SOR_SCG];                                 // group ids that passed the box test, up to two chunks
+      int grp[SOR_SCG + 64];                                // group ids that passed the box test (a step adds up to 64)
     };
     unsigned key[LCAP][32];                                 // step 4: order keys of the columns
   };
@@ -867,7 +867,7 @@ __device__ __forceinline__ bool sor_tighten(SorSweepSmem<LCAP>& w, SorSweepLane&
   bool exhausted = false;
   for (int a = 0; a < 48; a++) {
     const bool open = want && !exhausted && chi > kk + slack + 4 && a < 3;
-    const bool forced = want && !exhausted && need && chi > LCAP - 24;
+    const bool forced = want && !exhausted && need && chi > (LCAP - 24 > kk + 4 ? LCAP - 24 : kk + 4);
     if (!__any_sync(full, open || forced)) break;
     const int c = sor_count_le<LCAP>(w, cnt, cmax, X, lane);
     if (open || forced) {
@@ -906,29 +906,24 @@ __device__ __forceinline__ bool sor_sweep_chunk(SorSweepSmem<LCAP>& w, const int
                                                 int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int lane) {
   const unsigned full = 0xffffffffu;
   bool tightened = false;
-  float4 xa, xb, ya, yb, za, zb, ba, bb;
-  auto load = [&](int g) {
-    const SorGroupF& G = w.fst[g];
-    xa = *reinterpret_cast<const float4*>(&G.x[0]); xb = *reinterpret_cast<const float4*>(&G.x[4]);
-    ya = *reinterpret_cast<const float4*>(&G.y[0]); yb = *reinterpret_cast<const float4*>(&G.y[4]);
-    za = *reinterpret_cast<const float4*>(&G.z[0]); zb = *reinterpret_cast<const float4*>(&G.z[4]);
-    ba = *reinterpret_cast<const float4*>(&G.lo[0]); bb = *reinterpret_cast<const float4*>(&G.hi[1]);   // lo xyz hi x | hi y z
-  };
-  load(0);
   for (int g = 0; g < ng; g++) {
-    const float gx[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
-    const float gy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
-    const float gz[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+    const SorGroupF& G = w.fst[g];
     // squared distance from the query to the group's float box, by the same monotone operations as the point distances
     // below: it is <= the screened distance of every point of the group, so a group no lane can reach is skipped
+    const float4 ba = *reinterpret_cast<const float4*>(&G.lo[0]), bb = *reinterpret_cast<const float4*>(&G.hi[1]);   // lo xyz hi x | hi y z
     const float ex = fmaxf(fmaxf(ba.x - L.fx, L.fx - ba.w), 0.f), ey = fmaxf(fmaxf(ba.y - L.fy, L.fy - bb.x), 0.f),
                 ez = fmaxf(fmaxf(ba.z - L.fz, L.fz - bb.y), 0.f);
     const float bd = __fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex)));
-    if (g + 1 < ng) load(g + 1);                            // the next group's broadcast loads overlap this group's arithmetic
 #ifdef SOR_STATS
     if (lane == 0) atomicAdd(&g_sor_stats[1], 1ull);
 #endif
     if (!__any_sync(full, bd <= L.thr)) continue;
+    const float4 xa = *reinterpret_cast<const float4*>(&G.x[0]), xb = *reinterpret_cast<const float4*>(&G.x[4]);
+    const float4 ya = *reinterpret_cast<const float4*>(&G.y[0]), yb = *reinterpret_cast<const float4*>(&G.y[4]);
+    const float4 za = *reinterpret_cast<const float4*>(&G.z[0]), zb = *reinterpret_cast<const float4*>(&G.z[4]);
+    const float gx[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const float gy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    const float gz[8] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
     if (__any_sync(full, cnt > LCAP - 8)) {
 #ifdef SOR_STATS
       if (lane == 0) atomicAdd(&g_sor_stats[3], 1ull);
