@@ -8,29 +8,32 @@
 //   mu      = sum over mean_i > 0 of mean_i / n,   sigma = sqrt(sum over mean_i > 0 of (mean_i - mu)^2 / (n - 1))
 //   keep_i  = 0 < mean_i < mu + ratio * sigma
 //
-// Exact k-NN, cell-centric, shared-memory staged (round 2 rebuild; the round-1 kernel walked an implicit octree with one
-// thread per point and kept its top-k list in local memory: 7 of 32 lanes active, 25 ms per 4 M points):
+// Exact k-NN, staged through shared memory with TMA bulk copies (round 2 rebuild; the round-1 kernel walked an implicit
+// octree with one thread per point and kept its top-k list in local memory: 7 of 32 lanes active, 25 ms per 4 M points):
 //   * ONE radix sort by a 48-bit Hilbert key per segment puts spatial neighbours next to each other; every segment is
-//     padded to a multiple of 32 points.  Leaves ("groups") are 8 consecutive sorted points with an exact float
-//     bounding box rounded outwards; an 8-ary pyramid of boxes over the group array is the search structure.
-//   * k_sor_tile: one WARP per tile of 32 consecutive sorted queries.
-//       1. upper bound of the k-th neighbour distance from the +-k curve neighbours (float insertion network in
-//          registers, rounded up), staged with one TMA bulk copy per coordinate array;
-//       2. the tile's search box (union of the lanes' balls) is intersected with the pyramid level by level, 32 nodes
-//          per step; the surviving groups arrive in ascending order, so they form a few contiguous RUNS of the sorted
-//          arrays;
-//       3. the runs are staged in shared memory 64 groups at a time with cp.async.bulk + mbarrier (expect-tx), each
-//          lane tests the 64 staged boxes against its OWN ball (a 64-bit mask) and walks only its own groups;
-//       4. pass A counts the lane's neighbours in 16 shells of d^2 (lane-private shared-memory counters), which yields
-//          the shell that holds the k-th neighbour; pass B collects the <= k + few candidates below that shell into a
-//          lane-private shared-memory column; the k smallest are extracted in ascending order and their square roots
-//          added sequentially (bit-identical to std::accumulate over the sorted distances).
-//     No top-k list in local memory, no per-thread tree walk; all distance arithmetic is the exact float64 expression.
+//     padded to a multiple of 32 points.  Leaves ("groups") are 8 consecutive sorted points: an exact float64 record
+//     (SorGroup) and a float32 screening record (SorGroupF: coordinates relative to the segment's box minimum + their
+//     box); an 8-ary pyramid of boxes over the group array is the search structure.
+//   * k_sor_sweep: one WARP per tile of 32 consecutive sorted queries.
+//       1. a proven bound of the k-th neighbour distance from the +-32 curve neighbours (float32 insertion network in
+//          registers over the bulk-copied window, turned into a bound by the error model below);
+//       2. the tile's search box (union of the lanes' balls) is intersected with the pyramid level by level; the
+//          surviving level-1 nodes are visited from the tile's own node outwards;
+//       3. the group boxes of 8 nodes are tested per step (the next step's boxes in flight), the groups that pass are
+//          staged 64 at a time with cp.async.bulk + mbarrier (one copy per run of consecutive groups) and SWEPT:
+//          every lane evaluates every staged point in float32 (broadcast reads, no atomics, no work list; a group
+//          whose box no lane can reach is skipped by one vote) and appends the points inside its ball to its own
+//          shared-memory column.  A column about to fill triggers a tightening of all balls (guess a smaller radius
+//          from the density seen so far, verify by counting, compact), so one sweep over the region suffices;
+//       4. the exact float64 distances of the few dozen survivors are computed in place, the k smallest extracted in
+//          ascending order on 32-bit order keys (with an exact fallback for ties) and their square roots added
+//          sequentially (bit-identical to std::accumulate over the sorted distances).
+//     float32 decides which points are looked at, never a value.  No local memory.
 //   * Queries whose bound is far larger than their tile's (salt outliers: their curve neighbours are far away), tiles
-//     whose search box meets too many nodes, and lanes whose k-th shell holds too many ties are DEFERRED to
-//     k_sor_single: one warp per query, nearest-first descent of the same pyramid with pruning against the current
-//     k-th distance, the k best kept sorted across the lanes of the warp (registers + shuffles).  k > 32 runs entirely
-//     on that kernel.
+//     whose search box meets too many nodes (a jump of the curve inside the tile), and lanes whose column holds more
+//     equal distances than it has room for are DEFERRED to k_sor_single: one warp per query, nearest-first descent of
+//     the same pyramid with pruning against the current k-th distance, the k best kept sorted across the lanes of the
+//     warp (registers + shuffles).  k > 32 runs entirely on that kernel.
 // The reductions for mu and sigma are two-stage and order-fixed (chunk partials, then one block per segment), so the
 // result does not depend on scheduling.
 #include <cub/device/device_radix_sort.cuh>
@@ -38,25 +41,15 @@
 #include "dfu_ops.cuh"
 
 #define SOR_KMAX 64
-#define SOR_KFAST 32        /* k_sor_tile handles k <= 32 */
+#define SOR_KFAST 32        /* k_sor_sweep handles k <= 32 */
 #define SOR_CHUNK 4096      /* points per partial sum of the mu / sigma reductions */
 #ifndef SOR_WARPS
-#define SOR_WARPS 2         /* warps (tiles in flight) per CTA of k_sor_tile */
+#define SOR_WARPS 2         /* warps (tiles in flight) per CTA of k_sor_sweep */
 #endif
-#ifndef SOR_CG
-#define SOR_CG 32           /* groups staged per chunk (one bit of the lane's mask each) */
-#endif
-#ifndef SOR_LCAP20
-#define SOR_LCAP20 40       /* column entries per lane of the k <= 20 instantiation */
-#endif
-#define SOR_NBIN 16
 #ifndef SOR_FRONT
 #define SOR_FRONT 384       /* level-1 frontier capacity per tile */
 #endif
 #define SOR_MAXLEV 10
-#ifndef SOR_SWEEP
-#define SOR_SWEEP 1       /* 1: k_sor_sweep (float32 screen), 0: k_sor_tile (all-float64 work list) */
-#endif
 #define SOR_DEFER 9.0f      /* lanes whose squared bound exceeds 9 x the tile median go to k_sor_single */
 enum { SO_SEGOFF = 170, SO_POFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_REC, SO_TMP, SO_SPI,
        SO_MEAN, SO_PART, SO_SEGSTAT, SO_SEGCH, SO_PYR, SO_TODO, SO_SCAL, SO_FREC };
@@ -282,213 +275,14 @@ __device__ __forceinline__ double sor_d2(double ax, double ay, double az, double
   return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
-// ---------------------------------------------------------------- the tile kernel
 #ifdef SOR_STATS
-__device__ unsigned long long g_sor_stats[8];   // consumes, pairs, passes, groups staged, frontier nodes, walking lanes
+__device__ unsigned long long g_sor_stats[8];   // tiles, groups tested, groups swept, tightenings, final entries, final lanes, lanes hit, appends
 #endif
-template <int LCAP>
-struct __align__(128) SorWarpSmem {
-  SorGroup stage[SOR_CG];                                   // staged groups (also the curve window of step 1)
-  double list[LCAP][32];                                    // squared distances of a lane's neighbours, one column per lane
-  unsigned cnt[SOR_NBIN + 1][32];                           // lanes with more than LCAP neighbours: per shell, [NBIN] = below slo
-  double opx[32], opy[32], opz[32];                         // the lanes' queries, readable by every lane of the warp
-  double oshi[32], oslo[32], ow[32], oinvw[32];             // neighbours: d2 <= shi; shells: 16 equal parts of (slo, shi]
-  int nl[32];                                               // neighbours found per lane in the current pass (may exceed LCAP)
-  union {
-    struct {
-      int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
-      int grp[SOR_CG];                                      // group ids of the chunk, ascending
-      unsigned short pair[SOR_CG * 32];                     // (owner lane << 8 | staged group): the chunk's work list
-    };
-    unsigned key[LCAP][32];                                 // step 4 (the walk is over): order keys of the lanes' columns
-  };
-  unsigned long long mbar;
-};
-
-struct SorLane {
-  double px, py, pz;      // the query
-  double shi, slo;        // current squared bound of the k-th neighbour distance / lower edge of the shells
-  float fx, fy, fz;       // float copy of the query
-  float flim;             // float-side squared test radius (conservative, see sor_lane_flim); < 0: the lane does not walk
-  bool active, walk;
-};
-
-// float-side test radius for the box tests of a lane: a group may only be skipped if no point of it can lie within
-// sqrt(lim2).  The float copy of the query is off by at most half an ulp per axis; boxes are rounded outwards.
-__device__ __forceinline__ float sor_lane_flim(double lim2, float fx, float fy, float fz) {
-  const float r = __double2float_ru(__dsqrt_ru(lim2));
-  const float e = 2.4e-7f * (fabsf(fx) + fabsf(fy) + fabsf(fz)) + 1e-30f;
-  const float rr = __fadd_ru(r, e);
-  return __fmul_ru(__fmul_ru(rr, rr), 1.000004f);
-}
-
-__device__ __forceinline__ float sor_box_d2f(const float4 lo, const float4 hi, float fx, float fy, float fz) {
-  const float dx = fmaxf(fmaxf(lo.x - fx, fx - hi.x), 0.f), dy = fmaxf(fmaxf(lo.y - fy, fy - hi.y), 0.f),
-              dz = fmaxf(fmaxf(lo.z - fz, fz - hi.z), 0.f);
-  return dx * dx + dy * dy + dz * dz;
-}
-
 __device__ __forceinline__ bool sor_box_hits(const SorBox& b, const float4 qlo, const float4 qhi) {
   return b.lo.x <= qhi.x && b.hi.x >= qlo.x && b.lo.y <= qhi.y && b.hi.y >= qlo.y && b.lo.z <= qhi.z && b.hi.z >= qlo.z;
 }
 
-// Shell of a neighbour with slo < d2 <= shi.  The shells are bounded by the EXACT doubles e_b = fl(slo + (b + 1) * w),
-// b < 15, and e_15 = shi, so that "all neighbours up to shell b" is the plain comparison d2 <= e_b of the next pass.
-__device__ __forceinline__ double sor_edge(int b, double slo, double w, double shi) {
-  return b >= SOR_NBIN - 1 ? shi : __fma_rn((double)(b + 1), w, slo);
-}
-__device__ __forceinline__ int sor_shell(double d2, double slo, double w, double invw, double shi) {
-  int b = __double2int_rz(__dmul_rn(__dsub_rn(d2, slo), invw));
-  b = b < 0 ? 0 : (b > SOR_NBIN - 1 ? SOR_NBIN - 1 : b);
-  if (b < SOR_NBIN - 1 && d2 > sor_edge(b, slo, w, shi)) b++;
-  else if (b > 0 && d2 <= sor_edge(b - 1, slo, w, shi)) b--;
-  return b;
-}
-
-// search box of the walking lanes: union of their balls, rounded outwards
-__device__ __forceinline__ void sor_search_box(const SorLane& L, float4& qlo, float4& qhi) {
-  const unsigned full = 0xffffffffu;
-  qlo = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
-  qhi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
-  if (L.walk) {
-    const double r = __dsqrt_ru(L.shi) * (1.0 + 1e-12);
-    qlo = make_float4(__double2float_rd(L.px - r), __double2float_rd(L.py - r), __double2float_rd(L.pz - r), 0.f);
-    qhi = make_float4(__double2float_ru(L.px + r), __double2float_ru(L.py + r), __double2float_ru(L.pz + r), 0.f);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    qlo.x = fminf(qlo.x, __shfl_xor_sync(full, qlo.x, o)); qlo.y = fminf(qlo.y, __shfl_xor_sync(full, qlo.y, o));
-    qlo.z = fminf(qlo.z, __shfl_xor_sync(full, qlo.z, o)); qhi.x = fmaxf(qhi.x, __shfl_xor_sync(full, qhi.x, o));
-    qhi.y = fmaxf(qhi.y, __shfl_xor_sync(full, qhi.y, o)); qhi.z = fmaxf(qhi.z, __shfl_xor_sync(full, qhi.z, o));
-  }
-}
-
-// Stage the chunk's groups (ids ascending in w.grp[0..ng)) with ONE bulk copy per run of consecutive ids, wait for the
-// bytes, let every lane mark the staged groups whose box can hold a point within its bound, flatten the (lane, group)
-// marks of the whole warp into one work list and spread it evenly over the lanes: each lane evaluates the 8 exact
-// squared distances of its (owner, group) items against the OWNER's query and appends the neighbours (d2 <= shi) to
-// the owner's column; beyond LCAP entries only the shell counts are kept.
-template <int LCAP>
-__device__ __forceinline__ void sor_consume(const SorTree& T, SorWarpSmem<LCAP>& w, int ng, unsigned& phase, const SorLane& L, int lane) {
-  const unsigned full = 0xffffffffu;
-  // ---- runs of consecutive groups -> bulk copies
-  const int g = lane < ng ? w.grp[lane] : -2;
-  const bool st = lane < ng && (lane == 0 || w.grp[lane - 1] + 1 != g);
-  const unsigned starts = __ballot_sync(full, st);
-  if (lane == 0) dfu_mbar_arrive_expect_tx(&w.mbar, (uint32_t)ng * (uint32_t)sizeof(SorGroup));
-  __syncwarp();
-  if (st) {
-    const unsigned later = lane < 31 ? (starts >> (lane + 1)) : 0u;
-    const int len = later ? __ffs((int)later) : ng - lane;
-    dfu_bulk_g2s(w.stage + lane, T.rec + g, (uint32_t)len * (uint32_t)sizeof(SorGroup), &w.mbar);
-  }
-  dfu_mbar_wait(&w.mbar, phase);
-  phase ^= 1u;
-  // ---- the lane's own groups
-  unsigned m = 0u;
-  if (L.flim >= 0.f) {
-    for (int gi = 0; gi < ng; gi++) {
-      const SorBox b = w.stage[gi].box;                  // broadcast
-      if (sor_box_d2f(b.lo, b.hi, L.fx, L.fy, L.fz) <= L.flim) m |= 1u << gi;
-    }
-  }
-  // ---- work list of the warp
-  int off = __popc(m);
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(full, off, o);
-    if (lane >= o) off += v;
-  }
-  const int P = __shfl_sync(full, off, 31);
-  off -= __popc(m);
-#ifdef SOR_STATS
-  if (lane == 0) { atomicAdd(&g_sor_stats[0], 1ull); atomicAdd(&g_sor_stats[1], (unsigned long long)P); atomicAdd(&g_sor_stats[3], (unsigned long long)ng); }
-#endif
-  while (m) {
-    const int gi = __ffs((int)m) - 1;
-    m &= m - 1;
-    w.pair[off++] = (unsigned short)((lane << 8) | gi);
-  }
-  __syncwarp();
-  // uniform trip count + a barrier per iteration: without it the lanes that leave the neighbour loop early run ahead
-  // into the next item on their own and the warp splinters (measured: 6 of 32 lanes per instruction)
-  for (int e0 = 0; e0 < P; e0 += 32, __syncwarp()) {
-    const int e = e0 + lane;
-    if (e >= P) continue;
-    const int pr = w.pair[e], o = pr >> 8;
-    const SorGroup& G = w.stage[pr & 255];
-    const double qx = w.opx[o], qy = w.opy[o], qz = w.opz[o], shi = w.oshi[o];
-    double d2v[8];
-#pragma unroll
-    for (int q = 0; q < 8; q++) {
-      const int j = (q + lane) & 7;                      // rotated: the lanes spread over the banks
-      d2v[q] = sor_d2(G.x[j], G.y[j], G.z[j], qx, qy, qz);
-    }
-    unsigned hm = 0u;
-#pragma unroll
-    for (int q = 0; q < 8; q++) hm |= (d2v[q] <= shi) ? (1u << q) : 0u;
-    if (hm) {
-      // the neighbours of the item take consecutive slots of the owner's column: one atomic per item
-      int slot = atomicAdd(&w.nl[o], __popc(hm));
-      while (hm) {
-        const int q = __ffs((int)hm) - 1;
-        hm &= hm - 1;
-        // d2v[q] through a select tree (a dynamic index would put the array in local memory)
-        const double a0 = (q & 1) ? d2v[1] : d2v[0], a1 = (q & 1) ? d2v[3] : d2v[2], a2 = (q & 1) ? d2v[5] : d2v[4],
-                     a3 = (q & 1) ? d2v[7] : d2v[6];
-        const double b0 = (q & 2) ? a1 : a0, b1 = (q & 2) ? a3 : a2;
-        const double d2 = (q & 4) ? b1 : b0;
-        if (slot < LCAP) {
-          w.list[slot][o] = d2;
-        } else {
-          const double slo = w.oslo[o];
-          const int b = d2 <= slo ? SOR_NBIN : sor_shell(d2, fmax(slo, 0.0), w.ow[o], w.oinvw[o], shi);
-          atomicAdd(&w.cnt[b][o], 1u);
-        }
-        slot++;
-      }
-    }
-  }
-  __syncwarp();
-}
-
-// One pass over the candidates of the tile: the level-1 frontier w.front[fsel][0..nf) is expanded 4 nodes (32 groups)
-// at a time against the search box of the walking lanes; every 32 surviving groups are consumed.
-template <int LCAP>
-__device__ __forceinline__ void sor_pass(const SorTree& T, SorWarpSmem<LCAP>& w, int fsel, int nf, int gfirst, int glast, unsigned& phase,
-                                         const SorLane& L, int lane) {
-  const unsigned full = 0xffffffffu;
-  float4 qlo, qhi;
-  sor_search_box(L, qlo, qhi);
-  int ng = 0;
-  const int NPS = SOR_CG >= 32 ? 4 : SOR_CG / 8;      // level-1 nodes expanded per step: at most SOR_CG groups
-  for (int f0 = 0; f0 < nf || ng > 0; f0 += NPS) {
-    const int fi = f0 + (lane >> 3);
-    bool hit = false;
-    int g = -1;
-    if (fi < nf && (lane >> 3) < NPS) {
-      g = w.front[fsel][fi] * 8 + (lane & 7);
-      if (g >= gfirst && g <= glast) hit = sor_box_hits(T.lv[0][g], qlo, qhi);
-    }
-    const unsigned bm = __ballot_sync(full, hit);
-    // fill the chunk up to SOR_CG groups; the rest of this batch opens the next chunk
-    const int room = SOR_CG - ng, nb = __popc(bm);
-    const int rank = __popc(bm & ((1u << lane) - 1u));
-    if (hit && rank < room) w.grp[ng + rank] = g;
-    __syncwarp();
-    const int filled = nb < room ? ng + nb : SOR_CG;
-    if (filled == SOR_CG || (f0 + NPS >= nf && filled > 0)) {
-      sor_consume<LCAP>(T, w, filled, phase, L, lane);
-      if (hit && rank >= room) w.grp[rank - room] = g;
-      ng = nb > room ? nb - room : 0;
-      __syncwarp();
-    } else {
-      ng = filled;
-    }
-  }
-}
-
-// cause: 0 far bound, 1 search box meets too many nodes, 2 ties in the k-th shell
+// cause: 0 far bound, 1 search box meets too many nodes, 2 more equal distances than the column holds
 __device__ __forceinline__ void sor_defer(bool want, int64_t t, int32_t* __restrict__ todo, int32_t* __restrict__ ntodo, int cause, int lane) {
   const unsigned m = __ballot_sync(0xffffffffu, want);
   if (!m) return;
@@ -501,269 +295,8 @@ __device__ __forceinline__ void sor_defer(bool want, int64_t t, int32_t* __restr
   if (want) todo[base + __popc(m & ((1u << lane) - 1u))] = (int32_t)t;
 }
 
-template <int KCAP, int LCAP>
-__global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_tile(SorTree T, double* __restrict__ mean_out, int32_t* __restrict__ todo,
-                                                             int32_t* __restrict__ ntodo, int32_t* __restrict__ tile_ctr) {
-  extern __shared__ __align__(128) unsigned char sor_smem_raw[];
-  SorWarpSmem<LCAP>& w = reinterpret_cast<SorWarpSmem<LCAP>*>(sor_smem_raw)[threadIdx.x >> 5];
-  const int lane = threadIdx.x & 31;
-  const unsigned full = 0xffffffffu;
-  const double inf = __longlong_as_double(0x7ff0000000000000ll);
-  if (lane == 0) dfu_mbar_init(&w.mbar, 1);
-  __syncwarp();
-  unsigned phase = 0;
-  const int W = T.k > 32 ? T.k : 32;                       // curve window of step 1 (staged: +-32 positions)
-  for (;;) {
-    int tile = 0;
-    if (lane == 0) tile = atomicAdd(tile_ctr, 1);
-    tile = __shfl_sync(full, tile, 0);
-    if (tile >= T.ntiles) break;
-    const int64_t t0 = (int64_t)tile * 32, t = t0 + lane;
-    const int s = sor_seg_of(T.poff, T.nseg, t0);
-    const int64_t ps = T.poff[s], pe = T.poff[s + 1];
-    const int ns = (int)(T.seg_off[s + 1] - T.seg_off[s]);
-    const int kk = ns < T.k ? ns : T.k;
-    SorLane L;
-    const int orig = T.spi[t];
-    L.active = orig >= 0;
-    // ---- 1. bound from the curve neighbours: positions t-32 .. t+32 of the segment, staged from [t0-32, t0+64)
-    {
-      const int64_t a = t0 - 32 > ps ? t0 - 32 : ps, b = t0 + 64 < pe ? t0 + 64 : pe;
-      const int off = (int)(a - (t0 - 32));              // 0 or 32
-      if (lane == 0) {
-        const uint32_t bytes = (uint32_t)((b - a) >> 3) * (uint32_t)sizeof(SorGroup);
-        dfu_mbar_arrive_expect_tx(&w.mbar, bytes);
-        dfu_bulk_g2s(w.stage + (off >> 3), T.rec + (a >> 3), bytes, &w.mbar);
-      }
-      dfu_mbar_wait(&w.mbar, phase);
-      phase ^= 1u;
-      {
-        const int p = 32 + lane;
-        L.px = w.stage[p >> 3].x[p & 7]; L.py = w.stage[p >> 3].y[p & 7]; L.pz = w.stage[p >> 3].z[p & 7];
-      }
-      float best[KCAP];
-#pragma unroll
-      for (int i = 0; i < KCAP; i++) best[i] = INFINITY;
-      const int last = (int)(b - (t0 - 32)) - 1;          // last staged position
-      const int jlo = off - (32 + lane) > -W ? off - (32 + lane) : -W;
-      const int jhi = last - (32 + lane) < W ? last - (32 + lane) : W;
-#pragma unroll 4
-      for (int j = jlo; j <= jhi; j++) {                   // unrolled: the insertions of consecutive points pipeline
-        const int p = 32 + lane + j;
-        const SorGroup& G = w.stage[p >> 3];
-        float v = __double2float_ru(sor_d2(G.x[p & 7], G.y[p & 7], G.z[p & 7], L.px, L.py, L.pz));   // pads: +inf
-#pragma unroll
-        for (int i = 0; i < KCAP; i++) {
-          const float lo = fminf(best[i], v);
-          v = fmaxf(best[i], v);
-          best[i] = lo;
-        }
-      }
-      // best[] ascends: the kk-th smallest is the largest of the first kk (a select chain keeps best[] in registers)
-      float kth = 0.f;
-#pragma unroll
-      for (int i = 0; i < KCAP; i++) kth = fmaxf(kth, i < kk ? best[i] : 0.f);
-      L.shi = (double)kth;
-      L.slo = -1.0;
-      __syncwarp();
-    }
-    // ---- 1b. lanes whose bound is far above the tile's median are handled one by one
-    {
-      float v = L.active ? (float)L.shi : INFINITY;
-#pragma unroll
-      for (int k2 = 2; k2 <= 32; k2 <<= 1)
-#pragma unroll
-        for (int j = k2 >> 1; j > 0; j >>= 1) {
-          const float o = __shfl_xor_sync(full, v, j);
-          const bool up = (lane & k2) == 0 || k2 == 32, lower = (lane & j) == 0;
-          v = (lower == up) ? fminf(v, o) : fmaxf(v, o);
-        }
-      const int nv = __popc(__ballot_sync(full, L.active));
-      const float med = __shfl_sync(full, v, nv > 0 ? nv >> 1 : 0);
-      const bool far = L.active && (!(L.shi < (double)INFINITY) || (float)L.shi > SOR_DEFER * med);
-      sor_defer(far, t, todo, ntodo, 0, lane);
-      if (far) L.active = false;
-    }
-    if (!__any_sync(full, L.active)) continue;
-    L.walk = L.active;
-    L.fx = (float)L.px; L.fy = (float)L.py; L.fz = (float)L.pz;
-    L.flim = L.walk ? sor_lane_flim(L.shi, L.fx, L.fy, L.fz) : -1.f;
-    w.opx[lane] = L.px; w.opy[lane] = L.py; w.opz[lane] = L.pz;
-    // ---- 2. pyramid descent to the level-1 nodes that meet the tile's search box
-    const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
-    int fsel = 0, nf = 0;
-    {
-      float4 qlo, qhi;
-      sor_search_box(L, qlo, qhi);
-      int lev = 1;
-      while (lev < T.nlev - 1 && ((glast >> (3 * lev)) - (gfirst >> (3 * lev)) + 1) > 32) lev++;
-      const int nfirst = gfirst >> (3 * lev), nlast = glast >> (3 * lev);
-      bool overflow = false;
-      for (int b0 = nfirst; b0 <= nlast; b0 += 32) {       // more than 32 nodes only at the top level
-        const int node = b0 + lane;
-        const bool hit = node <= nlast && sor_box_hits(T.lv[lev][node], qlo, qhi);
-        const unsigned bm = __ballot_sync(full, hit);
-        if (nf + __popc(bm) > SOR_FRONT) { overflow = true; break; }
-        if (hit) w.front[0][nf + __popc(bm & ((1u << lane) - 1u))] = node;
-        nf += __popc(bm);
-      }
-      __syncwarp();
-      while (!overflow && lev > 1) {
-        const int cl = lev - 1, cfirst = gfirst >> (3 * cl), clast = glast >> (3 * cl);
-        int nn = 0;
-        for (int f0 = 0; f0 < nf; f0 += 4) {
-          const int fi = f0 + (lane >> 3);
-          bool hit = false;
-          int c = -1;
-          if (fi < nf) {
-            c = w.front[fsel][fi] * 8 + (lane & 7);
-            if (c >= cfirst && c <= clast) hit = sor_box_hits(T.lv[cl][c], qlo, qhi);
-          }
-          const unsigned bm = __ballot_sync(full, hit);
-          if (nn + __popc(bm) > SOR_FRONT) { overflow = true; break; }
-          if (hit) w.front[fsel ^ 1][nn + __popc(bm & ((1u << lane) - 1u))] = c;
-          nn += __popc(bm);
-        }
-        __syncwarp();
-        fsel ^= 1; nf = nn; lev = cl;
-      }
-      if (overflow) {          // a search box that meets too many nodes (curve jump inside the tile): one by one
-        sor_defer(L.active, t, todo, ntodo, 1, lane);
-        continue;
-      }
-    }
-    // ---- 3. passes: every neighbour with d2 <= shi goes to the lane's column; a lane that finds more than LCAP
-    //         narrows (slo, shi] to the shell that holds its k-th neighbour and walks again
-    int nl = 0;
-    for (int pass = 0; pass < 40; pass++) {
-      if (L.walk) {
-        const double wd = (L.shi - fmax(L.slo, 0.0)) * (1.0 / SOR_NBIN);
-        w.oshi[lane] = L.shi; w.oslo[lane] = L.slo; w.ow[lane] = wd; w.oinvw[lane] = wd > 0.0 ? 1.0 / wd : 0.0;
-#pragma unroll
-        for (int b = 0; b <= SOR_NBIN; b++) w.cnt[b][lane] = 0u;
-      }
-      w.nl[lane] = 0;
-      __syncwarp();
-      sor_pass<LCAP>(T, w, fsel, nf, gfirst, glast, phase, L, lane);
-#ifdef SOR_STATS
-      if (lane == 0) { atomicAdd(&g_sor_stats[2], 1ull); atomicAdd(&g_sor_stats[4], (unsigned long long)nf); }
-      atomicAdd(&g_sor_stats[5], (unsigned long long)(L.walk ? 1 : 0));
-#endif
-      bool ties = false;
-      if (L.walk) {
-        nl = w.nl[lane];
-        L.walk = false;
-        L.flim = -1.f;
-        if (nl > LCAP) {
-          // the shell counts so far miss the LCAP neighbours that went into the column
-          const double slo = fmax(L.slo, 0.0), wd = w.ow[lane], invw = w.oinvw[lane];
-          for (int j = 0; j < LCAP; j++) {
-            const double d2 = w.list[j][lane];
-            w.cnt[d2 <= L.slo ? SOR_NBIN : sor_shell(d2, slo, wd, invw, L.shi)][lane] += 1u;
-          }
-          int cum = (int)w.cnt[SOR_NBIN][lane], bs = -1;
-#pragma unroll
-          for (int b = 0; b < SOR_NBIN; b++) {
-            if (bs < 0) {
-              cum += (int)w.cnt[b][lane];
-              if (cum >= kk) bs = b;
-            }
-          }
-          // neighbours up to shell bs: d2 <= e_bs, at least kk of them; those below e_(bs-1) are fewer than kk
-          const double nhi = bs < 0 ? L.shi : sor_edge(bs, slo, wd, L.shi);
-          const double nlo = bs <= 0 ? L.slo : sor_edge(bs - 1, slo, wd, L.shi);
-          ties = bs < 0 || !(nhi - fmax(nlo, 0.0) < L.shi - slo);       // no progress: equal distances
-          if (!ties) {
-            L.shi = nhi; L.slo = nlo;
-            L.walk = true;
-            L.flim = sor_lane_flim(L.shi, L.fx, L.fy, L.fz);
-          }
-        }
-      }
-      __syncwarp();
-      sor_defer(ties, t, todo, ntodo, 2, lane);
-      if (ties) L.active = false;
-      if (!__any_sync(full, L.walk)) break;
-    }
-    // ---- 4. the k' smallest in ascending order; sequential sum of square roots.
-    // The order is found on 32-bit keys: key = (T << 6) | slot with T = trunc(d2 * (2^26 - 2) / shi), a monotone
-    // non-decreasing map of d2 (every column entry is <= shi), so T_a < T_b implies d2_a < d2_b and ascending keys
-    // visit the column in ascending d2 except INSIDE a run of equal T.  Such a run is harmless when the doubles come
-    // out non-descending anyway (checked on the fly) and when no entry left out ties with the last one taken while
-    // being smaller (checked after the last round); a lane that fails a check redoes the selection on the doubles.
-    {
-      const bool fin = L.active && !L.walk;
-      const int nlf = fin ? nl : 0;
-      int nmax = nlf;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) nmax = max(nmax, __shfl_xor_sync(full, nmax, o));
-      nmax = (nmax + 3) & ~3;                  // <= LCAP (a multiple of 4)
-      const double sc = __ddiv_rn(67108862.0, L.shi);
-      for (int j = 0; j < nmax; j++) {
-        unsigned key = 0xffffffffu;
-        if (j < nlf) key = (__double2uint_rz(__dmul_rn(w.list[j][lane], sc)) << 6) | (unsigned)j;
-        w.key[j][lane] = key;
-      }
-      double acc = 0.0, prev = 0.0;
-      unsigned mlast = 0u;
-      bool redo = false;
-      for (int r = 0; r < kk; r++) {
-        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
-        for (int j = 0; j < nmax; j += 4) {
-          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
-          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
-        }
-        const unsigned m = min(min(m0, m1), min(m2, m3));
-        if (fin) {                              // nlf >= kk: m is a real key
-          const int slot = (int)(m & 63u);
-          const double d = w.list[slot][lane];
-          redo |= d < prev;
-          prev = d;
-          acc = __dadd_rn(acc, __dsqrt_rn(d));
-          w.key[slot][lane] = 0xffffffffu;
-          mlast = m;
-        }
-      }
-      // entries left out that share T with the last one taken
-      bool chk = fin && !redo;
-      while (__any_sync(full, chk)) {
-        unsigned m0 = 0xffffffffu, m1 = 0xffffffffu, m2 = 0xffffffffu, m3 = 0xffffffffu;
-        for (int j = 0; j < nmax; j += 4) {
-          m0 = min(m0, w.key[j][lane]); m1 = min(m1, w.key[j + 1][lane]);
-          m2 = min(m2, w.key[j + 2][lane]); m3 = min(m3, w.key[j + 3][lane]);
-        }
-        const unsigned m = min(min(m0, m1), min(m2, m3));
-        if (chk) {
-          if ((m >> 6) != (mlast >> 6)) chk = false;          // also the sentinel: T = 2^26 - 1 is never a real T
-          else if (w.list[m & 63u][lane] < prev) { redo = true; chk = false; }
-          else w.key[m & 63u][lane] = 0xffffffffu;
-        }
-      }
-      if (__any_sync(full, redo)) {              // rare: exact selection on the doubles (the column is intact)
-        const int nr = redo ? nlf : 0;
-        double acc2 = 0.0;
-        for (int r = 0; r < kk; r++) {
-          double b0 = inf;
-          int i0 = 0;
-          for (int j = 0; j < nr; j++) {
-            const double x = w.list[j][lane];
-            if (x < b0) { b0 = x; i0 = j; }
-          }
-          acc2 = __dadd_rn(acc2, __dsqrt_rn(b0));
-          if (redo) w.list[i0][lane] = inf;
-        }
-        if (redo) acc = acc2;
-      }
-      if (fin) mean_out[orig] = __ddiv_rn(acc, (double)kk);
-      __syncwarp();
-    }
-    sor_defer(L.active && L.walk, t, todo, ntodo, 2, lane);      // still narrowing after 40 passes: cannot happen
-    __syncwarp();
-  }
-}
-
 // ---------------------------------------------------------------- the sweep kernel (float32 screen, exact finish)
-// One warp per tile of 32 consecutive sorted queries, like k_sor_tile, but the candidates are SCREENED in float32:
+// One warp per tile of 32 consecutive sorted queries; the candidates are SCREENED in float32:
 // every lane sweeps every staged point (the point is a shared-memory broadcast, the arithmetic is 7 float
 // instructions, all 32 lanes busy, no atomics, no work list) and appends the points inside its own ball to its own
 // column as (float d2, sorted position).  When a column is about to fill, the warp tightens: each lane guesses a
@@ -1591,7 +1124,6 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
     if (k <= SOR_KFAST) {
       int grid = 148 * 16;
       if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
-#if SOR_SWEEP
       grid = 148 * 8;
       if (grid > (ntiles + SOR_WARPS - 1) / SOR_WARPS) grid = (ntiles + SOR_WARPS - 1) / SOR_WARPS;
       if (k <= 20) {
@@ -1605,17 +1137,6 @@ extern "C" int dfu_sor_filter(dfu_ctx* ctx, void* stream, const double* xyz, int
         DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_sweep<32, 64>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         k_sor_sweep<32, 64><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
       }
-#else
-      if (k <= 20) {
-        const size_t smem = sizeof(SorWarpSmem<SOR_LCAP20>) * SOR_WARPS;
-        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<20, SOR_LCAP20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_sor_tile<20, SOR_LCAP20><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
-      } else {
-        const size_t smem = sizeof(SorWarpSmem<64>) * SOR_WARPS;
-        DFU_CUDA(ctx, cudaFuncSetAttribute(k_sor_tile<32, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_sor_tile<32, 64><<<grid, SOR_WARPS * 32, smem, st>>>(T, mean, todo, scal + 1, scal + 2);
-      }
-#endif
       DFU_LAUNCH_CHECK(ctx);
       k_sor_single<<<grid_single, 128, 0, st>>>(T, todo, scal + 1, 0, mean);
       DFU_LAUNCH_CHECK(ctx);
