@@ -313,7 +313,7 @@ __device__ __forceinline__ void sor_defer(bool want, int64_t t, int32_t* __restr
 //   * a point with d2f <= X has d <= dmax(X), the positive root of (1 - 1e-6) d^2 - 4 delta d - (X + 4 delta^2) = 0,
 //     so k entries with d2f <= X prove that the k-th neighbour lies within B' = dmax(X)^2.
 #ifndef SOR_SCG
-#define SOR_SCG 64          /* float groups staged per chunk of the sweep */
+#define SOR_SCG 64          /* float groups staged per chunk of the sweep (32: one more CTA per SM, measured no faster) */
 #endif
 #ifndef SOR_SLCAP20
 #define SOR_SLCAP20 64      /* column entries per lane (k <= 20) */
@@ -324,7 +324,7 @@ struct __align__(128) SorSweepSmem {
   union {
     struct {
       SorGroupF fst[SOR_SCG];                               // staged float groups (step 1: the curve window)
-      int front[2][SOR_FRONT];                              // pyramid frontiers (ping-pong)
+      int front[SOR_FRONT];                                 // level-1 frontier (the descent's second buffer is fst)
       int grp[SOR_SCG + 64];                                // group ids that passed the box test (a step adds up to 64)
     };
     unsigned key[LCAP][32];                                 // step 4: order keys of the columns
@@ -591,12 +591,16 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
     L.thr = L.active ? sor_screen(L.B, er) : -1.f;
     // ---- 2. pyramid descent to the level-1 nodes that meet the tile's search box
     const int gfirst = (int)(ps >> 3), glast = (int)(pe >> 3) - 1;
-    int fsel = 0, nf = 0;
+    int nf = 0;
     float4 qlo, qhi;
     sor_sweep_box(L, qlo, qhi);
     {
       int lev = 1;
       while (lev < T.nlev - 1 && ((glast >> (3 * lev)) - (gfirst >> (3 * lev)) + 1) > 32) lev++;
+      // ping-pong between the frontier array and the (still idle) staging buffer, arranged to END in the frontier array
+      int* const fb0 = w.front; int* const fb1 = reinterpret_cast<int*>(w.fst);
+      static_assert(sizeof(w.fst) >= sizeof(w.front), "the staging buffer doubles as the second frontier");
+      int fsel = (lev - 1) & 1;
       const int nfirst = gfirst >> (3 * lev), nlast = glast >> (3 * lev);
       bool overflow = false;
       for (int b0 = nfirst; b0 <= nlast; b0 += 32) {
@@ -604,7 +608,7 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
         const bool hit = node <= nlast && sor_box_hits(T.lv[lev][node], qlo, qhi);
         const unsigned bm = __ballot_sync(full, hit);
         if (nf + __popc(bm) > SOR_FRONT) { overflow = true; break; }
-        if (hit) w.front[0][nf + __popc(bm & ((1u << lane) - 1u))] = node;
+        if (hit) (fsel ? fb1 : fb0)[nf + __popc(bm & ((1u << lane) - 1u))] = node;
         nf += __popc(bm);
       }
       __syncwarp();
@@ -616,12 +620,12 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
           bool hit = false;
           int c = -1;
           if (fi < nf) {
-            c = w.front[fsel][fi] * 8 + (lane & 7);
+            c = (fsel ? fb1 : fb0)[fi] * 8 + (lane & 7);
             if (c >= cfirst && c <= clast) hit = sor_box_hits(T.lv[cl][c], qlo, qhi);
           }
           const unsigned bm = __ballot_sync(full, hit);
           if (nn + __popc(bm) > SOR_FRONT) { overflow = true; break; }
-          if (hit) w.front[fsel ^ 1][nn + __popc(bm & ((1u << lane) - 1u))] = c;
+          if (hit) (fsel ? fb0 : fb1)[nn + __popc(bm & ((1u << lane) - 1u))] = c;
           nn += __popc(bm);
         }
         __syncwarp();
@@ -641,7 +645,7 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
       const int own = (int)(t0 >> 6);
       int m = 0;                                            // frontier nodes below the tile's own
       for (int f0 = 0; f0 < nf; f0 += 32)
-        m += __popc(__ballot_sync(full, f0 + lane < nf && w.front[fsel][f0 + lane] < own));
+        m += __popc(__ballot_sync(full, f0 + lane < nf && w.front[f0 + lane] < own));
       const int nu = nf - m, nd = m, nalt = 2 * (nu < nd ? nu : nd);
       const int nsteps = (nf + 7) >> 3;
       int ng = 0;
@@ -656,7 +660,7 @@ __global__ void __launch_bounds__(SOR_WARPS * 32) k_sor_sweep(SorTree T, double*
           int g = -1;
           if (i < nf) {
             const int fi = i < nalt ? ((i & 1) ? m - 1 - (i >> 1) : m + (i >> 1)) : (nu > nd ? m + (i - nd) : m - 1 - (i - nu));
-            g = w.front[fsel][fi] * 8 + (lane & 7);
+            g = w.front[fi] * 8 + (lane & 7);
             if (g < gfirst || g > glast) g = -1;
           }
           if (h == 0) { ga = g; if (g >= 0) bxa = T.lv[0][g]; } else { gb = g; if (g >= 0) bxb = T.lv[0][g]; }
