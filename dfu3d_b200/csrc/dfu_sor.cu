@@ -50,7 +50,9 @@
 #define SOR_FRONT 384       /* level-1 frontier capacity per tile */
 #endif
 #define SOR_MAXLEV 10
+#ifndef SOR_DEFER
 #define SOR_DEFER 9.0f      /* lanes whose squared bound exceeds 9 x the tile median go to k_sor_single */
+#endif
 enum { SO_SEGOFF = 170, SO_POFF, SO_BOX, SO_KEY, SO_IDX, SO_SKEY, SO_SIDX, SO_REC, SO_TMP, SO_SPI,
        SO_MEAN, SO_PART, SO_SEGSTAT, SO_SEGCH, SO_PYR, SO_TODO, SO_SCAL, SO_FREC };
 
