@@ -37,15 +37,40 @@ __global__ void __launch_bounds__(G_THREADS) k_grid_bbox(const double* __restric
       bx = ox < bx ? ox : bx; by = oy < by ? oy : by; bz = oz < bz ? oz : bz;
       sv = os > sv ? os : sv;
     }
-    if ((threadIdx.x & 31) == 0 && sv >= 0) {
-      atomicMin(segmin + 3 * sv + 0, bx);
-      atomicMin(segmin + 3 * sv + 1, by);
-      atomicMin(segmin + 3 * sv + 2, bz);
-    }
+    s = sv;
   } else if (ok) {
     atomicMin(segmin + 3 * s + 0, bx);
     atomicMin(segmin + 3 * s + 1, by);
     atomicMin(segmin + 3 * s + 2, bz);
+  }
+  // one atomic per axis and BLOCK when all its warps sit in one segment (a single segment of millions of points would
+  // otherwise send three atomics per warp to the same three words: 258 us per 4 M points, 8 % issue utilisation)
+  __shared__ unsigned long long shv[G_THREADS / 32][3];
+  __shared__ int shs[G_THREADS / 32];
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) {
+    shs[w] = uniform ? s : -2;                               // -1: nothing to add, -2: handled above
+    shv[w][0] = bx; shv[w][1] = by; shv[w][2] = bz;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    int sb = -1;
+    bool same = true;
+    for (int k = 0; k < G_THREADS / 32; k++) {
+      if (shs[k] == -1) continue;
+      if (shs[k] == -2 || (sb >= 0 && shs[k] != sb)) same = false;
+      sb = shs[k] >= 0 ? shs[k] : sb;
+    }
+    if (same && sb >= 0) {
+      unsigned long long v = ~0ull;
+      for (int k = 0; k < G_THREADS / 32; k++)
+        if (shs[k] >= 0 && shv[k][a] < v) v = shv[k][a];
+      atomicMin(segmin + 3 * sb + a, v);
+    } else {
+      for (int k = 0; k < G_THREADS / 32; k++)
+        if (shs[k] >= 0) atomicMin(segmin + 3 * shs[k] + a, shv[k][a]);
+    }
   }
 }
 
