@@ -127,6 +127,11 @@ void* dfu_pinned(dfu_ctx* ctx, size_t bytes);
 
 // exclusive sum of n int32 -> int64 offsets (n+1 outputs, last = total), on `stream`
 int dfu_exclusive_sum_i32(dfu_ctx* ctx, cudaStream_t stream, const int32_t* in, int64_t* out, int64_t n);
+// Small host -> device upload that does NOT use a copy engine: a kernel reads the words from the context's pinned buffer
+// over PCIe.  A copy engine keeps serving the stream that feeds it: behind another stream's bulk upload (the next frame
+// group of FusionPipeline.run_host) a 90 KB cudaMemcpyAsync from pinned memory waited until that upload had finished
+// (measured: 42 ms instead of 4 ms for the instance stage).  src must lie inside dfu_pinned() memory, bytes % 4 == 0.
+int dfu_upload_pinned(dfu_ctx* ctx, cudaStream_t stream, void* dst_dev, const void* src_pinned, size_t bytes);
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ unsigned long long dfu_order_f64(double v) {

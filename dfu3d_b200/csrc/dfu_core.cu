@@ -48,6 +48,22 @@ void* dfu_pinned(dfu_ctx* ctx, size_t bytes) {
   return ctx->pinned;
 }
 
+__global__ void __launch_bounds__(256) k_upload_words(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) dst[i] = src[i];
+}
+
+int dfu_upload_pinned(dfu_ctx* ctx, cudaStream_t stream, void* dst_dev, const void* src_pinned, size_t bytes) {
+  if (bytes == 0) return DFU_OK;
+  if (bytes & 3) return dfu_set_err(ctx, DFU_ERR_ARG, "dfu_upload_pinned: %zu bytes", bytes);
+  const void* dsrc = src_pinned;          // unified addressing: cudaMallocHost memory has one address on host and device
+  const size_t n = bytes >> 2;
+  unsigned nb = (unsigned)((n + 255) / 256);
+  if (nb > 296) nb = 296;
+  k_upload_words<<<nb, 256, 0, stream>>>((uint32_t*)dst_dev, (const uint32_t*)dsrc, n);
+  DFU_LAUNCH_CHECK(ctx);
+  return DFU_OK;
+}
+
 struct I32ToI64 {
   __host__ __device__ int64_t operator()(const int32_t& v) const { return (int64_t)v; }
 };

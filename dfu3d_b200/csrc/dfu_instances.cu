@@ -471,10 +471,12 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   DFU_SLOT(ctx, gprm, double*, IS_GPRM, (size_t)G * 24);
   DFU_SLOT(ctx, idev, InstDev*, IS_IDEV, (size_t)G * sizeof(InstDev));
   DFU_SLOT(ctx, angles, double*, IS_ANGLES, (size_t)na * 16);
-  DFU_CUDA(ctx, cudaMemcpyAsync(prm, sp_h, (size_t)nseg * sizeof(SegPrm), cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(gprm, g_h, (size_t)G * 24, cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(idev, id_h, (size_t)G * sizeof(InstDev), cudaMemcpyHostToDevice, st));
-  DFU_CUDA(ctx, cudaMemcpyAsync(angles, ang_h, (size_t)na * 16, cudaMemcpyHostToDevice, st));
+  // by kernel, not by copy engine: the engine may be busy with another stream's bulk upload for tens of milliseconds
+  int urc;
+  if ((urc = dfu_upload_pinned(ctx, st, prm, sp_h, (size_t)nseg * sizeof(SegPrm)))) return urc;
+  if ((urc = dfu_upload_pinned(ctx, st, gprm, g_h, (size_t)G * 24))) return urc;
+  if ((urc = dfu_upload_pinned(ctx, st, idev, id_h, (size_t)G * sizeof(InstDev)))) return urc;
+  if ((urc = dfu_upload_pinned(ctx, st, angles, ang_h, (size_t)na * 16))) return urc;
   // ---- radius filters, gate, fuse
   DFU_SLOT(ctx, keep, uint8_t*, IS_KEEP, NP);
   DFU_SLOT(ctx, ract, uint8_t*, IS_RACT, NP);

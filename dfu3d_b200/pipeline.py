@@ -11,6 +11,7 @@ import math
 from dataclasses import dataclass, field
 
 import os
+import time
 
 import numpy as np
 import torch
@@ -468,8 +469,12 @@ def _chunk_metas(hb, nchunk):
     return out
 
 
-def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
+def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4, prefetch=None):
     """The end-to-end call: pinned host buffers in, cloud + boxes back on the host.
+
+    prefetch: the HostBatch of the NEXT call (a sweep over a dataset knows it).  Its first group is put on the copy
+    stream while this call's last group is computed, read back, merged and formatted, so that the host->device link
+    does not idle between calls; the next call picks the group up (identity of the HostBatch object is checked).
 
     The batch is cut frame-wise into `chunks` groups that flow through three streams: host->device copies of group
     i+1 (copy stream) overlap the kernels of group i (the caller's stream) and the device->host copy of the cloud of
@@ -492,20 +497,35 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
             d = st[key] = torch.empty((int(h.shape[0] * 1.1) + 1,) + tuple(h.shape[1:]), dtype=h.dtype, device=dev)
         return d[:h.shape[0]]
 
-    done = {}
+    # groups are numbered through consecutive calls (base + i) so that the staging parity keeps alternating when a
+    # group of the next call is uploaded early; done[g]: the kernels of group g have finished with their staging buffers
+    pre = st.pop('prefetched', None)
+    if pre is not None and pre['hb'] is not hb:
+        pre['ev'].synchronize()
+        pre = None
+    base = pre['g'] if pre is not None else 0
+    done = {base - 1: pre['prev_done']} if pre is not None and pre['prev_done'] is not None else {}
 
-    def upload(i):
-        meta, (l0, l1), (v0, v1), (m0, m1) = metas[i]
-        par = i & 1
+    def upload(h, mts, j, g):
+        """Group j of batch h onto the copy stream; returns (device tensors, event).  The small parameter uploads of the
+        group being computed do not queue behind these copies: the library sends them by kernel (dfu_upload_pinned)."""
+        meta, (l0, l1), (v0, v1), (m0, m1) = mts[j]
+        par = g & 1
+        trace = st.get('trace')
+        srcs = (h.lidar[l0:l1], h.depth[v0:v1], h.image[v0:v1], h.masks[m0:m1] if h.labelmap is None else h.labelmap[v0:v1])
         with torch.cuda.stream(s_in):
-            if i - 2 in done:
-                s_in.wait_event(done[i - 2])          # the staging buffers of this parity are free again
-            srcs = (hb.lidar[l0:l1], hb.depth[v0:v1], hb.image[v0:v1], hb.masks[m0:m1] if hb.labelmap is None else hb.labelmap[v0:v1])
-            dst = [dbuf(n, par, h) for n, h in zip(('lidar', 'depth', 'image', 'masks' if hb.labelmap is None else 'packed'), srcs)]
-            for d, h in zip(dst, srcs):
-                d.copy_(h, non_blocking=True)
-            ev = torch.cuda.Event()
+            if g - 2 in done:
+                s_in.wait_event(done[g - 2])          # the staging buffers of this parity are free again
+            dst = [dbuf(n, par, x) for n, x in zip(('lidar', 'depth', 'image', 'masks' if h.labelmap is None else 'packed'), srcs)]
+            if trace is not None:
+                t0 = torch.cuda.Event(enable_timing=True)
+                t0.record(s_in)
+            for d, x in zip(dst, srcs):
+                d.copy_(x, non_blocking=True)
+            ev = torch.cuda.Event(enable_timing=trace is not None)
             ev.record(s_in)
+            if trace is not None:
+                trace.append((g, t0, ev, sum(x.numel() * x.element_size() for x in srcs)))
         return dst, ev
 
     # two pinned output buffers used alternately: the result of a call stays valid until the call after the next one
@@ -513,11 +533,22 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
     st['flip'] = st.get('flip', 0) ^ 1
     hkey = 'cloud_host%d' % st['flip']
     hc = st.get(hkey)
-    results, pending = [], upload(0)
+    results, pending = [], ((pre['dst'], pre['ev']) if pre is not None else upload(hb, metas, 0, base))
     row_base, rows_needed, d2h_ev = 0, 0, []
-    for i in range(len(metas)):
+    n_groups = len(metas)
+    for i in range(n_groups):
         dst, ev = pending
-        pending = upload(i + 1) if i + 1 < len(metas) else None
+        if i + 1 < n_groups:
+            pending = upload(hb, metas, i + 1, base + i + 1)
+        else:
+            pending = None
+            if prefetch is not None:
+                # first group of the next call: global group number base + n_groups; its parity was last used by group
+                # base + n_groups - 2, which has been computed (or is the group before this call's first)
+                nm = _chunk_metas(prefetch, int(os.environ.get('DFU3D_HOST_CHUNKS', chunks)))
+                g = base + n_groups
+                pdst, pev = upload(prefetch, nm, 0, g)
+                st['prefetched'] = {'hb': prefetch, 'dst': pdst, 'ev': pev, 'g': g & 1, 'prev_done': None}
         meta = metas[i][0]
         main.wait_event(ev)
         meta.labelmap = None
@@ -531,10 +562,16 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
             self.ctx.check(self.lib.dfu_widen_labelmap(self.ctx.h, self.ctx.stream, _lib.dptr(packed), packed.element_size(),
                                                        packed.numel(), _lib.dptr(lm)))
             meta.labelmap = lm
+        trace = st.get('trace')
+        if trace is not None:
+            c0 = torch.cuda.Event(enable_timing=True)
+            c0.record(main)
         res = self.run(meta, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines)
-        e = torch.cuda.Event()
+        e = torch.cuda.Event(enable_timing=trace is not None)
         e.record(main)
-        done[i] = e
+        done[base + i] = e
+        if trace is not None:
+            trace.append(('compute', base + i, c0, e, time.time()))
         n = int(res.cloud.shape[0])
         if hc is None or hc.dtype != res.cloud.dtype or hc.shape[0] < row_base + n:
             # first call (or a larger batch than ever seen): grow the pinned output, keeping what is already there
@@ -554,6 +591,8 @@ def _run_host(self, hb, cloud_dtype=torch.float16, want_lines=True, chunks=4):
             d2h_ev.append(x)
         results.append((res, row_base))
         row_base += n
+    if 'prefetched' in st:
+        st['prefetched']['prev_done'] = done.get(base + n_groups - 1)     # frees the other parity for the next call's group 1
     s_out.synchronize()
     main.synchronize()
     out = _merge_results(results, metas, want_lines)

@@ -212,6 +212,17 @@ def test_run_host_pipelined_equals_resident(chunks):
     snap = a.cloud_host.numpy().copy()
     b = pipe.run_host(hb, cloud_dtype=torch.float16, chunks=chunks)
     assert a.cloud_host.data_ptr() != b.cloud_host.data_ptr() and np.array_equal(a.cloud_host.numpy(), snap)
+    # a sweep: each call announces the next batch, whose first group is uploaded during this call's tail; a different
+    # batch than announced (here the compact one) discards the early upload
+    frs2 = [helpers.small_frame(s, 'nuscenes', scale=0.25, n_cams=2) for s in (7, 3)]
+    vb2 = pipeline.batch_from_frames(frs2, pipe.device)
+    ref2 = pipe.run(vb2, cloud_dtype=torch.float16)
+    hb2 = pipeline.HostBatch.from_device(vb2)
+    seq = [(hb, ref, hb2), (hb2, ref2, hb), (hb, ref, hb), (hb, ref, hb2), (hc, ref, None), (hb2, ref2, None)]
+    for h, want, nxt in seq:
+        r = pipe.run_host(h, cloud_dtype=torch.float16, chunks=chunks, prefetch=nxt)
+        assert np.array_equal(r.cloud_host.numpy(), want.cloud.cpu().numpy()) and np.array_equal(r.boxes, want.boxes)
+        assert r.label_lines == want.label_lines
 
 
 @pytest.mark.parametrize('parts', [2, 3])
