@@ -47,6 +47,8 @@ def gather_boxes(local_boxes, device=None, group=None):
     world = dist.get_world_size(group)
     backend = dist.get_backend(group)
     dev = torch.device('cpu') if backend == 'gloo' else (device or torch.device('cuda', torch.cuda.current_device()))
+    if backend != 'gloo':
+        return sort_boxes(_gather_one_collective(local, world, dev, group))
     cnt = torch.tensor([local.shape[0]], dtype=torch.int64, device=dev)
     cnts = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
     dist.all_gather(cnts, cnt, group=group)
@@ -59,6 +61,32 @@ def gather_boxes(local_boxes, device=None, group=None):
     dist.all_gather(bufs, pad, group=group)
     parts = [b[:c].cpu().numpy() for b, c in zip(bufs, counts)]
     return sort_boxes(np.concatenate(parts, 0))
+
+
+_CAP = {}
+
+
+def _gather_one_collective(local, world, dev, group):
+    """NCCL path: ONE all_gather_into_tensor of [count | records padded to a capacity every rank agrees on] and one
+    device->host copy (the list form needs two collectives, world + 1 host syncs for the counts and a copy per rank).
+    The capacity is remembered; a rank that holds more records than it makes every rank repeat with the larger size."""
+    n = int(local.shape[0])
+    cap = _CAP.get(id(group), 2048)
+    while True:
+        host = np.zeros((cap + 1, BOX_DOUBLES), np.float64)
+        host[0, 0] = n
+        m = min(n, cap)
+        host[1:1 + m] = local[:m]
+        buf = torch.from_numpy(host).to(dev)
+        out = torch.empty((world * (cap + 1), BOX_DOUBLES), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(out, buf, group=group)
+        h = out.cpu().numpy().reshape(world, cap + 1, BOX_DOUBLES)
+        counts = h[:, 0, 0].astype(np.int64)
+        if int(counts.max()) <= cap:
+            return np.concatenate([h[r, 1:1 + int(counts[r])] for r in range(world)], 0)
+        while cap < int(counts.max()):
+            cap *= 2
+        _CAP[id(group)] = cap
 
 
 def sort_boxes(boxes):
