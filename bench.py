@@ -324,10 +324,29 @@ def main():
     def finish(res):
         # the step delivers what depth2pointsrgbpm delivers: the label text of every box (formatted on the host) and, at
         # N > 1, the host-side gather of the pseudo-box lists (north star; dfu3d_b200/shard.py) -- both inside the timed region
-        if world > 1:
-            allb = shard.gather_boxes(shard.globalise(res.boxes, frame_of_view), device=dev)
-            gathered['boxes'] = int(allb.shape[0])
+        # The gather of step n runs on a helper thread while step n + 1 computes (it mostly WAITS for the slowest rank); it is
+        # joined before the next gather starts and before the timed region ends (drain), so every step's gather is inside it.
+        if world > 1 and not os.environ.get('DFU_DIAG_NO_GATHER'):       # diagnosis only: a line without the gather is not a bench line
+            drain()
+            boxes = shard.globalise(res.boxes, frame_of_view)
+
+            def job():
+                torch.cuda.set_device(local)
+                t0 = time.perf_counter()
+                allb = shard.gather_boxes(boxes, device=dev)
+                gathered['boxes'] = int(allb.shape[0])
+                gathered['seconds'] = gathered.get('seconds', 0.0) + time.perf_counter() - t0
+                gathered['calls'] = gathered.get('calls', 0) + 1
+            gathered['fut'] = gather_pool.submit(job)
         return res
+
+    import concurrent.futures
+    gather_pool = concurrent.futures.ThreadPoolExecutor(max_workers=1)
+
+    def drain():
+        f = gathered.pop('fut', None)
+        if f is not None:
+            f.result()
 
     def step_resident():
         # two frame groups in flight (own stream / context / host thread each): the host-side sizing between the stages of
@@ -360,6 +379,7 @@ def main():
                                     prefetch=host_c['hb'] if sweep['left'] > 0 else None))
 
     def barrier():
+        drain()                    # never two threads in a collective at once
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -375,6 +395,7 @@ def main():
         last = None
         for _ in range(steps):
             last = fn()
+        drain()
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -486,7 +507,10 @@ def main():
                 'ms_per_step': ms / a.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
                 'dtype': 'f64', 'data': 'synthetic', 'config': workload_config(a), 'e2e': e2e,
                 'gpu_launches': int(launches), 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
-                'kernels': kernels, 'batch': st, 'filters': filt, 'numa_node_rank0': numa}
+                'kernels': kernels, 'batch': st, 'filters': filt, 'numa_node_rank0': numa,
+                'box_gather': ({'records': gathered['boxes'], 'helper_thread_wall_ms_per_call': 1e3 * gathered.get('seconds', 0.0) / max(gathered.get('calls', 1), 1),
+                                'how': 'helper thread, overlapped with the next step, joined inside the timed region'}
+                               if world > 1 else None)}
         if json_fd is None:
             print(json.dumps(line))
         else:
