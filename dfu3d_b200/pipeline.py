@@ -232,6 +232,8 @@ class FusionPipeline(object):
 
     # ------------------------------------------------------------------ the pipeline
     def run(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=True, no_fov_cull=False):
+        if instances and self.cfg.instances and len(vb.n_inst) and max(vb.n_inst) > _lib.MAX_INSTANCES:
+            return self._run_wide(vb, cloud_dtype, want_lines, no_fov_cull)
         cfg = self.cfg
         V = len(vb.view_sweep)
         H, W = vb.depth.shape[1:3]
@@ -256,6 +258,46 @@ class FusionPipeline(object):
         if instances and cfg.instances:
             self.run_instances(vb, res, want_lines=want_lines)
         return res
+
+    def _run_wide(self, vb, cloud_dtype, want_lines, no_fov_cull):
+        """Views with more than 32 instances (the label word of a pixel holds 32; the reference keeps every SEEM instance,
+        vis_utils.py:218).  The reference treats the instances of a view one by one (my_loader.py:547-607), nothing couples
+        them, so such a view is run as ceil(n / 32) views that share its inputs and take 32 masks each; the cloud and the
+        counts are taken from the first of them, the box records get the original view number back."""
+        lim = _lib.MAX_INSTANCES
+        idx, n_inst, classes, boxes2d, first = [], [], [], [], []
+        for v, n in enumerate(vb.n_inst):
+            first.append(len(idx))
+            cls = np.asarray(vb.classes[v]).reshape(-1)
+            b2 = np.asarray(vb.boxes2d[v], np.float32).reshape(-1, 4)
+            for lo in range(0, max(int(n), 1), lim):
+                hi = min(int(n), lo + lim)
+                idx.append(v)
+                n_inst.append(hi - lo)
+                classes.append(cls[lo:hi])
+                boxes2d.append(b2[lo:hi])
+        sel = torch.as_tensor(idx, dtype=torch.int64, device=vb.depth.device)
+        vx = ViewBatch(lidar=vb.lidar, sweeps=vb.sweeps, view_sweep=[vb.view_sweep[v] for v in idx],
+                       calibs=[vb.calibs[v] for v in idx], planes=[vb.planes[v] for v in idx],
+                       depth=vb.depth.index_select(0, sel), image=vb.image.index_select(0, sel), masks=vb.masks,
+                       n_inst=n_inst, classes=classes, boxes2d=boxes2d, thing_classes=vb.thing_classes)
+        r = self.run(vx, cloud_dtype=cloud_dtype, instances=True, want_lines=want_lines, no_fov_cull=no_fov_cull)
+        V = len(vb.n_inst)
+        rows = [r.cloud[int(r.row_off[i]):int(r.row_off[i + 1])] for i in first]
+        row_off = np.zeros(V + 1, np.int64)
+        row_off[1:] = np.cumsum([int(x.shape[0]) for x in rows])
+        out = FusionResult(cloud=torch.cat(rows, 0) if rows else r.cloud[:0], row_off=row_off,
+                           counts_project=r.counts_project[first], counts_densify=r.counts_densify[first])
+        orig = np.asarray(idx, np.int64)
+        out.boxes = r.boxes.copy()
+        if out.boxes.shape[0]:
+            out.boxes[:, 0] = orig[out.boxes[:, 0].astype(np.int64)]
+        out.seg_counts, out.box2d = r.seg_counts, r.box2d
+        if r.label_lines is not None:
+            out.label_lines = [[] for _ in range(V)]
+            for i, lines in enumerate(r.label_lines):
+                out.label_lines[idx[i]].extend(lines)
+        return out
 
     def inst_params(self, vb):
         """dfu_inst_params of every instance of the batch (cached on the ViewBatch)."""

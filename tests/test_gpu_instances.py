@@ -225,6 +225,75 @@ def test_run_host_pipelined_equals_resident(chunks):
         assert r.label_lines == want.label_lines
 
 
+def test_more_than_32_instances_in_a_view():
+    """The reference keeps every instance (vis_utils.py:218, no cap) and treats them one by one; the label word of a pixel
+    holds 32, so a view with more is run as several views of 32 masks each.  Checked against the same instances run in
+    views of their own (the masks of the fullest view repeated until it holds more than 32, the other views unchanged) and, for the records
+    of the first repetition, against the oracle-checked plain run."""
+    frs = [helpers.small_frame(s, 'nuscenes', scale=0.25, n_cams=2) for s in (3, 4)]
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames(frs, pipe.device)
+    ref = pipe.run(vb, cloud_dtype=torch.float16)
+    inst_off = np.concatenate([[0], np.cumsum(vb.n_inst)])
+    wide_v = int(np.argmax(vb.n_inst))
+    n0 = int(vb.n_inst[wide_v])
+    assert n0 >= 2
+    rep = 32 // n0 + 2                                     # > 32 instances in that view
+    m0, m1 = int(inst_off[wide_v]), int(inst_off[wide_v + 1])
+    masks = torch.cat([vb.masks[:m0]] + [vb.masks[m0:m1]] * rep + [vb.masks[m1:]], 0).contiguous()
+    wb = pipeline.ViewBatch(lidar=vb.lidar, sweeps=vb.sweeps, view_sweep=vb.view_sweep, calibs=vb.calibs, planes=vb.planes,
+                            depth=vb.depth, image=vb.image, masks=masks,
+                            n_inst=[n * rep if v == wide_v else n for v, n in enumerate(vb.n_inst)],
+                            classes=[np.tile(c, rep) if v == wide_v else c for v, c in enumerate(vb.classes)],
+                            boxes2d=[np.tile(np.asarray(b).reshape(-1, 4), (rep, 1)) if v == wide_v else b for v, b in enumerate(vb.boxes2d)],
+                            thing_classes=vb.thing_classes)
+    assert max(wb.n_inst) > 32
+    res = pipe.run(wb, cloud_dtype=torch.float16)
+    # the cloud and the per-view counts do not depend on the instances
+    assert torch.equal(res.cloud, ref.cloud) and np.array_equal(res.row_off, ref.row_off)
+    assert np.array_equal(res.counts_project, ref.counts_project) and np.array_equal(res.counts_densify, ref.counts_densify)
+    # every repetition of an instance yields the records of the original instance
+    def key(b):
+        return b[:, 2:20]                                  # everything but view / instance numbering
+    rb, fb = res.boxes, ref.boxes
+    assert rb.shape[0] == fb.shape[0] + (rep - 1) * int(((fb[:, 1] >= m0) & (fb[:, 1] < m1)).sum())
+    for g in range(int(sum(wb.n_inst))):
+        if g < m0:
+            og = g
+        elif g < m0 + rep * n0:
+            og = m0 + (g - m0) % n0
+        else:
+            og = g - (rep - 1) * n0
+        a, b = rb[rb[:, 1] == g], fb[fb[:, 1] == og]
+        assert a.shape == b.shape and np.array_equal(key(a), key(b)), g
+        assert np.all(a[:, 0] == b[:, 0])                  # the original view number
+    assert sum(len(x) for x in res.label_lines) == rb.shape[0] - int((rb[:, 20] != 0).sum())
+    assert len(res.label_lines) == len(vb.n_inst)
+
+
+def test_more_than_32_instances_match_oracle():
+    """The same against the oracle (which loops over the instances like the reference): a view whose masks are repeated
+    until it holds 36 or more instances."""
+    fr = helpers.small_frame(4, 'nuscenes', scale=0.25)
+    vw = fr['views'][0]
+    n0 = int(vw['masks'].shape[0])
+    rep = 36 // n0 + 1
+    vw['masks'] = torch.cat([vw['masks']] * rep, 0)
+    vw['classes'] = np.tile(np.asarray(vw['classes']), rep)
+    vw['boxes2d'] = np.tile(np.asarray(vw['boxes2d'], np.float32).reshape(-1, 4), (rep, 1))
+    inp, (fov, allp, lines, recs, dbg) = helpers.oracle_view(fr)
+    assert inp['masks'].shape[0] == n0 * rep > 32
+    pipe = pipeline.FusionPipeline(0)
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, cloud_dtype=torch.float64, instances=True)
+    assert res.seg_counts.shape[0] == n0 * rep
+    for i, d in enumerate(dbg['inst']):
+        got = res.seg_counts[i]
+        assert (got[0], got[1], got[2], got[3], got[4]) == (d['nL'], d['nP'], d['nL1'], d['nP1'], d['nP2']), (i, got, d)
+    assert compare_boxes(res, recs) > 0
+    assert len(res.label_lines[0]) == len(lines)
+
+
 @pytest.mark.parametrize('parts', [2, 3])
 def test_run_split_equals_run(parts):
     """The concurrent frame-group run (own stream, context and host thread per group) returns exactly what the plain
