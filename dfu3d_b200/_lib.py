@@ -24,7 +24,7 @@ assert VIEW_DTYPE.itemsize == 248, VIEW_DTYPE.itemsize
 
 FUSION_DTYPE = np.dtype([
     ('H', np.int32), ('W', np.int32), ('Hm', np.int32), ('Wm', np.int32), ('bound_x', np.int32), ('bound_y', np.int32),
-    ('round_mode', np.int32), ('image_is_i32', np.int32), ('min_depth', np.float32), ('pad1', np.float32),
+    ('round_mode', np.int32), ('image_is_i32', np.int32), ('min_depth', np.float32), ('max_voxels', np.int32),
     ('max_z', np.float64), ('plane_offset', np.float64), ('plane_range', np.float64, (4,)), ('min_theta', np.float64),
     ('max_per_voxel', np.int32), ('no_fov_cull', np.int32),
 ], align=True)

@@ -483,6 +483,30 @@ __global__ void __launch_bounds__(256) k_vox_finish(const dfu_view* __restrict__
   repy_label[t] = labelmap ? __ldg(labelmap + ((size_t)v * q.Hm + row) * q.Wm + col) : 0u;
 }
 
+// The voxeliser's max_num_voxels (my_loader.py:74): a view keeps its first `maxv` angular voxels in first-appearance order
+// (= the order of the voxel lists), the points of later voxels are dropped.  Rare (the table has 1.29 M cells against
+// the default limit of 10^6), so the lists are simply re-packed: thread per KEPT voxel, out of place.
+__global__ void __launch_bounds__(256) k_vox_cut(int V, const int64_t* __restrict__ old_off, const int64_t* __restrict__ new_off,
+                                                  int64_t old_total, int64_t new_total, const int32_t* __restrict__ repz,
+                                                  const int32_t* __restrict__ repy, const double* __restrict__ repy_xyz,
+                                                  const uint32_t* __restrict__ repy_label, int32_t* __restrict__ oz,
+                                                  int32_t* __restrict__ oy, double* __restrict__ oxyz, uint32_t* __restrict__ ol) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= new_total) return;
+  int lo = 0, hi = V;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (new_off[mid] <= t) lo = mid; else hi = mid;
+  }
+  const int64_t src = old_off[lo] + (t - new_off[lo]);
+  oz[t] = repz[src];
+  oy[t] = repy[src];
+  ol[t] = repy_label[src];
+  oxyz[t] = repy_xyz[src];
+  oxyz[new_total + t] = repy_xyz[old_total + src];
+  oxyz[2 * new_total + t] = repy_xyz[2 * old_total + src];
+}
+
 __global__ void k_vox_view_offsets(const int64_t* __restrict__ blkoff, int V, int bpv, int64_t* out) {
   int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v <= V) out[v] = blkoff[(int64_t)v * bpv];
@@ -731,6 +755,49 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
     k_vox_finish<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(vd, q, V, bpv, owner, blkoff, blkbits, key, ctx->depth,
                                                                  ctx->labelmap, table, repz, repy, repy_xyz, repy_label, nvox);
     DFU_LAUNCH_CHECK(ctx);
+  }
+  // ---- max_num_voxels: keep the first max_voxels voxels of every view
+  {
+    const int64_t maxv = ctx->prm.max_voxels > 0 ? (int64_t)ctx->prm.max_voxels : INT64_MAX;
+    bool cut = false;
+    for (int v = 0; v < V; v++) cut = cut || ctx->cnt_vox[v] > maxv;
+    if (cut) {
+      int64_t* noff_h = (int64_t*)malloc((size_t)(V + 1) * 8);
+      if (!noff_h) return dfu_set_err(ctx, DFU_ERR_CUDA, "out of host memory");
+      int64_t tot = 0;
+      for (int v = 0; v < V; v++) {
+        noff_h[v] = tot;
+        tot += ctx->cnt_vox[v] < maxv ? ctx->cnt_vox[v] : maxv;
+      }
+      noff_h[V] = tot;
+      // scratch: new offsets | repz | repy | label | xyz   (the scans' temporary storage is free by now)
+      const size_t offb = ((size_t)(V + 1) * 8 + 255) & ~(size_t)255;
+      char* tmpc = (char*)dfu_slot(ctx, SL_CUBTMP, offb + (size_t)tot * 36 + 1024);
+      if (!tmpc) { free(noff_h); return DFU_ERR_CUDA; }
+      int64_t* noff = (int64_t*)tmpc;
+      double* oxyz = (double*)(tmpc + offb);
+      int32_t* oz = (int32_t*)(oxyz + 3 * tot);
+      int32_t* oy = oz + tot;
+      uint32_t* ol = (uint32_t*)(oy + tot);
+      cudaError_t ce = cudaMemcpyAsync(noff, noff_h, (size_t)(V + 1) * 8, cudaMemcpyHostToDevice, st);   // pageable: staged before return
+      if (ce == cudaSuccess && tot > 0) {
+        k_vox_cut<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(V, voxoff, noff, nvox, tot, repz, repy, repy_xyz, repy_label, oz, oy, oxyz, ol);
+        ctx->launches++;
+        ce = cudaGetLastError();
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(repz, oz, (size_t)tot * 4, cudaMemcpyDeviceToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(repy, oy, (size_t)tot * 4, cudaMemcpyDeviceToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(repy_label, ol, (size_t)tot * 4, cudaMemcpyDeviceToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(repy_xyz, oxyz, (size_t)tot * 24, cudaMemcpyDeviceToDevice, st);
+      }
+      if (ce == cudaSuccess) ce = cudaMemcpyAsync(voxoff, noff, (size_t)(V + 1) * 8, cudaMemcpyDeviceToDevice, st);
+      for (int v = 0; v <= V; v++) ctx->off_vox[v] = noff_h[v];
+      for (int v = 0; v < V; v++) {
+        ctx->cnt_vox[v] = noff_h[v + 1] - noff_h[v];
+        if (counts_host) counts_host[v * 4 + 2] = ctx->cnt_vox[v];
+      }
+      free(noff_h);
+      if (ce != cudaSuccess) return dfu_set_err(ctx, DFU_ERR_CUDA, "voxel cut: %s", cudaGetErrorString(ce));
+    }
   }
   ctx->table_clean_ptr = (void*)table;
   ctx->table_clean_bytes = ctx->slot_bytes[SL_TABLE];

@@ -35,6 +35,7 @@ class FusionConfig:
     plane_range: tuple = (-54.0, 54.0, -54.0, 54.0)   # :471
     min_theta: float = 1.5                 # :176
     max_per_voxel: int = 100               # :73
+    max_voxels: int = 1000000              # :74 (angular voxels kept per view, first-appearance order)
     gate_dist: float = 0.1                 # :603
     cluster_R0: float = 3.0                # rectangle_fitting.py:36
     cluster_Rd: float = 0.001              # rectangle_fitting.py:37
@@ -124,6 +125,7 @@ def fusion_params(cfg, H, W, Hm, Wm, image_is_i32=False, round_mode=0, no_fov_cu
     p['plane_range'] = np.asarray(cfg.plane_range, np.float64)
     p['min_theta'] = cfg.min_theta
     p['max_per_voxel'] = cfg.max_per_voxel
+    p['max_voxels'] = cfg.max_voxels
     p['no_fov_cull'] = int(no_fov_cull)
     return p
 

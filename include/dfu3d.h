@@ -59,7 +59,7 @@ typedef struct dfu_fusion_params {
   int32_t round_mode;        /* 0 = np.round half-to-even (my_loader.py:520); 1 = truncate (my_loader.py:113) */
   int32_t image_is_i32;      /* image dtype: 0 = uint8 [.,3], 1 = int32 [.,3] */
   float   min_depth;         /* my_loader.py:507 (0.001) */
-  float   pad1;
+  int32_t max_voxels;        /* my_loader.py:74 (1000000): angular voxels kept per view, in first-appearance order; 0 = no limit */
   double  max_z;             /* height gate of my_loader.py:540 (1.0) */
   double  plane_offset;      /* my_loader.py:471 (0.05) */
   double  plane_range[4];    /* x lo, x hi, y lo, y hi (my_loader.py:471: -54, 54, -54, 54) */

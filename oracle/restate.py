@@ -420,7 +420,7 @@ PRESETS = {   # SURVEY.md 8(a) "Variants": literals of my_loader.py vs my_loader
 
 def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes, boxes2d, plane,
                       bounds=(1600, 900), return_debug=False, only_range=((-54, 54), (-54, 54)), instances=True,
-                      legacy=False, max_per_voxel=100):
+                      legacy=False, max_per_voxel=100, max_voxels=1000000):
     """Restatement of my_loader.py:502-617 (nuScenes preset).  ``lidar`` is already FOV culled
     (vis_utils.py:152-154); ``plane`` replaces the unseeded RANSAC of :511 (Q8).  Returns
     (all_points [N+M',8] float64, label lines, records, debug dict)."""
@@ -437,7 +437,7 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
     low = new_p[:, 2] < 1.
     new_p0 = new_p[low]
     pix0 = (rows * depth.shape[1] + cols)[low]
-    rep_z, rep_y, overflow = angular_dedup(new_p0, max_per_voxel=max_per_voxel)
+    rep_z, rep_y, overflow = angular_dedup(new_p0, max_per_voxel=max_per_voxel, max_voxels=max_voxels)
     new_p1 = new_p0[rep_z].copy()
     new_p1[:, -1] = 1
     lines, recs = [], []
@@ -478,7 +478,7 @@ def depth2pointsrgbpm(depth, image, calib, lidar, thing_classes, masks, classes,
     return all_points, lines, recs
 
 
-def run_view(inp, plane=None, return_debug=False, preset='nuscenes', max_per_voxel=100):
+def run_view(inp, plane=None, return_debug=False, preset='nuscenes', max_per_voxel=100, max_voxels=1000000):
     """vis_utils.save_depth_as_points (vis_utils.py:142-166) minus file I/O, on the dict layout of
     dfu3d_b200.synth.view_as_reference_inputs."""
     calib = Calib(inp['P2'], inp['R0'], inp['V2C'])
@@ -490,7 +490,7 @@ def run_view(inp, plane=None, return_debug=False, preset='nuscenes', max_per_vox
     depth = np.array(inp['depth'], np.float32).reshape(H, W, 1)
     pl = inp['plane'] if plane is None else plane
     out = depth2pointsrgbpm(depth, image, calib, lidar, inp['thing_classes'], inp['masks'], inp['classes'],
-                            inp['boxes2d'], pl, return_debug=return_debug, max_per_voxel=max_per_voxel, **PRESETS[preset])
+                            inp['boxes2d'], pl, return_debug=return_debug, max_per_voxel=max_per_voxel, max_voxels=max_voxels, **PRESETS[preset])
     return (fov,) + tuple(out)
 
 

@@ -83,6 +83,36 @@ def test_kitti_preset_matches_oracle():
     assert np.array_equal(cloud[nF:, 3:], allp[nF:, 3:])
 
 
+@pytest.mark.parametrize('seed,maxv', [(3, 700), (4, 1), (5, 2500)])
+def test_voxel_count_limit_keeps_the_first_voxels(seed, maxv):
+    """The voxeliser's max_num_voxels (my_loader.py:74, 10^6 in the reference): a view keeps its first max_voxels angular
+    voxels in first-appearance order, the points of the others are dropped from the cloud and from the instances' pseudo
+    points.  A small limit on small frames; two views, so that the lists are re-packed across views."""
+    fr = helpers.small_frame(seed, 'nuscenes', scale=0.25, n_cams=2)
+    from oracle import restate
+    free = pipeline.FusionPipeline(0).run(pipeline.batch_from_frames([fr], torch.device('cuda', 0)), cloud_dtype=torch.float64)
+    pipe = pipeline.FusionPipeline(0, config=pipeline.FusionConfig(max_voxels=maxv))      # same context: run it last
+    vb = pipeline.batch_from_frames([fr], pipe.device)
+    res = pipe.run(vb, cloud_dtype=torch.float64, instances=True)
+    assert int(free.counts_densify[:, 2].max()) > maxv                      # the limit bites
+    rz, ry, xz, xy = helpers.emit_voxels(pipe, int(res.counts_densify[:, 2].sum()))
+    off = np.concatenate([[0], np.cumsum(res.counts_densify[:, 2])])
+    inst0 = 0
+    for v in range(2):
+        inp = synth.view_as_reference_inputs(fr, v)
+        fov, allp, lines, recs, dbg = restate.run_view(inp, return_debug=True, max_voxels=maxv)
+        nv = int(res.counts_densify[v, 2])
+        assert nv == min(maxv, int(free.counts_densify[v, 2])) == dbg['rep_z_pix'].shape[0]
+        assert np.array_equal(rz[off[v]:off[v + 1]], dbg['rep_z_pix']) and np.array_equal(ry[off[v]:off[v + 1]], dbg['rep_y_pix'])
+        cloud = res.cloud[int(res.row_off[v]):int(res.row_off[v + 1])].cpu().numpy()
+        nF = int(fov.sum())
+        assert cloud.shape == allp.shape
+        np.testing.assert_allclose(cloud[nF:, :3], allp[nF:, :3], rtol=1e-5, atol=1e-9)
+        for i, d in enumerate(dbg['inst']):
+            assert tuple(res.seg_counts[inst0 + i][:2]) == (d['nL'], d['nP'])
+        inst0 += len(dbg['inst'])
+
+
 @pytest.mark.parametrize('seed,mpv', [(3, 12), (4, 10), (5, 16)])
 def test_overflowing_voxels_keep_the_first_points_in_input_order(seed, mpv):
     """the reference's voxeliser keeps the first max_num_points_per_voxel points of an angular voxel in
