@@ -26,7 +26,16 @@ struct S1Out {
   uint32_t label;
 };
 
-__device__ __forceinline__ S1Out s1_point(const dfu_view& vw, const S1Prm& q, float4 p, const uint32_t* __restrict__ lm) {
+// norm of the plane's normal, the same expression for every point of a view (np.linalg.norm: sqrt of the sum of squares)
+__device__ __forceinline__ double s1_plane_norm(const dfu_view& vw) {
+  return __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(vw.plane[0], vw.plane[0]), __dmul_rn(vw.plane[1], vw.plane[1])),
+                              __dmul_rn(vw.plane[2], vw.plane[2])));
+}
+
+// fov_only: the fused pipeline reads the plane / bounds flags and the label of FOV points only (the three lists nest),
+// so a point outside the FOV (5 of 6 for a six-camera frame) skips the float64 plane distance and the label gather.
+__device__ __forceinline__ S1Out s1_point(const dfu_view& vw, const S1Prm& q, float4 p, const uint32_t* __restrict__ lm,
+                                          double nrm, bool fov_only = false) {
   S1Out o;
   // lidar_to_rect (calibration_kitti.py:104-112)
   float rx = dfu_row4_f32(p.x, p.y, p.z, 1.0f, vw.M43, 0, 3);
@@ -41,13 +50,17 @@ __device__ __forceinline__ S1Out s1_point(const dfu_view& vw, const S1Prm& q, fl
   o.depth = __fsub_rn(h2, vw.P2T[3 * 3 + 2]);
   // get_fov_flag (vis_utils.py:108-123): un-rounded coordinates against the depth-map shape
   bool fov = q.no_fov || ((o.u >= 0.0f) && (o.u < (float)q.W) && (o.v >= 0.0f) && (o.v < (float)q.H) && (o.depth >= 0.0f));
+  if (fov_only && !fov) {
+    o.px = o.py = 0;
+    o.label = 0;
+    o.flags = 0;
+    return o;
+  }
   // above_plane (my_loader.py:471-484); dgemv order measured on the reference container: y*b first
   double acc = __dmul_rn((double)p.y, vw.plane[1]);
   acc = __fma_rn((double)p.x, vw.plane[0], acc);
   acc = __fma_rn((double)p.z, vw.plane[2], acc);
   double dist = __dadd_rn(acc, vw.plane[3]);
-  double nrm = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(vw.plane[0], vw.plane[0]), __dmul_rn(vw.plane[1], vw.plane[1])),
-                                    __dmul_rn(vw.plane[2], vw.plane[2])));
   dist = __ddiv_rn(dist, nrm);
   bool in_rng = ((double)p.x < q.xhi) && ((double)p.x > q.xlo) && ((double)p.y < q.yhi) && ((double)p.y > q.ylo);
   bool above = !((dist < q.plane_offset) && in_rng);
@@ -71,16 +84,19 @@ __global__ void __launch_bounds__(S1_THREADS) k_project(const dfu_view* __restri
                                                         float* out_depth, int2* out_pix, uint8_t* out_flags,
                                                         uint32_t* out_label, int32_t* blkcnt) {
   __shared__ dfu_view vw;
+  __shared__ double s_nrm;
   const int v = blockIdx.y;
   for (int i = threadIdx.x; i < (int)(sizeof(dfu_view) / 4); i += blockDim.x)
     ((uint32_t*)&vw)[i] = ((const uint32_t*)(views + v))[i];
+  __syncthreads();
+  if (threadIdx.x == 0) s_nrm = s1_plane_norm(vw);
   __syncthreads();
   const int i = blockIdx.x * S1_THREADS + threadIdx.x;
   unsigned fl = 0;
   if (i < vw.lidar_cnt) {
     float4 p = __ldg(lidar + vw.lidar_off + i);
     const uint32_t* lm = labelmap ? labelmap + (size_t)v * q.Hm * q.Wm : nullptr;
-    S1Out o = s1_point(vw, q, p, lm);
+    S1Out o = s1_point(vw, q, p, lm, s_nrm, blkcnt != nullptr && !q.no_fov);
     const int64_t s = vw.slot_off + i;
     if (out_uv) out_uv[s] = make_float2(o.u, o.v);
     if (out_depth) out_depth[s] = o.depth;
@@ -116,6 +132,8 @@ __global__ void __launch_bounds__(S1_THREADS) k_lists_scatter(const dfu_view* __
   const int i = blockIdx.x * S1_THREADS + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   unsigned fl = (i < cnt) ? flags[slot_off + i] : 0u;
+  // a camera sees about a sixth of the sweep and the rows are in azimuth order: most blocks hold no FOV point at all
+  if (!__syncthreads_or((fl & 1u) != 0)) return;
   bool p[3] = {(fl & 1u) != 0, (fl & 3u) == 3u, (fl & 7u) == 7u};
   int pre[3];
 #pragma unroll
@@ -201,7 +219,7 @@ __global__ void __launch_bounds__(S1_THREADS) k_sparse_winner(const dfu_view* __
   __syncthreads();
   const int i = blockIdx.x * S1_THREADS + threadIdx.x;
   if (i >= vw.lidar_cnt) return;
-  S1Out o = s1_point(vw, q, __ldg(lidar + vw.lidar_off + i), nullptr);
+  S1Out o = s1_point(vw, q, __ldg(lidar + vw.lidar_off + i), nullptr, 1.0, true);
   // fov implies 0 <= u < W, 0 <= v < H, so the second bounds test of my_loader.py:110-111 is implied
   if (o.flags & 1u) atomicMax(winner + ((int64_t)v * q.H + o.py) * q.W + o.px, i);
 }
@@ -220,7 +238,7 @@ __global__ void __launch_bounds__(256) k_sparse_write(const dfu_view* __restrict
   int wi = winner[g];
   double d = 0.0;
   if (wi >= 0) {
-    S1Out o = s1_point(vw, q, __ldg(lidar + vw.lidar_off + wi), nullptr);
+    S1Out o = s1_point(vw, q, __ldg(lidar + vw.lidar_off + wi), nullptr, s1_plane_norm(vw));
     d = (double)o.depth;
   }
   out[g] = d;
