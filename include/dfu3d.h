@@ -182,7 +182,9 @@ int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t capacity_row
 int dfu_fuse_emit_voxels(dfu_ctx* ctx, int32_t* repz_pix, int32_t* repy_pix, double* repz_xyz, double* repy_xyz,
                          int64_t capacity);
 
-/* Per-slot S1 results of the bound batch (same layout as dfu_project_label). */
+/* Per-slot S1 results of the bound batch (same layout as dfu_project_label).  Debug / parity output: the fused pipeline
+ * evaluates the plane flag, the bounds flag, the pixel index and the label of FOV points only (the three lists nest);
+ * a slot outside the FOV reads flags = 0, pix = (0, 0), label = 0 unless the batch was bound with no_fov_cull. */
 int dfu_fuse_emit_project(dfu_ctx* ctx, int32_t* out_pix, uint8_t* out_flags, uint32_t* out_label);
 
 /* Instances: gather of inherited LiDAR points and masked pseudo points, radius filters
