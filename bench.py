@@ -290,6 +290,14 @@ def main():
     json_fd = None
     torch.cuda.set_device(local)
     numa = bind_to_gpu_numa(local) if world > 1 else None
+    # Host cores per rank (reported): with 8 ranks on a 32-core host the host side of a step stretches (two group threads,
+    # the gather thread and NCCL's threads per rank on 4 cores).  Measured there: 23.5 ms per step as is, 25.0 ms with the
+    # library sleeping in its stream syncs (DFU3D_BLOCKING_SYNC=1), 28.2 ms with one frame group in flight (--parts 1).
+    try:
+        cores_per_rank = len(os.sched_getaffinity(0)) / float(world)
+    except Exception:
+        cores_per_rank = (os.cpu_count() or 1) / float(world)
+
     dev = torch.device('cuda', local)
     if world > 1:
         # an externally set NCCL_DEBUG is honoured (the driver counts ranks from the INFO lines); NCCL writes to fd 1,
@@ -333,7 +341,7 @@ def main():
             def job():
                 torch.cuda.set_device(local)
                 t0 = time.perf_counter()
-                allb = shard.gather_boxes(boxes, device=dev)
+                allb = shard.gather_boxes(boxes, device=dev, dst=0)     # the lists of all ranks, ordered, on rank 0's host
                 gathered['boxes'] = int(allb.shape[0])
                 gathered['seconds'] = gathered.get('seconds', 0.0) + time.perf_counter() - t0
                 gathered['calls'] = gathered.get('calls', 0) + 1
@@ -348,11 +356,13 @@ def main():
         if f is not None:
             f.result()
 
+    parts = a.parts if a.parts > 0 else 2
+
     def step_resident():
         # two frame groups in flight (own stream / context / host thread each): the host-side sizing between the stages of
         # one group overlaps the kernels of the other
         vb.labelmap = None
-        return finish(pipe.run_split(vb, cloud_dtype=torch.float16, instances=True, want_lines=True, parts=a.parts))
+        return finish(pipe.run_split(vb, cloud_dtype=torch.float16, instances=True, want_lines=True, parts=parts))
 
     def step_profiled():
         vb.labelmap = None
@@ -508,6 +518,8 @@ def main():
                 'dtype': 'f64', 'data': 'synthetic', 'config': workload_config(a), 'e2e': e2e,
                 'gpu_launches': int(launches), 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
                 'kernels': kernels, 'batch': st, 'filters': filt, 'numa_node_rank0': numa,
+                'frame_groups_in_flight': parts, 'host_cores_per_rank': cores_per_rank,
+                'blocking_stream_syncs': os.environ.get('DFU3D_BLOCKING_SYNC') == '1',
                 'box_gather': ({'records': gathered['boxes'], 'helper_thread_wall_ms_per_call': 1e3 * gathered.get('seconds', 0.0) / max(gathered.get('calls', 1), 1),
                                 'how': 'helper thread, overlapped with the next step, joined inside the timed region'}
                                if world > 1 else None)}

@@ -22,6 +22,10 @@ struct dfu_ctx {
   // pinned host staging for small read-backs
   void* pinned;
   size_t pinned_bytes;
+  // stream syncs of the fused pipeline: spin (default) or sleep on a blocking event (DFU3D_BLOCKING_SYNC=1 at dfu_create:
+  // for hosts with fewer free cores than waiting threads, e.g. 8 ranks x 3 threads on 32 cores)
+  int blocking_sync;
+  cudaEvent_t sync_ev;
   // ---- bound batch (dfu_fuse_begin) ----
   cudaStream_t stream;
   int V;
@@ -132,6 +136,7 @@ int dfu_exclusive_sum_i32(dfu_ctx* ctx, cudaStream_t stream, const int32_t* in, 
 // group of FusionPipeline.run_host) a 90 KB cudaMemcpyAsync from pinned memory waited until that upload had finished
 // (measured: 42 ms instead of 4 ms for the instance stage).  src must lie inside dfu_pinned() memory, bytes % 4 == 0.
 int dfu_upload_pinned(dfu_ctx* ctx, cudaStream_t stream, void* dst_dev, const void* src_pinned, size_t bytes);
+cudaError_t dfu_stream_sync(dfu_ctx* ctx, cudaStream_t stream);
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ unsigned long long dfu_order_f64(double v) {

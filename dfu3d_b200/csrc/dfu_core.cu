@@ -64,6 +64,16 @@ int dfu_upload_pinned(dfu_ctx* ctx, cudaStream_t stream, void* dst_dev, const vo
   return DFU_OK;
 }
 
+cudaError_t dfu_stream_sync(dfu_ctx* ctx, cudaStream_t stream) {
+  if (!ctx->blocking_sync) return cudaStreamSynchronize(stream);
+  if (!ctx->sync_ev) {
+    cudaError_t e = cudaEventCreateWithFlags(&ctx->sync_ev, cudaEventBlockingSync | cudaEventDisableTiming);
+    if (e != cudaSuccess) return e;
+  }
+  cudaError_t e = cudaEventRecord(ctx->sync_ev, stream);
+  return e != cudaSuccess ? e : cudaEventSynchronize(ctx->sync_ev);
+}
+
 struct I32ToI64 {
   __host__ __device__ int64_t operator()(const int32_t& v) const { return (int64_t)v; }
 };
@@ -97,6 +107,8 @@ extern "C" int dfu_create(dfu_ctx** out, int device) {
   dfu_ctx* c = (dfu_ctx*)calloc(1, sizeof(dfu_ctx));
   if (!c) return DFU_ERR_CUDA;
   c->device = device;
+  const char* bs = getenv("DFU3D_BLOCKING_SYNC");
+  c->blocking_sync = bs && bs[0] == '1';
   *out = c;
   return DFU_OK;
 }
@@ -108,6 +120,7 @@ extern "C" void dfu_destroy(dfu_ctx* ctx) {
   for (int i = 0; i < DFU_NSLOTS; i++)
     if (ctx->slot[i]) cudaFree(ctx->slot[i]);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->sync_ev) cudaEventDestroy(ctx->sync_ev);
   if (ctx->prof_ev) {
     for (int i = 0; i < 2 * DFU_PROF_POOL; i++) cudaEventDestroy(ctx->prof_ev[i]);
     free(ctx->prof_ev);

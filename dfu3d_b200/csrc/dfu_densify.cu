@@ -719,7 +719,7 @@ extern "C" int dfu_fuse_densify_sync(dfu_ctx* ctx, int64_t* counts_host, int all
   DFU_CUDA(ctx, cudaMemcpyAsync(pin, voxoff, (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(pin + (V + 1) * sizeof(int64_t), stats, (V * 8 + 8) * sizeof(unsigned long long),
                                 cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   memcpy(ctx->off_vox, pin, (V + 1) * sizeof(int64_t));
   const unsigned long long* hs = (const unsigned long long*)(pin + (V + 1) * sizeof(int64_t));
   int64_t total_over = 0, total_miss = 0;
@@ -856,7 +856,7 @@ extern "C" int dfu_fuse_emit_cloud(dfu_ctx* ctx, void* out, int dtype, int64_t c
   DFU_LAUNCH_CHECK(ctx);
   }
   // rowoff_h (pinned) is re-used by later calls: make sure the H2D copy is done
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   return DFU_OK;
 }
 
@@ -980,7 +980,7 @@ extern "C" int dfu_backproject_sync(dfu_ctx* ctx, void* stream, int V, const dfu
   int64_t* pin = (int64_t*)dfu_pinned(ctx, (V + 1) * sizeof(int64_t));
   if (!pin) return DFU_ERR_CUDA;
   DFU_CUDA(ctx, cudaMemcpyAsync(pin, voxoff, (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));   // also covers the pageable views_host copy
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));   // also covers the pageable views_host copy
   for (int v = 0; v < V; v++) counts_host[v] = pin[v + 1] - pin[v];
   const int64_t total = pin[V];
   if (!out_xyz) return DFU_OK;   // size query

@@ -341,7 +341,7 @@ extern "C" int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view
   int32_t hk[2] = {0, 0};
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[0], co.ncluster, 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(&hk[1], dfu_grid_err_ptr(ctx, GA_CLUSTER), 4, cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   if (hk[1] & 2) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "dfu_generate_anns_sync: R0 <= 0, Rd < 0 or R0 + Rd*|p| > sqrt(2)*R0 for some point (the cell neighbourhood of the clustering would miss pairs)");
   if (hk[1]) return dfu_set_err(ctx, DFU_ERR_DATA, "dfu_generate_anns_sync: a coordinate is NaN or the set spans more than 65533 cells");
   const int K = hk[0];
@@ -355,7 +355,7 @@ extern "C" int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view
   k_anns_single<<<(K + 127) / 128, 128, 0, st>>>(rect, K, *view_host, car_aspect_rule, (const unsigned long long*)(misc + 2), boxes);
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cudaMemcpyAsync(boxes_out_host, boxes, (size_t)K * DFU_BOX_DOUBLES * 8, cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   return DFU_OK;
 }
 
@@ -416,7 +416,7 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
     int rc = dfu_exclusive_sum_i32(ctx, st, cnt, poff, E);
     if (rc) return rc;
     DFU_CUDA(ctx, cudaMemcpyAsync(rb, poff + E, 8, cudaMemcpyDeviceToHost, st));
-    DFU_CUDA(ctx, cudaStreamSynchronize(st));
+    DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
     NP = rb[0];
   }
   if (NP >= 0x7fffffffLL) return dfu_set_err(ctx, DFU_ERR_DATA, "too many (point, instance) pairs");
@@ -514,7 +514,7 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   DFU_CUDA(ctx, cudaMemcpyAsync(rb + 1, dfu_grid_err_ptr(ctx, OPS_A), 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(rb_seg, seg_off, (size_t)(nseg + 1) * 8, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(rb_cnt, cnt12, (size_t)nseg * 8, cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   const int64_t NF = rb[0];
   if ((int32_t)rb[1] != 0) return dfu_set_err(ctx, DFU_ERR_DATA, "radius/gate grid: a coordinate is NaN or spans more than 65533 cells");
   if (seg_counts_host)
@@ -538,7 +538,7 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   if (rc) return rc;
   DFU_CUDA(ctx, cudaMemcpyAsync(rb, co.ncluster, 4, cudaMemcpyDeviceToHost, st));
   DFU_CUDA(ctx, cudaMemcpyAsync(rb + 1, dfu_grid_err_ptr(ctx, OPS_B), 4, cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   const int K = *(int32_t*)rb;
   if (*(int32_t*)(rb + 1) & 2) return dfu_set_err(ctx, DFU_ERR_UNSUPPORTED, "cluster: R0 <= 0, Rd < 0 or R0 + Rd*|p| > sqrt(2)*R0 for some point (the cell neighbourhood of the clustering would miss pairs)");
   if (*(int32_t*)(rb + 1) != 0) return dfu_set_err(ctx, DFU_ERR_DATA, "cluster grid: a coordinate is NaN or spans more than 65533 cells");
@@ -553,7 +553,7 @@ extern "C" int dfu_fuse_instances_sync(dfu_ctx* ctx, const dfu_inst_params* ip, 
   k_anns<<<(K + 127) / 128, 128, 0, st>>>(rect, K, co.first_point, finst, co.cluster_of_point, inst_off, idev, T.views, zmax, boxes);
   DFU_LAUNCH_CHECK(ctx);
   DFU_CUDA(ctx, cudaMemcpyAsync(boxes_out_host, boxes, (size_t)K * DFU_BOX_DOUBLES * 8, cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   if (seg_counts_host)
     for (int k = 0; k < K; k++) seg_counts_host[6 * (int64_t)boxes_out_host[(size_t)k * DFU_BOX_DOUBLES + 1] + 5] += 1;
   return DFU_OK;

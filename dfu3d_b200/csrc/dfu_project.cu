@@ -500,7 +500,7 @@ extern "C" int dfu_fuse_project_sync(dfu_ctx* ctx, int64_t* counts_host) {
   int64_t* pin = (int64_t*)dfu_pinned(ctx, 3 * (V + 1) * sizeof(int64_t));
   if (!pin) return DFU_ERR_CUDA;
   DFU_CUDA(ctx, cudaMemcpyAsync(pin, voff, 3 * (V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
-  DFU_CUDA(ctx, cudaStreamSynchronize(st));
+  DFU_CUDA(ctx, dfu_stream_sync(ctx, st));
   memcpy(ctx->off_project, pin, 3 * (V + 1) * sizeof(int64_t));
   for (int v = 0; v < V; v++)
     for (int j = 0; j < 3; j++) {

@@ -38,9 +38,10 @@ def globalise(boxes, frame_of_view):
     return out
 
 
-def gather_boxes(local_boxes, device=None, group=None):
-    """All ranks' box records on every rank, sorted by (frame, camera, instance, cluster).  No-op without an
-    initialised process group."""
+def gather_boxes(local_boxes, device=None, group=None, dst=None):
+    """All ranks' box records, sorted by (frame, camera, instance, cluster): on every rank (dst=None) or on rank `dst`
+    only (the other ranks get an empty list and skip the read-back and the sort).  No-op without an initialised
+    process group."""
     local = np.ascontiguousarray(np.asarray(local_boxes, np.float64).reshape(-1, BOX_DOUBLES))
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return sort_boxes(local)
@@ -48,7 +49,7 @@ def gather_boxes(local_boxes, device=None, group=None):
     backend = dist.get_backend(group)
     dev = torch.device('cpu') if backend == 'gloo' else (device or torch.device('cuda', torch.cuda.current_device()))
     if backend != 'gloo':
-        return sort_boxes(_gather_one_collective(local, world, dev, group))
+        return sort_boxes(_gather_one_collective(local, world, dev, group, dst))
     cnt = torch.tensor([local.shape[0]], dtype=torch.int64, device=dev)
     cnts = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
     dist.all_gather(cnts, cnt, group=group)
@@ -66,7 +67,7 @@ def gather_boxes(local_boxes, device=None, group=None):
 _CAP = {}
 
 
-def _gather_one_collective(local, world, dev, group):
+def _gather_one_collective(local, world, dev, group, dst=None):
     """NCCL path: ONE all_gather_into_tensor of [count | records padded to a capacity every rank agrees on] and one
     device->host copy (the list form needs two collectives, world + 1 host syncs for the counts and a copy per rank).
     The capacity is remembered; a rank that holds more records than it makes every rank repeat with the larger size."""
@@ -80,9 +81,12 @@ def _gather_one_collective(local, world, dev, group):
         buf = torch.from_numpy(host).to(dev)
         out = torch.empty((world * (cap + 1), BOX_DOUBLES), dtype=torch.float64, device=dev)
         dist.all_gather_into_tensor(out, buf, group=group)
-        h = out.cpu().numpy().reshape(world, cap + 1, BOX_DOUBLES)
-        counts = h[:, 0, 0].astype(np.int64)
+        # every rank needs the counts (they decide whether the round is repeated); the records only where they are wanted
+        counts = out.view(world, cap + 1, BOX_DOUBLES)[:, 0, 0].cpu().numpy().astype(np.int64)
         if int(counts.max()) <= cap:
+            if dst is not None and dist.get_rank(group) != dst:
+                return np.zeros((0, BOX_DOUBLES), np.float64)
+            h = out.cpu().numpy().reshape(world, cap + 1, BOX_DOUBLES)
             return np.concatenate([h[r, 1:1 + int(counts[r])] for r in range(world)], 0)
         while cap < int(counts.max()):
             cap *= 2
