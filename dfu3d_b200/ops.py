@@ -205,9 +205,14 @@ def crop_boxes(points, boxes, ctx=None):
         c64 = c64.to(ctx.device).contiguous()
     args = (ctx.h, ctx.stream, _lib.dptr(p) if p.numel() else None, Cc, n, _lib.dptr(b) if b.numel() else None, M,
             _lib.dptr(c64) if c64 is not None and c64.numel() else None)
-    ctx.check(ctx.lib.dfu_crop_boxes_sync(*args, None, 0, _lib.hptr(off)))
-    rows = torch.empty((max(int(off[-1]), 1), Cc), dtype=torch.float32, device=ctx.device)
-    ctx.check(ctx.lib.dfu_crop_boxes_sync(*args, _lib.dptr(rows), rows.shape[0], _lib.hptr(off)))
+    # one call: ground-truth boxes seldom overlap, so n rows nearly always suffice; the offsets are filled in even when the
+    # capacity does not, and only then is the call repeated with the exact size (no separate size query)
+    rows = torch.empty((max(n, 1), Cc), dtype=torch.float32, device=ctx.device)
+    rc = ctx.lib.dfu_crop_boxes_sync(*args, _lib.dptr(rows), rows.shape[0], _lib.hptr(off))
+    if rc == -3 and int(off[-1]) > rows.shape[0]:           # DFU_ERR_CAPACITY
+        rows = torch.empty((int(off[-1]), Cc), dtype=torch.float32, device=ctx.device)
+        rc = ctx.lib.dfu_crop_boxes_sync(*args, _lib.dptr(rows), rows.shape[0], _lib.hptr(off))
+    ctx.check(rc)
     return _out(rows[:int(off[-1])], as_np), off
 
 

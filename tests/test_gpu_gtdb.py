@@ -56,6 +56,16 @@ def test_crop_is_the_integrated_database_layout():
         gt = pts[mask64[i] > 0].copy()
         gt[:, :3] -= b64[i, :3]
         assert np.array_equal(rows64[off64[i]:off64[i + 1]], gt)
+    # more rows than points (every box taken three times: the first call's capacity does not suffice and it is repeated)
+    inside = pts[mask.any(0)]
+    rows3, off3 = ops.crop_boxes(inside, np.concatenate([boxes] * 3, 0))
+    assert off3[-1] > inside.shape[0] and rows3.shape[0] == off3[-1]
+    m3 = ops.points_in_boxes(inside, boxes)
+    assert np.array_equal(np.diff(off3), np.tile(m3.sum(1), 3))
+    k = boxes.shape[0] + 3
+    gt = inside[m3[3] > 0].copy()
+    gt[:, :3] -= boxes[3, :3]
+    assert np.array_equal(rows3[off3[k]:off3[k + 1]], gt)
     # empty inputs
     r0, o0 = ops.crop_boxes(pts[:0], boxes)
     assert r0.shape == (0, 8) and not o0.any()
