@@ -359,12 +359,14 @@ def main():
     parts = a.parts if a.parts > 0 else 2
 
     def step_resident():
+        pipeline.forget_marshalling(vb)        # nothing derived from the inputs on the host survives from step to step
         # two frame groups in flight (own stream / context / host thread each): the host-side sizing between the stages of
         # one group overlaps the kernels of the other
         vb.labelmap = None
         return finish(pipe.run_split(vb, cloud_dtype=torch.float16, instances=True, want_lines=True, parts=parts))
 
     def step_profiled():
+        pipeline.forget_marshalling(vb)
         vb.labelmap = None
         return finish(pipe.run(vb, cloud_dtype=torch.float16, instances=True, want_lines=True))
 
@@ -375,15 +377,18 @@ def main():
     sweep = {'left': 0}
 
     def step_e2e():
+        pipeline.forget_marshalling(host)
         sweep['left'] -= 1
         return finish(pipe.run_host(host, cloud_dtype=torch.float16, want_lines=True, prefetch=host if sweep['left'] > 0 else None))
 
     def step_e2e_single():
+        pipeline.forget_marshalling(host)
         return finish(pipe.run_host(host, cloud_dtype=torch.float16, want_lines=True))
 
     host_c = {}
 
     def step_e2e_compact():
+        pipeline.forget_marshalling(host_c['hb'])
         sweep['left'] -= 1
         return finish(pipe.run_host(host_c['hb'], cloud_dtype=torch.float16, want_lines=True,
                                     prefetch=host_c['hb'] if sweep['left'] > 0 else None))

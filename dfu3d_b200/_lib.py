@@ -80,6 +80,7 @@ _SIGS = {
     'dfu_radius_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P, _P]),
     'dfu_sor_filter': (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_double, _P, _P, _P]),
     'dfu_repr_f64': (C.c_int64, [_P, C.c_int64, _P, C.c_int64]),
+    'dfu_box2d_tokens': (C.c_int64, [_P, C.c_int64, _P, C.c_int64, _P]),
     'dfu_format_label_lines': (C.c_int64, [_P, C.c_int64, C.c_int, _P, _P, C.c_int, _P, _P, C.c_int64, _P, C.c_int64, _P]),
     'dfu_sor_counter': (C.c_int64, [_P, C.c_int]),
     'dfu_nn_gate': (C.c_int, [_P, _P, _P, C.c_int64, _P, C.c_int64, C.c_double, _P]),

@@ -9,7 +9,10 @@
 #include <cmath>
 #include "dfu_common.cuh"
 
-static char* put_repr_f64(char* p, double v) {
+// T = double: repr(float) / str(np.float64); T = float: str(np.float32) (numpy prints the shortest digits that round-trip
+// in float32; its positional / scientific switch differs, see below)
+template <typename T>
+static char* put_repr(char* p, T v) {
   if (std::isnan(v)) { memcpy(p, "nan", 3); return p + 3; }
   if (std::isinf(v)) {
     if (v < 0) *p++ = '-';
@@ -34,8 +37,12 @@ static char* put_repr_f64(char* p, double v) {
     for (; q < r.ptr; q++) ex = ex * 10 + (*q - '0');
     if (neg) ex = -ex;
   }
-  if (v == 0.0) { memcpy(p, "0.0", 3); return p + 3; }
-  if (ex >= -4 && ex < 16) {
+  if (v == (T)0) { memcpy(p, "0.0", 3); return p + 3; }
+  // Python's repr(float) chooses by the decimal exponent of the shortest digits (-4 <= ex < 16); numpy's str(np.float32)
+  // by the VALUE (1e-4 <= |v| < 1e6: float32(0.0001) = 9.9999997e-05 prints as 1e-04)
+  const double av = fabs((double)v);
+  const bool positional = sizeof(T) == 8 ? (ex >= -4 && ex < 16) : (av >= 1e-4 && av < 1e6);
+  if (positional) {
     if (ex < 0) {                                  // 0.000ddd
       *p++ = '0'; *p++ = '.';
       for (int i = 0; i < -ex - 1; i++) *p++ = '0';
@@ -66,6 +73,8 @@ static char* put_repr_f64(char* p, double v) {
 
 // vals [n] -> out: the n strings, each followed by '\n'.  Returns the bytes written or -needed if cap is too small
 // (48 bytes per value always suffice).
+static char* put_repr_f64(char* p, double v) { return put_repr<double>(p, v); }
+
 extern "C" int64_t dfu_repr_f64(const double* vals_host, int64_t n, char* out_host, int64_t cap) {
   if (!vals_host || !out_host || n < 0) return -1;
   if (cap < n * 48) return -(n * 48);
@@ -73,6 +82,24 @@ extern "C" int64_t dfu_repr_f64(const double* vals_host, int64_t n, char* out_ho
   for (int64_t i = 0; i < n; i++) {
     p = put_repr_f64(p, vals_host[i]);
     *p++ = '\n';
+  }
+  return (int64_t)(p - out_host);
+}
+
+// The four float32 tokens "xmin ymin xmax ymax" of every instance's 2-D box as str(np.float32) prints them
+// (my_loader.py:680 formats box2d[i] values that are float32), NUL-terminated, off_host[i] = start of instance i: the b2txt /
+// b2_off table of dfu_format_label_lines.  Returns the bytes written or -needed (100 bytes per instance always suffice).
+extern "C" int64_t dfu_box2d_tokens(const float* b2_host, int64_t n_inst, char* out_host, int64_t cap, int32_t* off_host) {
+  if (n_inst < 0 || (n_inst > 0 && (!b2_host || !out_host || !off_host))) return -1;
+  if (cap < n_inst * 100) return -(n_inst * 100);
+  char* p = out_host;
+  for (int64_t i = 0; i < n_inst; i++) {
+    off_host[i] = (int32_t)(p - out_host);
+    for (int k = 0; k < 4; k++) {
+      if (k) *p++ = ' ';
+      p = put_repr<float>(p, b2_host[4 * i + k]);
+    }
+    *p++ = '\0';
   }
   return (int64_t)(p - out_host);
 }

@@ -176,6 +176,7 @@ class FusionPipeline(object):
         self.lib = self.ctx.lib
         self._angles, _ = search_angles_cs()
         self._calib_cache = {}
+        self._calib_ids = {}
 
     # ------------------------------------------------------------------ helpers
     def build_views(self, vb):
@@ -185,22 +186,43 @@ class FusionPipeline(object):
             return cached
         V = len(vb.view_sweep)
         views = np.zeros(V, _lib.VIEW_DTYPE)
-        consts = []
+        # A rig has a handful of cameras: the derived constants are kept per calibration.  First by the identity of the three
+        # arrays (the same Calibration objects come back frame after frame; the entry holds them, so an id cannot be reused
+        # by other arrays), else by their bytes.  One template record per calibration, then one fancy-indexed copy.
+        rows, index = [], np.empty(V, np.int64)
+        seen = {}
         for v in range(V):
-            P2, R0, V2C = vb.calibs[v]
-            ck = (np.asarray(P2, np.float32).tobytes(), np.asarray(R0, np.float32).tobytes(), np.asarray(V2C, np.float32).tobytes())
-            c = self._calib_cache.get(ck)
-            if c is None:
-                if len(self._calib_cache) > 4096:
-                    self._calib_cache.clear()
-                c = self._calib_cache[ck] = calib_constants(P2, R0, V2C)
-            consts.append(c)
-        views['M43'] = np.stack([c['M43'].reshape(-1) for c in consts])
-        views['P2T'] = np.stack([c['P2T'].reshape(-1) for c in consts])
-        views['inv44'] = np.stack([c['inv44'].reshape(-1) for c in consts])
-        for k in ('cu', 'cv', 'fu', 'fv', 'tx', 'ty'):
-            views[k] = np.array([c[k] for c in consts], np.float32)
-        views['plane'] = np.stack([np.asarray(p if p is not None else (0, 0, 1, 1e9), np.float64) for p in vb.planes])
+            cal = vb.calibs[v]
+            ik = (id(cal[0]), id(cal[1]), id(cal[2]))
+            j = seen.get(ik)
+            if j is None:
+                ent = self._calib_ids.get(ik)
+                if ent is None or ent[0] is not cal[0] or ent[1] is not cal[1] or ent[2] is not cal[2]:
+                    P2, R0, V2C = cal
+                    ck = (np.asarray(P2, np.float32).tobytes(), np.asarray(R0, np.float32).tobytes(), np.asarray(V2C, np.float32).tobytes())
+                    c = self._calib_cache.get(ck)
+                    if c is None:
+                        if len(self._calib_cache) > 4096:
+                            self._calib_cache.clear()
+                        c = self._calib_cache[ck] = calib_constants(P2, R0, V2C)
+                    rec = np.zeros(1, _lib.VIEW_DTYPE)
+                    rec['M43'], rec['P2T'], rec['inv44'] = c['M43'].reshape(-1), c['P2T'].reshape(-1), c['inv44'].reshape(-1)
+                    for k in ('cu', 'cv', 'fu', 'fv', 'tx', 'ty'):
+                        rec[k] = c[k]
+                    if len(self._calib_ids) > 4096:
+                        self._calib_ids.clear()
+                    ent = self._calib_ids[ik] = (cal[0], cal[1], cal[2], rec)
+                j = seen[ik] = len(rows)
+                rows.append(ent[3])
+            index[v] = j
+        tab = np.zeros(len(rows), _lib.VIEW_DTYPE)      # (np.concatenate of structured arrays promotes field by field: 2 ms)
+        for i, r in enumerate(rows):
+            tab[i] = r[0]
+        views[:] = tab[index]
+        if all(p is not None for p in vb.planes):
+            views['plane'] = np.asarray(vb.planes, np.float64).reshape(V, 4)
+        else:
+            views['plane'] = np.stack([np.asarray(p if p is not None else (0, 0, 1, 1e9), np.float64) for p in vb.planes])
         sw = np.asarray([vb.sweeps[s] for s in vb.view_sweep], np.int64).reshape(V, 2)
         views['lidar_off'] = sw[:, 0]
         views['lidar_cnt'] = sw[:, 1]
@@ -307,7 +329,7 @@ class FusionPipeline(object):
         if cached is not None:
             return cached
         cfg = self.cfg
-        cls = np.concatenate([np.asarray(c, np.int64).reshape(-1) for c in vb.classes] + [np.zeros(0, np.int64)])
+        cls = np.concatenate(list(vb.classes) + [np.zeros(0, np.int64)]).astype(np.int64, copy=False).reshape(-1)
         assert cls.shape[0] == int(sum(vb.n_inst)), 'classes / n_inst mismatch'
         table = np.zeros(len(vb.thing_classes), _lib.INST_DTYPE)
         for c in np.unique(cls):
@@ -356,7 +378,7 @@ class FusionPipeline(object):
         res.seg_counts = segc[:tot]
         b2 = getattr(vb, '_boxes2d_flat', None)
         if b2 is None or b2.shape[0] != tot:
-            b2 = np.concatenate([np.asarray(b, np.float32).reshape(-1, 4) for b in vb.boxes2d] + [np.zeros((0, 4), np.float32)], 0)
+            b2 = np.concatenate([np.reshape(b, (-1, 4)) for b in vb.boxes2d] + [np.zeros((0, 4), np.float32)], 0).astype(np.float32, copy=False)
             vb._boxes2d_flat = b2
         res.box2d = b2[res.boxes[:, 1].astype(np.int64)] if res.boxes.shape[0] else np.zeros((0, 4), np.float32)
         if want_lines:
@@ -377,22 +399,22 @@ def _string_table(strings):
 
 def format_label_lines(names, boxes, vb, b2_flat, V):
     """All label lines of a batch (my_loader.py:680), per view: the text of format_label_line for every record that
-    the Car aspect rule did not skip, produced by the library's host routine dfu_format_label_lines (Python spends
-    ~1 us per repr(float); a 64-frame batch has ~32 k of them).  The float32 2-D box tokens are formatted once per
-    instance and cached on the ViewBatch."""
+    the Car aspect rule did not skip, produced by the library's host routines dfu_box2d_tokens + dfu_format_label_lines
+    (Python spends ~1 us per repr(float); a 64-frame batch has ~36 k of them).  Nothing is cached between calls."""
     lines = [[] for _ in range(V)]
     n = int(boxes.shape[0])
     if n == 0:
         return lines
     lib = _lib.load()
-    tabs = getattr(vb, '_label_tabs', None)
-    if tabs is None or tabs[4] != b2_flat.shape[0] or tabs[5] != tuple(names):
-        b2s = [' '.join(str(np.float32(x)) for x in row) for row in b2_flat]
-        nt, no = _string_table(names)
-        bt, bo = _string_table(b2s if b2s else [''])
-        tabs = (nt, no, bt, bo, b2_flat.shape[0], tuple(names))
-        vb._label_tabs = tabs
-    nt, no, bt, bo = tabs[:4]
+    # class names and the instances' float32 2-D box tokens as NUL-separated tables; both are rebuilt on every call (the
+    # tokens by the library: a batch has ~1000 instances, Python's str(np.float32) would take milliseconds)
+    nt, no = _string_table(names)
+    ni = int(b2_flat.shape[0])
+    b2c = np.ascontiguousarray(b2_flat, np.float32).reshape(-1, 4)
+    bt = np.empty(max(ni, 1) * 100, np.uint8)
+    bo = np.zeros(max(ni, 1), np.int32)
+    if lib.dfu_box2d_tokens(_lib.hptr(b2c), ni, _lib.hptr(bt), bt.shape[0], _lib.hptr(bo)) < 0:
+        raise RuntimeError('dfu_box2d_tokens failed')
     boxes = np.ascontiguousarray(boxes, np.float64)
     out = np.empty(n * 512, np.uint8)
     per_view = np.zeros(V, np.int64)
@@ -738,6 +760,18 @@ def _run_split(self, vb, cloud_dtype=torch.float16, instances=True, want_lines=T
         out.label_lines = None
     out.cloud = torch.cat([r.cloud for r in parts_res], 0)
     return out
+
+
+def forget_marshalling(batch):
+    """Drops everything the pipeline memoises on a ViewBatch / HostBatch between calls (view records and their device
+    copy, instance parameter table, flat 2-D boxes, frame-group splits), so that the next call marshals its inputs from
+    scratch as it does for a batch it has never seen.  bench.py calls it before every step: the synthetic batch is the
+    same object step after step, a sweep over a dataset never is."""
+    for k in ('_views', '_views_dev', '_inst_params', '_boxes2d_flat', '_split_holder', '_chunks'):
+        batch.__dict__.pop(k, None)
+    meta = getattr(batch, 'meta', None)
+    if meta is not None:
+        forget_marshalling(meta)
 
 
 def _total_launches(self):

@@ -254,6 +254,11 @@ int dfu_generate_anns_sync(dfu_ctx* ctx, void* stream, const dfu_view* view_host
                            int car_aspect_rule, double R0, double Rd, const double* angles_cs_host, int n_angles,
                            double* boxes_out_host, int64_t capacity, int64_t* n_boxes_host);
 
+/* The 2-D box tokens of the label lines: "xmin ymin xmax ymax" of every instance as str(np.float32(.)) prints them
+ * (my_loader.py:680; box2d holds float32), NUL-terminated, off_host[i] = start of instance i -- the b2txt / b2_off table of
+ * dfu_format_label_lines.  Host routine.  Returns the bytes written, or -needed when cap is too small. */
+int64_t dfu_box2d_tokens(const float* b2_host, int64_t n_inst, char* out_host, int64_t cap, int32_t* off_host);
+
 /* ---- label text (host only; my_loader.py:680) --------------------------------------------------------------
  * dfu_repr_f64: Python's str() / repr() of float64 values (shortest round-trip digits, fixed notation for
  * 1e-4 <= |v| < 1e16), one per line.  dfu_format_label_lines: every KITTI label line of a batch of box records

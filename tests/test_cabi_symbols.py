@@ -85,3 +85,15 @@ def test_host_label_text_equals_python_str_of_floats():
         if rec[20] == 0:
             want[int(rec[0])].append(pipeline.format_label_line(pipeline.NUSC_NAMES[int(rec[3])], rec, b2[int(rec[1])]))
     assert got == want
+    # float32 tokens of the 2-D boxes: str(np.float32(v)) on 4e4 values over 24 decades plus special cases
+    f = np.concatenate([(r.normal(size=40000) * 10.0 ** r.integers(-8, 16, 40000)).astype(np.float32),
+                        np.array([0.0, -0.0, 1e16, 1e-5, 1e-4, 123456.0, 1e15, 16777216.0, 0.1, 1600.0, 899.5, np.inf, -np.inf, np.nan,
+                                  1e-45, 3.4028235e38, 1e22, 100.0, 0.5, 1e8], np.float32)])
+    f = f[:f.size // 4 * 4].reshape(-1, 4)
+    out = np.empty(f.shape[0] * 100, np.uint8)
+    off = np.zeros(f.shape[0], np.int32)
+    nb = lib.dfu_box2d_tokens(_lib.hptr(f), f.shape[0], _lib.hptr(out), out.size, _lib.hptr(off))
+    assert nb > 0
+    toks = out[:nb].tobytes().decode().split('\0')[:-1]
+    assert len(toks) == f.shape[0] and off[1] == len(toks[0]) + 1
+    assert toks == [' '.join(str(np.float32(v)) for v in row) for row in f]
