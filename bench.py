@@ -13,8 +13,17 @@ torch.cuda.synchronize() and the max over ranks is reported.
 
 The line carries: value (inputs resident in HBM), e2e (host pinned buffers in, cloud + boxes back to
 the host, through dfu3d_b200.pipeline.FusionPipeline — the public API), roofline (dominant kernel,
-CUDA-event time inside the timed region, algorithmic bytes of SURVEY.md §8(d)), cpu_baseline (the
-oracle port on the host cores, bounded sample; rank 0, N=1 only), clocks, gpu_launches.
+CUDA-event time inside the timed region, algorithmic bytes of SURVEY.md §8(d); roofline.filters = the
+worst filter kernel of the configs[2] leg), cpu_baseline (the oracle port on the host cores, bounded
+sample; rank 0, N=1 only), clocks, gpu_launches.
+
+What is inside every timed step: the host-side marshalling of the inputs (pipeline.forget_marshalling
+drops every memoised record first: the synthetic batch is the same object each step, a sweep never
+is), all kernels, the label text of every box and, at N > 1, the gather of the box lists to rank 0's
+host (on a helper thread that overlaps the next step and is joined before the region ends).  The e2e
+legs are a sweep: each call names the next batch (run_host(prefetch=...)), whose first frame group is
+uploaded during the call before; exactly `steps` batches cross PCIe inside the region, and
+e2e.single_call is the same call without a successor.
 
 --impl reference: the reference's CPU implementation of the path.  The reference is pure Python over
 numpy / Open3D / spconv / sklearn (no native code) and /root/reference does not exist on the GPU box,
