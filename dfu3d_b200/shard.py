@@ -60,6 +60,8 @@ def gather_boxes(local_boxes, device=None, group=None, dst=None):
         pad[:local.shape[0]] = torch.from_numpy(local).to(dev)
     bufs = [torch.zeros_like(pad) for _ in range(world)]
     dist.all_gather(bufs, pad, group=group)
+    if dst is not None and dist.get_rank(group) != dst:
+        return np.zeros((0, BOX_DOUBLES), np.float64)
     parts = [b[:c].cpu().numpy() for b, c in zip(bufs, counts)]
     return sort_boxes(np.concatenate(parts, 0))
 

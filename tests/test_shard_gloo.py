@@ -41,6 +41,7 @@ def _worker(rank, world, port, n_frames, out_dir):
     local = np.concatenate(local + [np.zeros((0, shard.BOX_DOUBLES))], 0)
     allb = shard.gather_boxes(local)
     np.save(os.path.join(out_dir, 'rank%d.npy' % rank), allb)
+    np.save(os.path.join(out_dir, 'dst0_rank%d.npy' % rank), shard.gather_boxes(local, dst=0))     # delivery to rank 0 only
     dist.barrier()
     dist.destroy_process_group()
 
@@ -62,6 +63,9 @@ def test_gather_boxes_world2(tmp_path):
     assert np.array_equal(a, b)
     want = shard.sort_boxes(np.concatenate([shard.globalise(_fake_boxes(f), [(f, 0), (f, 1)]) for f in range(n_frames)], 0))
     assert np.array_equal(a, want)
+    d0 = np.load(os.path.join(str(tmp_path), 'dst0_rank0.npy'))
+    d1 = np.load(os.path.join(str(tmp_path), 'dst0_rank1.npy'))
+    assert np.array_equal(d0, want) and d1.shape == (0, shard.BOX_DOUBLES)
     key = a[:, [0, 21, 1, 2]]
     assert np.array_equal(key, key[np.lexsort((key[:, 3], key[:, 2], key[:, 1], key[:, 0]))])
 
