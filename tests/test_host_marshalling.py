@@ -23,7 +23,8 @@ def _batch(V=30, cams=3, seed=0, share=True):
     calibs = [rig[v % cams] if share else tuple(a.copy() for a in rig[v % cams]) for v in range(V)]
     return types.SimpleNamespace(
         view_sweep=[v // cams for v in range(V)], calibs=calibs, planes=[r.normal(size=4) for _ in range(V)],
-        sweeps=[(sum(1000 - j for j in range(i)), 1000 - i) for i in range(V // cams)],      # contiguous rows of `lidar` n_inst=n_inst, classes=[r.integers(0, 10, n) for n in n_inst],
+        sweeps=[(sum(1000 - j for j in range(i)), 1000 - i) for i in range(V // cams)],      # contiguous rows of `lidar`
+        n_inst=n_inst, classes=[r.integers(0, 10, n) for n in n_inst],
         boxes2d=[r.uniform(0, 900, (n, 4)).astype(np.float32) for n in n_inst], thing_classes=list(pipeline.NUSC_NAMES))
 
 
